@@ -1,0 +1,504 @@
+"""ALS matrix factorisation with side features on B200 — host orchestration.
+
+Same public surface as the reference model (`scripts/als.py:104-574`):
+
+    model = ALS(config=ALSConfig(...), lambda_w={"genres": 5.0})
+    model.fit(R, features={...}, tol=1e-3, min_iters=5, verbose=1)   # -> self
+    R_hat = model.predict(features={...})                            # (m, n) float64
+
+plus sparse-first entry points for shapes whose dense matrix cannot exist:
+`fit_coo(flat_idx, vals, shape, ...)` and `predict_pairs(rows, cols, ...)`.
+
+The model is  R ≈ U (V + Σ_f X_f W_f)ᵀ + μ + b_u + b_i  (als.py:10).  Python
+only sequences the work; every array operation of the fit loop
+(als.py:408-523) runs in libb200als kernels on device tensors that torch merely
+owns.  There is no CPU fallback: without the library or a B200 this raises.
+"""
+from __future__ import annotations
+
+import ctypes as C
+import logging
+
+import numpy as np
+import torch
+
+from . import _lib, graph as _graph
+from ._lib import StepArgs, check, ptr
+from .config import ALSConfig
+from .dist import Shard
+from .sparse import Ratings, ratings_from_dense, ratings_from_flat, row_schedule
+
+SCALE_FACTOR = 0.1      # als.py:93 — std of the Gaussian factor init
+EPS = 1e-10             # als.py:94 — added to every ridge term
+
+logger = logging.getLogger(__name__)
+
+
+def _round4(k: int) -> int:
+    return (k + 3) & ~3
+
+
+class ALS:
+    """Drop-in for `scripts.als.ALS` (constructor contract: als.py:134-191)."""
+
+    def __init__(self, config: ALSConfig, lambda_w: dict[str, float] | None = None) -> None:
+        if config is None:
+            raise ValueError("ALSConfig must be provided.")
+        self.cfg = config
+        self.W: dict[str, np.ndarray] = {}
+        self.lambda_w: dict[str, float] = dict(lambda_w or {})
+
+        core = self.cfg.core
+        self.n_factors = core.n_factors
+        self.n_iters = core.n_iters
+        self.lambda_u = core.lambda_u
+        self.lambda_v = core.lambda_v
+        self.random_state = core.random_state
+        self.update_w_every = core.update_w_every
+        self.pop_reg_mode = core.pop_reg_mode
+        # falsy (None or 0.0) bias penalties fall back to the factor penalties (als.py:166-167)
+        self.lambda_bu = self.cfg.biases.lambda_bu or self.lambda_u
+        self.lambda_bi = self.cfg.biases.lambda_bi or self.lambda_v
+        self.alpha = self.cfg.graph.alpha
+        sim = self.cfg.graph.sim
+        self.S_topk = sim.topk if sim is not None else None
+        self.S_eps = sim.eps if sim is not None else EPS
+
+        self.U: np.ndarray | None = None
+        self.V: np.ndarray | None = None
+        self.b_u: np.ndarray | None = None
+        self.b_i: np.ndarray | None = None
+        self.mu: float = 0.0
+        self.S: np.ndarray | None = None
+        self.history: dict[str, list[float]] = {
+            "train_rmse": [], "U_norm": [], "V_norm": [], "bu_norm": [], "bi_norm": []}
+
+        # build-side knobs (not part of the reference surface)
+        self.device = None                 # torch device; default: current CUDA device
+        self.gram_path = _lib.PATH_AUTO    # PATH_FFMA / PATH_UMMA force one Gram path
+        self.shard: Shard | None = None    # row sharding across ranks (dist.Shard)
+        self.timings: dict[str, float] = {}
+        self.launches_per_iter: int = 0
+
+    # ------------------------------------------------------------------ helpers
+    def _item_reg(self, counts: np.ndarray) -> np.ndarray:
+        """λ_{v,i}: uniform, or λ_v / sqrt(c_i + 1) (als.py:243-259)."""
+        if not self.pop_reg_mode:
+            return np.full_like(counts, self.lambda_v, dtype=float)
+        if self.pop_reg_mode == "inverse_sqrt":
+            return self.lambda_v / np.sqrt(counts + 1.0)
+        raise ValueError(f"Unknown pop_reg_mode '{self.pop_reg_mode}'")
+
+    def _converged(self, tol: float, window: int = 2) -> bool:
+        """RMSE gain over the last `window` iterations ≤ tol (als.py:283-297)."""
+        h = self.history["train_rmse"]
+        return len(h) >= window + 1 and (h[-window - 1] - h[-1]) <= tol
+
+    @staticmethod
+    def _check_features(features, n, where):
+        for name, X in features.items():
+            if X.shape[0] != n:
+                if where == "fit":
+                    raise ValueError(f"Feature '{name}' has {X.shape[0]} rows; "
+                                     f"expected {n} (number of items).")
+                raise ValueError(f"Feature '{name}' has {X.shape[0]} rows. "
+                                 f"Expected number of rows: {n}.")
+            if not np.isfinite(X).all():
+                raise ValueError(f"Feature '{name}' contains infinite values.")
+
+    def _dev(self):
+        if self.device is not None:
+            return torch.device(self.device)
+        if not torch.cuda.is_available():
+            raise _lib.B200ALSError("CUDA is not available: the ALS path has no CPU fallback")
+        return torch.device("cuda", torch.cuda.current_device())
+
+    # ------------------------------------------------------------------ fit
+    def fit(self, R: np.ndarray, features: dict[str, np.ndarray] | None = None,
+            tol: float = 1e-3, min_iters: int = 5, verbose: int = 1) -> "ALS":
+        """Fit on a dense (m, n) matrix with NaN = missing (als.py:300-529)."""
+        _lib.load()
+        _lib.require_device()
+        dev = self._dev()
+        with torch.cuda.device(dev):
+            ratings = ratings_from_dense(np.asarray(R), dev)
+            mu0 = float(np.nanmean(R))                                  # als.py:360
+            return self._fit_ratings(ratings, mu0, features, tol, min_iters, verbose, None)
+
+    def fit_coo(self, flat_idx, vals, shape, features=None, tol=1e-3, min_iters=5, verbose=1,
+                sorted_input=False, init=None) -> "ALS":
+        """Fit on observed entries `R.ravel()[flat_idx] = vals`, flat_idx = u*n + i
+        (the fold convention of create_folds.py:73-84, 200-206) — the same model as
+        `fit(matrix_from_indices(shape, flat_idx, vals))` without the dense matrix.
+
+        init: None → reference RNG stream on the host (als.py:329, 367-376);
+              "device" → N(0, 0.1²) drawn on the GPU (benchmarks at shapes where the
+              host draw would dominate; not seed-compatible with the reference);
+              dict(U=, V=, W={}) → given arrays.
+        """
+        _lib.load()
+        _lib.require_device()
+        dev = self._dev()
+        with torch.cuda.device(dev):
+            ratings = ratings_from_flat(flat_idx, vals, shape, dev, sorted_input=sorted_input)
+            if ratings.nnz == 0:
+                raise ValueError("no observed ratings")
+            mu0 = float(ratings.vals.sum(dtype=torch.float64).item() / ratings.nnz)
+            return self._fit_ratings(ratings, mu0, features, tol, min_iters, verbose, init)
+
+    def fit_ratings(self, ratings: Ratings, features=None, tol=1e-3, min_iters=5, verbose=1,
+                    init=None) -> "ALS":
+        """Fit on an already-built device CSR/CSC (`sparse.Ratings`)."""
+        _lib.load()
+        _lib.require_device()
+        with torch.cuda.device(ratings.vals.device):
+            mu0 = float(ratings.vals.sum(dtype=torch.float64).item() / max(ratings.nnz, 1))
+            return self._fit_ratings(ratings, mu0, features, tol, min_iters, verbose, init)
+
+    # ------------------------------------------------------------------ core loop
+    def _fit_ratings(self, rt: Ratings, mu0, features, tol, min_iters, verbose, init) -> "ALS":
+        if verbose == 0:
+            logging.disable(logging.CRITICAL)          # als.py:325-326 (global, as in the reference)
+        lib = _lib.load()
+        dev = rt.vals.device
+        m, n, nnz, k = rt.m, rt.n, rt.nnz, int(self.n_factors)
+        if not (1 <= k <= _lib.MAX_K):
+            raise ValueError(f"n_factors={k} outside the supported range [1, {_lib.MAX_K}]")
+        if nnz == 0:
+            raise ValueError("no observed ratings")
+        shard = self.shard or Shard()
+        features = features or {}
+        self._check_features(features, n, "fit")                        # als.py:346-351
+        if len(features) > _lib.MAX_FEATURES:
+            raise ValueError(f"at most {_lib.MAX_FEATURES} feature matrices are supported")
+        names = list(features.keys())
+        stream = torch.cuda.current_stream().cuda_stream
+        ld = _round4(k)
+        f32, f64 = torch.float32, torch.float64
+
+        # ---- graph (host build for argpartition tie parity, als.py:354-357) ----
+        use_graph = (self.alpha > 0.0) and (self.cfg.graph.sim is not None)
+        self.S = None
+        if use_graph:
+            fname = self.cfg.graph.sim.feature_name
+            Xg = features.get(fname)
+            if Xg is None:
+                logger.warning(f"GraphSim feature '{fname}' not found in features dict. "
+                               f"Graph regularization disabled.")
+            else:
+                self.S = _graph.similarity_topk(Xg, self.S_topk, self.S_eps)
+        use_graph = self.S is not None
+        D = self.S.sum(axis=1) if use_graph else None                   # als.py:357 (S's dtype)
+
+        # ---- init (als.py:360-376): same PCG64 stream, order U, V, W_f ----------
+        m_pad, n_pad = shard.padded_rows(m), shard.padded_rows(n)
+        U_d = torch.zeros(m_pad, ld, dtype=f32, device=dev)
+        V_d = torch.zeros(n_pad, ld, dtype=f32, device=dev)
+        W_d = [torch.zeros(features[nm].shape[1], ld, dtype=f32, device=dev) for nm in names]
+        W64_d = [torch.zeros(features[nm].shape[1] * k, dtype=f64, device=dev) for nm in names]
+        if init is None:
+            rng = np.random.default_rng(self.random_state)              # als.py:329
+            U_d[:m, :k] = torch.from_numpy(rng.normal(scale=SCALE_FACTOR, size=(m, k)).astype(np.float32)).to(dev)
+            V_d[:n, :k] = torch.from_numpy(rng.normal(scale=SCALE_FACTOR, size=(n, k)).astype(np.float32)).to(dev)
+            for f, nm in enumerate(names):
+                w0 = rng.normal(scale=SCALE_FACTOR, size=(features[nm].shape[1], k))
+                W64_d[f].copy_(torch.from_numpy(w0.reshape(-1)).to(dev))
+                W_d[f][:, :k] = torch.from_numpy(w0.astype(np.float32)).to(dev)
+        elif isinstance(init, str) and init == "device":
+            g = torch.Generator(device=dev)
+            g.manual_seed(int(self.random_state))
+            U_d[:m, :k].normal_(0.0, SCALE_FACTOR, generator=g)
+            V_d[:n, :k].normal_(0.0, SCALE_FACTOR, generator=g)
+            for f in range(len(names)):
+                W_d[f][:, :k].normal_(0.0, SCALE_FACTOR, generator=g)
+                W64_d[f].copy_(W_d[f][:, :k].reshape(-1).double())
+        else:
+            U_d[:m, :k] = torch.as_tensor(np.asarray(init["U"], dtype=np.float32)).to(dev)
+            V_d[:n, :k] = torch.as_tensor(np.asarray(init["V"], dtype=np.float32)).to(dev)
+            for f, nm in enumerate(names):
+                w0 = np.asarray(init["W"][nm], dtype=np.float64)
+                W64_d[f].copy_(torch.from_numpy(w0.reshape(-1)).to(dev))
+                W_d[f][:, :k] = torch.from_numpy(w0.astype(np.float32)).to(dev)
+        b_u_d = torch.zeros(m_pad, dtype=f32, device=dev)
+        b_i_d = torch.zeros(n_pad, dtype=f32, device=dev)
+        mu_d = torch.full((1,), float(mu0), dtype=f32, device=dev)
+        self.mu = float(mu0)
+        X_d = [torch.from_numpy(np.ascontiguousarray(features[nm], dtype=np.float32)).to(dev) for nm in names]
+        Z_d = torch.zeros(n_pad, ld, dtype=f32, device=dev) if names else V_d
+
+        # ---- regularisers (als.py:379-384, 426, 450-454), folded in float64 ------
+        item_counts = (rt.cindptr[1:] - rt.cindptr[:-1]).cpu().numpy().astype(float)
+        lambda_v_i = self._item_reg(item_counts).astype(float)
+        reg_item = lambda_v_i + EPS
+        if use_graph:
+            reg_item = reg_item + float(self.alpha) * D.astype(np.float64)
+        reg_item_d = torch.from_numpy(reg_item.astype(np.float32)).to(dev)
+        reg_user = float(np.float32(self.lambda_u + EPS))
+        lam_bu = float(np.float32(self.lambda_bu + EPS))
+        lam_bi = float(np.float32(float(self.lambda_bi) + EPS))
+
+        # ---- schedules ------------------------------------------------------------
+        u_order, u_nonempty = row_schedule(rt.indptr)
+        i_order, i_nonempty = row_schedule(rt.cindptr)
+        if shard.active:
+            ulo, uhi = shard.my_range(m)
+            ilo, ihi = shard.my_range(n)
+            uo = u_order[:u_nonempty]
+            u_list = uo[(uo >= ulo) & (uo < uhi)].contiguous()
+            io = i_order[:i_nonempty]
+            i_list = io[(io >= ilo) & (io < ihi)].contiguous()
+        else:
+            ulo, uhi, ilo, ihi = 0, m, 0, n
+            u_list, i_list = u_order[:u_nonempty], i_order[:i_nonempty]
+        if use_graph:
+            i_list = i_order[:i_nonempty]       # the Gauss–Seidel sweep is not sharded (§8e)
+
+        need = C.c_size_t(0)
+        check(lib.b200als_step_workspace_bytes(k, self.gram_path, max(m, n), C.byref(need)), "step_workspace_bytes")
+        ws = torch.empty(need.value, dtype=torch.uint8, device=dev)
+        status = torch.zeros(_lib.STATUS_WORDS, dtype=torch.int32, device=dev)
+        n_iters = int(self.n_iters)
+        acc = torch.zeros(6, dtype=f64, device=dev)
+        hist = torch.zeros(max(n_iters, 1), 6, dtype=f64, device=dev)
+
+        if use_graph:
+            sptr, sidx, sval = _graph.to_csr(self.S)
+            level_ptr, level_rows = _graph.level_schedule(sptr, sidx, item_counts > 0)
+            sptr_d = torch.from_numpy(sptr).to(dev)
+            sidx_d = torch.from_numpy(sidx).to(dev)
+            sval_d = torch.from_numpy(sval).to(dev)
+            level_rows_d = torch.from_numpy(level_rows).to(dev)
+            chol_d = torch.empty(n * k * k, dtype=f32, device=dev)
+            aux_d = torch.empty(n * (2 * k + 2), dtype=f32, device=dev)
+        if names:
+            G_d = torch.empty(n * k * k, dtype=f64, device=dev)
+            cvec_d = torch.empty(n * k, dtype=f64, device=dev)
+            Zmf_d = torch.empty(n_pad, ld, dtype=f32, device=dev)
+            dmax = max(int(x.shape[1]) for x in X_d)
+            A_d = torch.empty((dmax * k) ** 2, dtype=f64, device=dev)
+            Wnew64 = [torch.empty_like(w) for w in W64_d]
+            xptr = (C.c_void_p * len(names))(*[x.data_ptr() for x in X_d])
+            wptr = (C.c_void_p * len(names))(*[w.data_ptr() for w in W_d])
+            dims = (C.c_int32 * len(names))(*[int(x.shape[1]) for x in X_d])
+
+        def compose(out, skip=-1):
+            check(lib.b200als_compose_z(ptr(V_d), ld, n, k, len(names), xptr, dims, wptr, ld, skip,
+                                        ptr(out), ld, stream), "compose_z")
+
+        def step(csr_ptr, csr_idx, csr_val, n_rows, rows, F, bias_other, reg, reg_row, lamb, X, bias_own, mode):
+            a = StepArgs()
+            a.struct_bytes = C.sizeof(StepArgs)
+            a.k, a.mode, a.path = k, mode, self.gram_path
+            a.n_rows = n_rows
+            a.indptr, a.indices, a.vals = ptr(csr_ptr), ptr(csr_idx), ptr(csr_val)
+            a.rows, a.n_list = ptr(rows), rows.numel()
+            a.F, a.ldf = ptr(F), ld
+            a.bias_other, a.mu = ptr(bias_other), ptr(mu_d)
+            a.reg, a.reg_row = reg, ptr(reg_row)
+            a.lam_bias, a.lam_bias_row = lamb, None
+            a.X, a.ldx = ptr(X), ld
+            a.bias_own = ptr(bias_own)
+            a.chol_out = ptr(chol_d) if mode == _lib.STEP_FACTOR else None
+            a.aux_out = ptr(aux_d) if mode == _lib.STEP_FACTOR else None
+            a.status = ptr(status)
+            a.workspace, a.workspace_bytes = ptr(ws), ws.numel()
+            check(lib.b200als_row_step(C.byref(a), stream), "row_step")
+            return lib.b200als_last_launch_count() + 1      # + the cursor memset
+
+        if verbose > 0:
+            logger.info(f"Starting ALS training: n_factors={k}, n_iters={n_iters}, "
+                        f"lambda_u={self.lambda_u}, lambda_v={self.lambda_v}, "
+                        f"pop_reg_mode={self.pop_reg_mode}, features={names}, "
+                        f"lambda_w={self.lambda_w}, random_state={self.random_state}, "
+                        f"graph_alpha={self.alpha}, graph_topk={self.S_topk}, "
+                        f"graph_eps={self.S_eps}, update_w_every={self.update_w_every}")
+
+        def raise_if_bad():
+            st = status.cpu().numpy()
+            if st[0] != 0:
+                raise np.linalg.LinAlgError(
+                    f"{int(st[0])} normal matrices were not positive definite (first row {int(st[1])})")
+
+        done = 0
+        launches = 0
+        for it in range(n_iters):                                       # als.py:408
+            launches = 0
+            if names:
+                compose(Z_d)                                            # als.py:411
+                launches += 1
+            # (1) users (als.py:414-433)
+            launches += step(rt.indptr, rt.indices, rt.vals, m, u_list, Z_d, b_i_d, reg_user, None, lam_bu,
+                             U_d, b_u_d, _lib.STEP_SOLVE)
+            if shard.active:
+                shard.all_gather_rows(U_d, m)
+                shard.all_gather_rows(b_u_d, m)
+            # (2) items (als.py:436-466); the item step ignores the feature term
+            if use_graph:
+                launches += step(rt.cindptr, rt.cindices, rt.cvals, n, i_list, U_d, b_u_d, 0.0, reg_item_d,
+                                 lam_bi, V_d, b_i_d, _lib.STEP_FACTOR)
+                for lv in range(level_ptr.size - 1):
+                    lo, hi = int(level_ptr[lv]), int(level_ptr[lv + 1])
+                    check(lib.b200als_graph_level_solve(
+                        k, level_rows_d.data_ptr() + 4 * lo, hi - lo, ptr(chol_d), ptr(aux_d),
+                        ptr(sptr_d), ptr(sidx_d), ptr(sval_d), float(self.alpha), lam_bi, None,
+                        ptr(V_d), ld, ptr(b_i_d), stream), "graph_level_solve")
+                    launches += 1
+            else:
+                launches += step(rt.cindptr, rt.cindices, rt.cvals, n, i_list, U_d, b_u_d, 0.0, reg_item_d,
+                                 lam_bi, V_d, b_i_d, _lib.STEP_SOLVE)
+                if shard.active:
+                    shard.all_gather_rows(V_d, n)
+                    shard.all_gather_rows(b_i_d, n)
+            # (3) W_f (als.py:468-501)
+            if names and ((it % self.update_w_every == 0) or (it == n_iters - 1)):
+                check(lib.b200als_item_gram_f64(n, ptr(rt.cindptr), ptr(rt.cindices), ptr(rt.cvals), k,
+                                                ptr(U_d), ld, ptr(b_u_d), ptr(b_i_d), ptr(mu_d),
+                                                ptr(G_d), ptr(cvec_d), stream), "item_gram_f64")
+                launches += 1
+                for f, nm in enumerate(names):
+                    d = int(X_d[f].shape[1])
+                    compose(Zmf_d, skip=f)        # all W still old: `residual` is never refreshed (als.py:474-489)
+                    lam = float(self.lambda_w.get(nm, 0.0)) + EPS
+                    check(lib.b200als_wstep_system(n, k, d, ptr(X_d[f]), ptr(G_d), ptr(cvec_d), ptr(Zmf_d), ld,
+                                                   lam, ptr(A_d), ptr(Wnew64[f]), stream), "wstep_system")
+                    check(lib.b200als_cholesky_solve_f64(ptr(A_d), ptr(Wnew64[f]), d * k, ptr(status), stream),
+                          "cholesky_solve_f64")
+                    launches += 7
+                for f in range(len(names)):
+                    W64_d[f].copy_(Wnew64[f])
+                    W_d[f][:, :k] = Wnew64[f].view(-1, k).to(f32)
+            # (4) mu, RMSE, norms (als.py:503-517)
+            if names:
+                compose(Z_d)
+                launches += 1
+            acc.zero_()
+            check(lib.b200als_residual_stats(uhi - ulo, rt.indptr.data_ptr() + 8 * ulo, ptr(rt.indices),
+                                             ptr(rt.vals), k, U_d.data_ptr() + 4 * ld * ulo, ld, ptr(Z_d), ld,
+                                             b_u_d.data_ptr() + 4 * ulo, ptr(b_i_d), ptr(acc), stream),
+                  "residual_stats")
+            if shard.active:
+                shard.all_reduce_sum(acc[:2])
+            check(lib.b200als_sumsq(ptr(U_d), m, k, ld, acc.data_ptr() + 16, stream), "sumsq")
+            check(lib.b200als_sumsq(ptr(V_d), n, k, ld, acc.data_ptr() + 24, stream), "sumsq")
+            check(lib.b200als_sumsq(ptr(b_u_d), 1, m, m, acc.data_ptr() + 32, stream), "sumsq")
+            check(lib.b200als_sumsq(ptr(b_i_d), 1, n, n, acc.data_ptr() + 40, stream), "sumsq")
+            check(lib.b200als_finalize_iter(ptr(acc), nnz, ptr(mu_d), hist.data_ptr() + 48 * it, stream),
+                  "finalize_iter")
+            launches += 7
+            done = it + 1
+            # early stopping needs this iteration's RMSE on the host (als.py:520-523)
+            if tol is not None and it + 1 >= min_iters:
+                h = hist[:done].cpu().numpy()
+                raise_if_bad()
+                self._set_history(h)
+                if self._converged(tol):
+                    if verbose > 0:
+                        logger.info(f"Early stopping at iter {it + 1}; ΔRMSE ≤ {tol:.3g}")
+                    break
+        self.launches_per_iter = launches
+
+        h = hist[:done].cpu().numpy()
+        raise_if_bad()
+        self._set_history(h)
+        if done:
+            self.mu = float(h[-1, 5])
+        self.U = U_d[:m, :k].double().cpu().numpy()
+        self.V = V_d[:n, :k].double().cpu().numpy()
+        self.b_u = b_u_d[:m].double().cpu().numpy()
+        self.b_i = b_i_d[:n].double().cpu().numpy()
+        for f, nm in enumerate(names):
+            self.W[nm] = W64_d[f].view(-1, k).cpu().numpy().copy()
+        # device-resident state for predict_pairs / evaluation without re-upload
+        self._dev_state = dict(U=U_d, V=V_d, Z=Z_d, b_u=b_u_d, b_i=b_i_d, mu=mu_d, ld=ld, m=m, n=n, k=k)
+        if verbose > 0 and self.history["train_rmse"]:
+            logger.info(f"ALS training finished. Final train RMSE: {self.history['train_rmse'][-1]:.4f}")
+        return self
+
+    def _set_history(self, h: np.ndarray) -> None:
+        keys = ("train_rmse", "U_norm", "V_norm", "bu_norm", "bi_norm")
+        for j, key in enumerate(keys):
+            self.history[key] = [float(x) for x in h[:, j]]
+
+    # ------------------------------------------------------------------ predict
+    def _upload_model(self, features, dev):
+        """Public attributes (float64 numpy, possibly edited by the caller) → device float32."""
+        lib = _lib.load()
+        m, k = self.U.shape
+        n = self.V.shape[0]
+        ld = _round4(k)
+        f32 = torch.float32
+        U_d = torch.zeros(m, ld, dtype=f32, device=dev)
+        V_d = torch.zeros(n, ld, dtype=f32, device=dev)
+        U_d[:, :k] = torch.from_numpy(np.asarray(self.U, dtype=np.float32)).to(dev)
+        V_d[:, :k] = torch.from_numpy(np.asarray(self.V, dtype=np.float32)).to(dev)
+        b_u_d = torch.from_numpy(np.asarray(self.b_u, dtype=np.float32)).to(dev)
+        b_i_d = torch.from_numpy(np.asarray(self.b_i, dtype=np.float32)).to(dev)
+        mu_d = torch.full((1,), float(self.mu), dtype=f32, device=dev)
+        used = [(nm, X) for nm, X in features.items() if self.W.get(nm) is not None]   # als.py:569-572
+        if len(used) > _lib.MAX_FEATURES:
+            raise ValueError(f"at most {_lib.MAX_FEATURES} feature matrices are supported")
+        if used:
+            X_d = [torch.from_numpy(np.ascontiguousarray(X, dtype=np.float32)).to(dev) for _, X in used]
+            W_d = []
+            for nm, X in used:
+                w = torch.zeros(X.shape[1], ld, dtype=f32, device=dev)
+                w[:, :k] = torch.from_numpy(np.asarray(self.W[nm], dtype=np.float32)).to(dev)
+                W_d.append(w)
+            xptr = (C.c_void_p * len(used))(*[x.data_ptr() for x in X_d])
+            wptr = (C.c_void_p * len(used))(*[w.data_ptr() for w in W_d])
+            dims = (C.c_int32 * len(used))(*[int(x.shape[1]) for x in X_d])
+            Z_d = torch.empty(n, ld, dtype=f32, device=dev)
+            check(lib.b200als_compose_z(ptr(V_d), ld, n, k, len(used), xptr, dims, wptr, ld, -1, ptr(Z_d), ld,
+                                        torch.cuda.current_stream().cuda_stream), "compose_z")
+            torch.cuda.current_stream().synchronize()
+        else:
+            Z_d = V_d
+        return dict(U=U_d, Z=Z_d, b_u=b_u_d, b_i=b_i_d, mu=mu_d, ld=ld, m=m, n=n, k=k)
+
+    def predict(self, features: dict[str, np.ndarray] | None = None) -> np.ndarray:
+        """Completed (m, n) float64 matrix  U Zᵀ + μ + b_u + b_i  (als.py:532-574)."""
+        if self.U is None or self.V is None:
+            raise RuntimeError("Model must be fitted before prediction.")
+        features = features or {}
+        self._check_features(features, self.V.shape[0], "predict")      # als.py:558-565
+        lib = _lib.load()
+        _lib.require_device()
+        dev = self._dev()
+        with torch.cuda.device(dev):
+            s = self._upload_model(features, dev)
+            out = torch.empty(s["m"], s["n"], dtype=torch.float64, device=dev)
+            check(lib.b200als_predict_dense(ptr(s["U"]), s["ld"], ptr(s["Z"]), s["ld"], ptr(s["b_u"]), ptr(s["b_i"]),
+                                            ptr(s["mu"]), s["m"], s["n"], s["k"], ptr(out),
+                                            torch.cuda.current_stream().cuda_stream), "predict_dense")
+            return out.cpu().numpy()
+
+    def predict_pairs(self, rows, cols, features: dict[str, np.ndarray] | None = None) -> np.ndarray:
+        """Entries of `predict(features)` at (rows, cols) — `R_pred.ravel()[u*n+i]` of
+        tune_params.py:165-167 without the dense matrix.  Returns float64."""
+        if self.U is None or self.V is None:
+            raise RuntimeError("Model must be fitted before prediction.")
+        features = features or {}
+        self._check_features(features, self.V.shape[0], "predict")
+        lib = _lib.load()
+        _lib.require_device()
+        dev = self._dev()
+        with torch.cuda.device(dev):
+            s = self._upload_model(features, dev)
+            r = torch.as_tensor(np.asarray(rows)).to(device=dev, dtype=torch.int32).contiguous()
+            c = torch.as_tensor(np.asarray(cols)).to(device=dev, dtype=torch.int32).contiguous()
+            if r.numel() != c.numel():
+                raise ValueError("rows and cols differ in length")
+            out = torch.empty(max(r.numel(), 1), dtype=torch.float32, device=dev)
+            check(lib.b200als_predict_pairs(ptr(s["U"]), s["ld"], ptr(s["Z"]), s["ld"], ptr(s["b_u"]), ptr(s["b_i"]),
+                                            ptr(s["mu"]), ptr(r), ptr(c), r.numel(), s["k"], ptr(out),
+                                            torch.cuda.current_stream().cuda_stream), "predict_pairs")
+            return out[:r.numel()].double().cpu().numpy()
+
+    def rmse_on_flat(self, flat_idx, y_true, features=None) -> float:
+        """RMSE over flat indices u*n+i (`_rmse_on_indices`, tune_params.py:147-167)."""
+        flat_idx = np.asarray(flat_idx, dtype=np.int64)
+        if flat_idx.size == 0:
+            return float("nan")
+        n = self.V.shape[0]
+        pred = self.predict_pairs(flat_idx // n, flat_idx % n, features)
+        return float(np.sqrt(np.mean((np.asarray(y_true, dtype=np.float64) - pred) ** 2)))

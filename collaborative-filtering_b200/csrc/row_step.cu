@@ -1,0 +1,178 @@
+// row_step.cu — b200als_row_step: dispatch of one ALS half-step (A6/A7) to the
+// Gram path that fits k: tcgen05 (row_step_umma.cuh) for k in {64, 128},
+// register-tiled FFMA (row_step_ffma.cuh) otherwise; and the Gauss–Seidel
+// Laplacian level solve (A8).
+#include "row_step_ffma.cuh"
+#include "row_step_umma.cuh"
+
+namespace b200als {
+
+template <int KP, int T>
+static int launch_ffma(const RowStepParams& p, cudaStream_t s) {
+    using C = FfmaCfg<KP, T>;
+    auto kern = row_step_ffma_kernel<KP, T>;
+    static thread_local int blocks_per_sm = 0;   // per (KP,T) instantiation
+    if (blocks_per_sm == 0) {
+        ALS_CUDA(cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)C::smem_bytes));
+        int b = 0;
+        ALS_CUDA(cudaOccupancyMaxActiveBlocksPerMultiprocessor(&b, kern, C::THREADS, C::smem_bytes));
+        if (b < 1) {
+            set_error("row_step_ffma<%d,%d>: kernel does not fit on an SM (smem %zu)", KP, T, C::smem_bytes);
+            return B200ALS_E_UNSUPPORTED;
+        }
+        blocks_per_sm = b;
+    }
+    int64_t grid = (int64_t)kNumSMs * blocks_per_sm;
+    if (grid > p.n_list) grid = p.n_list;
+    kern<<<(unsigned)grid, C::THREADS, C::smem_bytes, s>>>(p);
+    ALS_LAUNCH_CHECK();
+    return B200ALS_OK;
+}
+
+static int dispatch_ffma(const RowStepParams& p, cudaStream_t s) {
+    const int k = p.k;
+    if (k <= 8) return launch_ffma<8, 4>(p, s);
+    if (k <= 16) return launch_ffma<16, 4>(p, s);
+    if (k <= 32) return launch_ffma<32, 4>(p, s);
+    if (k <= 64) return launch_ffma<64, 4>(p, s);
+    if (k <= 96) return launch_ffma<96, 8>(p, s);
+    if (k <= 128) return launch_ffma<128, 8>(p, s);
+    return launch_ffma<160, 8>(p, s);
+}
+
+// ---- A8: one Gauss–Seidel level ------------------------------------------------
+// One warp per item of the level.  b = c - b_i*s + alpha * S[i,:] V (CSR row, live V),
+// forward/back substitution against the stored lower factor, closed-form bias.
+template <int KMAX>
+__global__ void __launch_bounds__(128) graph_level_kernel(int k, const int32_t* __restrict__ level_rows,
+                                                          int64_t n_level, const float* __restrict__ chol,
+                                                          const float* __restrict__ aux,
+                                                          const int64_t* __restrict__ sptr,
+                                                          const int32_t* __restrict__ sidx,
+                                                          const float* __restrict__ sval, float alpha, float lam_bias,
+                                                          const float* __restrict__ lam_bias_row, float* V,
+                                                          int64_t ldv, float* b_i) {
+    __shared__ float ysm[4][KMAX];
+    const int lane = threadIdx.x & 31, w = threadIdx.x >> 5;
+    const int64_t item_slot = (int64_t)blockIdx.x * 4 + w;
+    if (item_slot >= n_level) return;
+    const int64_t i = level_rows[item_slot];
+    float* y = ysm[w];
+    const float* L = chol + (size_t)i * k * k;
+    const float* ax = aux + (size_t)i * (2 * k + 2);
+    const float bold = b_i[i];
+    // rhs
+    for (int c = lane; c < k; c += 32) y[c] = ax[c] - bold * ax[k + c];
+    __syncwarp();
+    for (int64_t e = sptr[i]; e < sptr[i + 1]; ++e) {
+        const float sv = alpha * sval[e];
+        const float* vj = V + (size_t)sidx[e] * ldv;
+        for (int c = lane; c < k; c += 32) y[c] = fmaf(sv, vj[c], y[c]);
+    }
+    __syncwarp();
+    // forward: L y' = y
+    for (int j = 0; j < k; ++j) {
+        const float yj = y[j] / L[j * k + j];
+        __syncwarp();
+        if (lane == 0) y[j] = yj;
+        for (int r = j + 1 + lane; r < k; r += 32) y[r] -= L[r * k + j] * yj;
+        __syncwarp();
+    }
+    // backward: L^T x = y'
+    for (int j = k - 1; j >= 0; --j) {
+        const float xj = y[j] / L[j * k + j];
+        __syncwarp();
+        if (lane == 0) y[j] = xj;
+        for (int r = lane; r < j; r += 32) y[r] -= L[j * k + r] * xj;
+        __syncwarp();
+    }
+    float dot = 0.0f;
+    for (int c = lane; c < k; c += 32) {
+        const float x = y[c];
+        V[(size_t)i * ldv + c] = x;
+        dot = fmaf(ax[k + c], x, dot);
+    }
+    dot = warp_sum(dot);
+    if (lane == 0) {
+        const float lb = lam_bias_row ? lam_bias_row[i] : lam_bias;
+        b_i[i] = (ax[2 * k] - dot) / (ax[2 * k + 1] + lb);
+    }
+}
+
+}  // namespace b200als
+
+using namespace b200als;
+
+extern "C" {
+
+int b200als_step_workspace_bytes(int32_t k, int32_t path, int64_t n_list, size_t* bytes_host) {
+    ALS_CHECK_ARG(bytes_host, "null");
+    ALS_CHECK_ARG(k >= 1 && k <= B200ALS_MAX_K, "k out of range");
+    (void)path;
+    (void)n_list;
+    *bytes_host = umma_workspace_bytes(k, n_list);
+    return B200ALS_OK;
+}
+
+int b200als_row_step(const b200als_step_args* a, b200als_stream_t stream) {
+    g_launch_count = 0;
+    ALS_CHECK_ARG(a && a->struct_bytes == sizeof(b200als_step_args), "args struct size mismatch (ABI)");
+    ALS_CHECK_ARG(a->k >= 1 && a->k <= B200ALS_MAX_K, "k out of range [1,160]");
+    ALS_CHECK_ARG(a->indptr && a->indices && a->vals && a->F && a->bias_other && a->mu, "null input");
+    ALS_CHECK_ARG(a->bias_own, "null bias_own");
+    ALS_CHECK_ARG((a->ldf & 3) == 0 && a->ldf >= ((a->k + 3) & ~3), "ldf must be a multiple of 4 and >= round4(k)");
+    ALS_CHECK_ARG(a->n_list >= 0 && a->n_list < (1ll << 31), "n_list out of range");
+    if (a->mode == B200ALS_STEP_SOLVE) {
+        ALS_CHECK_ARG(a->X && a->ldx >= a->k, "null X / ldx < k");
+    } else if (a->mode == B200ALS_STEP_FACTOR) {
+        ALS_CHECK_ARG(a->chol_out && a->aux_out, "FACTOR mode needs chol_out and aux_out");
+    } else {
+        ALS_CHECK_ARG(false, "unknown mode");
+    }
+    size_t need = 0;
+    b200als_step_workspace_bytes(a->k, a->path, a->n_list, &need);
+    if (!a->workspace || a->workspace_bytes < need) {
+        set_error("b200als_row_step: workspace %zu < required %zu", a->workspace_bytes, need);
+        return B200ALS_E_WORKSPACE;
+    }
+    if (a->n_list == 0) return B200ALS_OK;
+    cudaStream_t s = as_stream(stream);
+    RowStepParams p;
+    p.k = a->k; p.mode = a->mode; p.n_list = a->n_list;
+    p.indptr = a->indptr; p.indices = a->indices; p.vals = a->vals; p.rows = a->rows;
+    p.F = a->F; p.ldf = a->ldf; p.bias_other = a->bias_other; p.mu = a->mu;
+    p.reg = a->reg; p.reg_row = a->reg_row; p.lam_bias = a->lam_bias; p.lam_bias_row = a->lam_bias_row;
+    p.X = a->X; p.ldx = a->ldx; p.bias_own = a->bias_own;
+    p.chol_out = a->chol_out; p.aux_out = a->aux_out; p.status = a->status;
+    p.cursor = reinterpret_cast<unsigned long long*>(a->workspace);
+    ALS_CUDA(cudaMemsetAsync(a->workspace, 0, 256, s));
+
+    int path = a->path;
+    if (path == B200ALS_PATH_AUTO)
+        path = umma_supported(a->k, a->ldf) ? B200ALS_PATH_UMMA : B200ALS_PATH_FFMA;
+    if (path == B200ALS_PATH_UMMA) {
+        if (!umma_supported(a->k, a->ldf)) {
+            set_error("b200als_row_step: tcgen05 path needs k in {64,128} and ldf == k (got k=%d ldf=%lld)", a->k,
+                      (long long)a->ldf);
+            return B200ALS_E_UNSUPPORTED;
+        }
+        return launch_umma(p, static_cast<char*>(a->workspace) + 256, a->workspace_bytes - 256, s);
+    }
+    return dispatch_ffma(p, s);
+}
+
+int b200als_graph_level_solve(int32_t k, const int32_t* level_rows, int64_t n_level, const float* chol,
+                              const float* aux, const int64_t* sptr, const int32_t* sidx, const float* sval,
+                              float alpha, float lam_bias, const float* lam_bias_row, float* V, int64_t ldv,
+                              float* b_i, b200als_stream_t stream) {
+    ALS_CHECK_ARG(k >= 1 && k <= B200ALS_MAX_K, "k out of range");
+    ALS_CHECK_ARG(level_rows && chol && aux && sptr && sidx && sval && V && b_i, "null pointer");
+    if (n_level <= 0) return B200ALS_OK;
+    cudaStream_t s = as_stream(stream);
+    graph_level_kernel<B200ALS_MAX_K><<<(unsigned)ceil_div64(n_level, 4), 128, 0, s>>>(
+        k, level_rows, n_level, chol, aux, sptr, sidx, sval, alpha, lam_bias, lam_bias_row, V, ldv, b_i);
+    ALS_LAUNCH_CHECK();
+    return B200ALS_OK;
+}
+
+}  // extern "C"

@@ -1,0 +1,239 @@
+/*
+ * b200als.h — C-ABI of libb200als.so: the B200 (sm_100a) ALS block-update path.
+ *
+ * Drop-in boundary for the hot path of zhukovanadezhda/collaborative-filtering
+ * `scripts/als.py` (ALS.fit loop, als.py:408-523, and ALS.predict, als.py:532-574).
+ * The reference is pure Python/numpy, so its "FFI for this path" is the set of
+ * numpy expressions listed per entry point below; each function names the
+ * reference lines it replaces.  INTEGRATION.md shows the ctypes binding.
+ *
+ * Conventions
+ *  - every pointer is a DEVICE pointer unless its name ends in `_host`;
+ *  - the caller owns all memory; the library allocates nothing persistent.
+ *    Entry points that need scratch take (workspace, workspace_bytes); the
+ *    matching *_workspace_bytes call says how much;
+ *  - every call is asynchronous on `stream` (a cudaStream_t) unless stated;
+ *  - return value: 0 = ok, <0 = error (B200ALS_E_*); b200als_last_error() gives
+ *    the thread-local message.  No C++ exception crosses the boundary;
+ *  - factor matrices are row-major float32 with a row stride (`ld*`, in
+ *    floats, multiple of 4 so rows are 16-byte aligned); index arrays are
+ *    int32, row pointers int64 (nnz may exceed 2^31 across a job);
+ *  - a device `int32 status[B200ALS_STATUS_WORDS]` word array collects
+ *    numerical failures (non-SPD pivot → row id) without a host sync.
+ */
+#ifndef B200ALS_H_
+#define B200ALS_H_
+
+#include <stddef.h>
+#include <stdint.h>
+
+#ifdef __cplusplus
+extern "C" {
+#endif
+
+#define B200ALS_ABI_VERSION 3
+
+#define B200ALS_OK            0
+#define B200ALS_E_INVALID    -1   /* bad argument */
+#define B200ALS_E_CUDA       -2   /* CUDA runtime error (message has the string) */
+#define B200ALS_E_WORKSPACE  -3   /* workspace too small */
+#define B200ALS_E_UNSUPPORTED -4  /* shape outside what the kernels cover */
+
+#define B200ALS_MAX_K        160  /* tune_params.py:99 N_FACTORS_MAX = 150 */
+#define B200ALS_MAX_FEATURES 8
+#define B200ALS_STATUS_WORDS 4    /* [0]=#non-SPD rows, [1]=first bad row, [2]=phase, [3]=reserved */
+
+typedef void* b200als_stream_t;   /* cudaStream_t */
+
+int         b200als_abi_version(void);
+const char* b200als_last_error(void);
+/* 1 if a usable sm_100 device is current, 0 otherwise (sync; never throws). */
+int         b200als_device_ok(void);
+
+/* ------------------------------------------------------------------------
+ * A1 — CSR / CSC construction (als.py:335-340), index-bit-exact:
+ *   CSR  indices[indptr[u] : indptr[u+1]] == np.flatnonzero(mask[u])      (ascending)
+ *   CSC cindices[cindptr[i]:cindptr[i+1]] == np.flatnonzero(mask[:, i])   (ascending)
+ *   COO order of (rows_u, rows_i) = np.where(mask)  == CSR order
+ *   perm[p_csc] = p_csr  (optional, may be NULL)
+ * ---------------------------------------------------------------------- */
+
+/* Dense input: R is (m, n) float64 row-major, NaN = missing (als.py:335).
+ * Step 1 writes indptr[m+1] and cindptr[n+1]; nnz = indptr[m] (caller reads it
+ * back, allocates, then calls step 2). */
+int b200als_dense_indptr(const double* R, int64_t m, int64_t n,
+                         int64_t* indptr, int64_t* cindptr,
+                         b200als_stream_t stream);
+int b200als_dense_fill(const double* R, int64_t m, int64_t n,
+                       const int64_t* indptr, const int64_t* cindptr,
+                       int32_t* indices, float* vals,
+                       int32_t* cindices, float* cvals, int64_t* perm,
+                       b200als_stream_t stream);
+
+/* COO input: flat_idx[e] = u*n + i (create_folds.py:73-84 convention), unique,
+ * any order unless `sorted` != 0 (then ascending, as np.flatnonzero and
+ * np.setdiff1d give it, create_folds.py:200).  Replaces the dense
+ * matrix_from_indices round trip (create_folds.py:152-174 + als.py:335-340). */
+int b200als_coo_workspace_bytes(int64_t nnz, int64_t m, int64_t n, size_t* bytes_host);
+int b200als_coo_to_csr_csc(const int64_t* flat_idx, const float* vals_in,
+                           int64_t nnz, int64_t m, int64_t n, int sorted,
+                           int64_t* indptr, int32_t* indices, float* vals,
+                           int64_t* cindptr, int32_t* cindices, float* cvals,
+                           int64_t* perm,
+                           void* workspace, size_t workspace_bytes,
+                           b200als_stream_t stream);
+
+/* Row schedule: order[] = row ids sorted by descending rating count (longest
+ * first, ties by ascending id); empty rows are placed last and *n_nonempty
+ * (device int64) receives how many rows have >=1 rating (als.py:418-419,
+ * 440-441 skip the others). */
+int b200als_row_order_workspace_bytes(int64_t n_rows, size_t* bytes_host);
+int b200als_row_order(const int64_t* indptr, int64_t n_rows,
+                      int32_t* order, int64_t* n_nonempty,
+                      void* workspace, size_t workspace_bytes,
+                      b200als_stream_t stream);
+
+/* ------------------------------------------------------------------------
+ * A5 — Z = V + sum_f X_f W_f  (als.py:262-281, 411, 504, 568-572)
+ * X_f is (n, d_f) float32 row-major, W_f is (d_f, k) float32 row-major with
+ * row stride ldw.  `skip` >= 0 leaves feature `skip` out (W step, als.py:485).
+ * ---------------------------------------------------------------------- */
+int b200als_compose_z(const float* V, int64_t ldv, int64_t n, int32_t k,
+                      int32_t n_features,
+                      const float* const* X_host_array_of_dev_ptrs,
+                      const int32_t* d_host,
+                      const float* const* W_host_array_of_dev_ptrs,
+                      int64_t ldw, int32_t skip,
+                      float* Z, int64_t ldz,
+                      b200als_stream_t stream);
+
+/* ------------------------------------------------------------------------
+ * A6 / A7 / A8 / A11 — one ALS half-step over a set of rows.
+ *
+ * For every row r in `rows` (or 0..n_rows-1 when rows == NULL) with cnt > 0:
+ *   idx  = indices[indptr[r] : indptr[r+1]]
+ *   q_j  = vals_j - (mu + bias_other[idx_j])
+ *   A    = F[idx]^T F[idx] + reg_r I                       (als.py:426 / 455)
+ *   b    = F[idx]^T (q - bias_own[r])  (+ rhs_extra[r])    (als.py:427 / 456-458)
+ *   x    = cholesky_solve(A, b)                            (helpers.py:19-20)
+ *   bias_own[r] = sum_j (q_j - F[idx_j]·x) / (cnt + lam_bias_r)   (als.py:431-433 / 464-466)
+ * with reg_r = reg_row ? reg_row[r] : reg   (EPS, alpha*D_i already folded in
+ * by the caller in float64, als.py:426,450-454) and likewise lam_bias.
+ * User step: F = Z, bias_other = b_i, X = U.  Item step: F = U, bias_other =
+ * b_u, X = V.  Rows with no ratings are left untouched.
+ *
+ * mode B200ALS_STEP_SOLVE   : as above.
+ * mode B200ALS_STEP_FACTOR  : (graph sweep, A8) do not solve; store the lower
+ *     Cholesky factor of A in chol_out[r] (k*k floats, row-major, ld = k) and
+ *     c_r = F^T q  (k), s_r = F^T 1 (k), t_r = sum q, in aux_out[r] (2k+2
+ *     floats: c, s, t, cnt) for b200als_graph_level_solve.
+ * ---------------------------------------------------------------------- */
+#define B200ALS_STEP_SOLVE  0
+#define B200ALS_STEP_FACTOR 1
+
+#define B200ALS_PATH_AUTO   0   /* tcgen05 when k in {64,128}, else FFMA */
+#define B200ALS_PATH_FFMA   1
+#define B200ALS_PATH_UMMA   2
+
+typedef struct b200als_step_args {
+    uint32_t struct_bytes;       /* = sizeof(b200als_step_args) */
+    int32_t  k;
+    int32_t  mode;
+    int32_t  path;
+    int64_t  n_rows;             /* rows of the sparse matrix (bounds for rows[]) */
+    const int64_t* indptr;
+    const int32_t* indices;
+    const float*   vals;
+    const int32_t* rows;         /* optional row list (e.g. b200als_row_order output) */
+    int64_t  n_list;             /* entries of rows[] to process (or n_rows if rows==NULL) */
+    const float* F;  int64_t ldf;
+    const float* bias_other;
+    const float* mu;             /* device scalar */
+    float  reg;        const float* reg_row;
+    float  lam_bias;   const float* lam_bias_row;
+    float* X;  int64_t ldx;
+    float* bias_own;
+    float* chol_out;             /* FACTOR mode: n_rows * k * k */
+    float* aux_out;              /* FACTOR mode: n_rows * (2k+2) */
+    int32_t* status;             /* B200ALS_STATUS_WORDS ints, may be NULL */
+    void*  workspace; size_t workspace_bytes;   /* see b200als_step_workspace_bytes */
+} b200als_step_args;
+
+int b200als_step_workspace_bytes(int32_t k, int32_t path, int64_t n_list, size_t* bytes_host);
+int b200als_row_step(const b200als_step_args* args_host, b200als_stream_t stream);
+/* Number of kernel launches the last b200als_row_step on this thread issued. */
+int b200als_last_launch_count(void);
+
+/* A8 — one level of the Gauss–Seidel Laplacian sweep (als.py:453-461).
+ * For every item i in level_rows[0..n_level):
+ *   b = c_i - b_i[i]*s_i + alpha * sum_j S[i,j] V[j]      (live V)
+ *   V[i] = L_i^-T L_i^-1 b ;  b_i[i] = (t_i - s_i·V[i]) / (cnt_i + lam_bias_i)
+ * S is CSR (sptr int64, sidx int32, sval float32). */
+int b200als_graph_level_solve(int32_t k, const int32_t* level_rows, int64_t n_level,
+                              const float* chol, const float* aux,
+                              const int64_t* sptr, const int32_t* sidx, const float* sval,
+                              float alpha,
+                              float lam_bias, const float* lam_bias_row,
+                              float* V, int64_t ldv, float* b_i,
+                              b200als_stream_t stream);
+
+/* ------------------------------------------------------------------------
+ * A10 — residual statistics over all observed entries (als.py:503-517):
+ *   d_e = R_e - (U[u]·Z[i] + b_u[u] + b_i[i]);  acc[0] += sum d, acc[1] += sum d^2
+ * in float64.  The caller zeroes acc.  b200als_sumsq adds sum x^2 (Frobenius
+ * norms, als.py:514-517) over an (rows, cols, ld) matrix into *acc.
+ * b200als_finalize_iter turns them into mu / rmse / norms on the device:
+ *   mu = acc[0]/nnz (als.py:507)  → *mu_f32 (read by the next half-steps)
+ *   hist[0..5] = {rmse, |U|, |V|, |b_u|, |b_i|, mu} float64 (als.py:510-517)
+ * ---------------------------------------------------------------------- */
+int b200als_residual_stats(int64_t m, const int64_t* indptr, const int32_t* indices,
+                           const float* vals, int32_t k,
+                           const float* U, int64_t ldu, const float* Z, int64_t ldz,
+                           const float* b_u, const float* b_i,
+                           double* acc, b200als_stream_t stream);
+int b200als_sumsq(const float* x, int64_t rows, int64_t cols, int64_t ld,
+                  double* acc, b200als_stream_t stream);
+int b200als_finalize_iter(const double* acc6, int64_t nnz_total,
+                          float* mu_f32, double* hist6, b200als_stream_t stream);
+
+/* ------------------------------------------------------------------------
+ * A9 — W_f update (als.py:468-501) in Kronecker form, float64:
+ *   G_i = sum_{u in Omega_i} U_u U_u^T,  c_i = sum_u (R_ui - mu - b_u - b_i) U_u
+ *   h_i = c_i - G_i (Z_i - X_f[i] W_f)            (own contribution added back)
+ *   A   = sum_i (x_i x_i^T) (x) G_i + lam I,  b = sum_i x_i (x) h_i,  index a*k+c
+ *   vec(W_f) = cholesky_solve(A, b)
+ * b200als_item_gram_f64 fills G (n,k,k) and c (n,k);
+ * b200als_wstep_system builds A (dk x dk, lower+upper) and b (dk);
+ * b200als_cholesky_solve_f64 solves in place (x overwrites b).
+ * ---------------------------------------------------------------------- */
+int b200als_item_gram_f64(int64_t n, const int64_t* cindptr, const int32_t* cindices,
+                          const float* cvals, int32_t k,
+                          const float* U, int64_t ldu,
+                          const float* b_u, const float* b_i, const float* mu,
+                          double* G, double* c, b200als_stream_t stream);
+int b200als_wstep_system(int64_t n, int32_t k, int32_t d,
+                         const float* X, const double* G, const double* c,
+                         const float* Zmf, int64_t ldz, double lam,
+                         double* A, double* b, b200als_stream_t stream);
+int b200als_cholesky_solve_f64(double* A, double* b, int32_t N, int32_t* status,
+                               b200als_stream_t stream);
+/* W_f (float32, ld = ldw) <- vec (float64, d*k) ; also the reverse for upload */
+int b200als_f64_to_f32(const double* src, float* dst, int64_t count, b200als_stream_t stream);
+
+/* ------------------------------------------------------------------------
+ * A13 — predictions (als.py:574): out[u, i] = U[u]·Z[i] + mu + b_u[u] + b_i[i]
+ * dense (m, n) float64, or at (rows, cols) pairs (tune_params.py:165-167).
+ * ---------------------------------------------------------------------- */
+int b200als_predict_dense(const float* U, int64_t ldu, const float* Z, int64_t ldz,
+                          const float* b_u, const float* b_i, const float* mu,
+                          int64_t m, int64_t n, int32_t k,
+                          double* out, b200als_stream_t stream);
+int b200als_predict_pairs(const float* U, int64_t ldu, const float* Z, int64_t ldz,
+                          const float* b_u, const float* b_i, const float* mu,
+                          const int32_t* rows, const int32_t* cols, int64_t count, int32_t k,
+                          float* out, b200als_stream_t stream);
+
+#ifdef __cplusplus
+}
+#endif
+#endif /* B200ALS_H_ */
