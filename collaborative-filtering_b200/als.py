@@ -156,260 +156,34 @@ class ALS:
             return self._fit_ratings(ratings, mu0, features, tol, min_iters, verbose, init)
 
     # ------------------------------------------------------------------ core loop
+    def session(self, rt: Ratings, mu0: float, features=None, init=None, profile: bool = False) -> "FitSession":
+        """Set up device state for a fit and return the stepping handle (bench / tests)."""
+        return FitSession(self, rt, mu0, features, init, profile)
+
     def _fit_ratings(self, rt: Ratings, mu0, features, tol, min_iters, verbose, init) -> "ALS":
         if verbose == 0:
             logging.disable(logging.CRITICAL)          # als.py:325-326 (global, as in the reference)
-        lib = _lib.load()
-        dev = rt.vals.device
-        m, n, nnz, k = rt.m, rt.n, rt.nnz, int(self.n_factors)
-        if not (1 <= k <= _lib.MAX_K):
-            raise ValueError(f"n_factors={k} outside the supported range [1, {_lib.MAX_K}]")
-        if nnz == 0:
-            raise ValueError("no observed ratings")
-        shard = self.shard or Shard()
-        features = features or {}
-        self._check_features(features, n, "fit")                        # als.py:346-351
-        if len(features) > _lib.MAX_FEATURES:
-            raise ValueError(f"at most {_lib.MAX_FEATURES} feature matrices are supported")
-        names = list(features.keys())
-        stream = torch.cuda.current_stream().cuda_stream
-        ld = _round4(k)
-        f32, f64 = torch.float32, torch.float64
-
-        # ---- graph (host build for argpartition tie parity, als.py:354-357) ----
-        use_graph = (self.alpha > 0.0) and (self.cfg.graph.sim is not None)
-        self.S = None
-        if use_graph:
-            fname = self.cfg.graph.sim.feature_name
-            Xg = features.get(fname)
-            if Xg is None:
-                logger.warning(f"GraphSim feature '{fname}' not found in features dict. "
-                               f"Graph regularization disabled.")
-            else:
-                self.S = _graph.similarity_topk(Xg, self.S_topk, self.S_eps)
-        use_graph = self.S is not None
-        D = self.S.sum(axis=1) if use_graph else None                   # als.py:357 (S's dtype)
-
-        # ---- init (als.py:360-376): same PCG64 stream, order U, V, W_f ----------
-        m_pad, n_pad = shard.padded_rows(m), shard.padded_rows(n)
-        U_d = torch.zeros(m_pad, ld, dtype=f32, device=dev)
-        V_d = torch.zeros(n_pad, ld, dtype=f32, device=dev)
-        W_d = [torch.zeros(features[nm].shape[1], ld, dtype=f32, device=dev) for nm in names]
-        W64_d = [torch.zeros(features[nm].shape[1] * k, dtype=f64, device=dev) for nm in names]
-        if init is None:
-            rng = np.random.default_rng(self.random_state)              # als.py:329
-            U_d[:m, :k] = torch.from_numpy(rng.normal(scale=SCALE_FACTOR, size=(m, k)).astype(np.float32)).to(dev)
-            V_d[:n, :k] = torch.from_numpy(rng.normal(scale=SCALE_FACTOR, size=(n, k)).astype(np.float32)).to(dev)
-            for f, nm in enumerate(names):
-                w0 = rng.normal(scale=SCALE_FACTOR, size=(features[nm].shape[1], k))
-                W64_d[f].copy_(torch.from_numpy(w0.reshape(-1)).to(dev))
-                W_d[f][:, :k] = torch.from_numpy(w0.astype(np.float32)).to(dev)
-        elif isinstance(init, str) and init == "device":
-            g = torch.Generator(device=dev)
-            g.manual_seed(int(self.random_state))
-            U_d[:m, :k].normal_(0.0, SCALE_FACTOR, generator=g)
-            V_d[:n, :k].normal_(0.0, SCALE_FACTOR, generator=g)
-            for f in range(len(names)):
-                W_d[f][:, :k].normal_(0.0, SCALE_FACTOR, generator=g)
-                W64_d[f].copy_(W_d[f][:, :k].reshape(-1).double())
-        else:
-            U_d[:m, :k] = torch.as_tensor(np.asarray(init["U"], dtype=np.float32)).to(dev)
-            V_d[:n, :k] = torch.as_tensor(np.asarray(init["V"], dtype=np.float32)).to(dev)
-            for f, nm in enumerate(names):
-                w0 = np.asarray(init["W"][nm], dtype=np.float64)
-                W64_d[f].copy_(torch.from_numpy(w0.reshape(-1)).to(dev))
-                W_d[f][:, :k] = torch.from_numpy(w0.astype(np.float32)).to(dev)
-        b_u_d = torch.zeros(m_pad, dtype=f32, device=dev)
-        b_i_d = torch.zeros(n_pad, dtype=f32, device=dev)
-        mu_d = torch.full((1,), float(mu0), dtype=f32, device=dev)
-        self.mu = float(mu0)
-        X_d = [torch.from_numpy(np.ascontiguousarray(features[nm], dtype=np.float32)).to(dev) for nm in names]
-        Z_d = torch.zeros(n_pad, ld, dtype=f32, device=dev) if names else V_d
-
-        # ---- regularisers (als.py:379-384, 426, 450-454), folded in float64 ------
-        item_counts = (rt.cindptr[1:] - rt.cindptr[:-1]).cpu().numpy().astype(float)
-        lambda_v_i = self._item_reg(item_counts).astype(float)
-        reg_item = lambda_v_i + EPS
-        if use_graph:
-            reg_item = reg_item + float(self.alpha) * D.astype(np.float64)
-        reg_item_d = torch.from_numpy(reg_item.astype(np.float32)).to(dev)
-        reg_user = float(np.float32(self.lambda_u + EPS))
-        lam_bu = float(np.float32(self.lambda_bu + EPS))
-        lam_bi = float(np.float32(float(self.lambda_bi) + EPS))
-
-        # ---- schedules ------------------------------------------------------------
-        u_order, u_nonempty = row_schedule(rt.indptr)
-        i_order, i_nonempty = row_schedule(rt.cindptr)
-        if shard.active:
-            ulo, uhi = shard.my_range(m)
-            ilo, ihi = shard.my_range(n)
-            uo = u_order[:u_nonempty]
-            u_list = uo[(uo >= ulo) & (uo < uhi)].contiguous()
-            io = i_order[:i_nonempty]
-            i_list = io[(io >= ilo) & (io < ihi)].contiguous()
-        else:
-            ulo, uhi, ilo, ihi = 0, m, 0, n
-            u_list, i_list = u_order[:u_nonempty], i_order[:i_nonempty]
-        if use_graph:
-            i_list = i_order[:i_nonempty]       # the Gauss–Seidel sweep is not sharded (§8e)
-
-        need = C.c_size_t(0)
-        check(lib.b200als_step_workspace_bytes(k, self.gram_path, max(m, n), C.byref(need)), "step_workspace_bytes")
-        ws = torch.empty(need.value, dtype=torch.uint8, device=dev)
-        status = torch.zeros(_lib.STATUS_WORDS, dtype=torch.int32, device=dev)
+        ses = FitSession(self, rt, mu0, features, init, False)
         n_iters = int(self.n_iters)
-        acc = torch.zeros(6, dtype=f64, device=dev)
-        hist = torch.zeros(max(n_iters, 1), 6, dtype=f64, device=dev)
-
-        if use_graph:
-            sptr, sidx, sval = _graph.to_csr(self.S)
-            level_ptr, level_rows = _graph.level_schedule(sptr, sidx, item_counts > 0)
-            sptr_d = torch.from_numpy(sptr).to(dev)
-            sidx_d = torch.from_numpy(sidx).to(dev)
-            sval_d = torch.from_numpy(sval).to(dev)
-            level_rows_d = torch.from_numpy(level_rows).to(dev)
-            chol_d = torch.empty(n * k * k, dtype=f32, device=dev)
-            aux_d = torch.empty(n * (2 * k + 2), dtype=f32, device=dev)
-        if names:
-            G_d = torch.empty(n * k * k, dtype=f64, device=dev)
-            cvec_d = torch.empty(n * k, dtype=f64, device=dev)
-            Zmf_d = torch.empty(n_pad, ld, dtype=f32, device=dev)
-            dmax = max(int(x.shape[1]) for x in X_d)
-            A_d = torch.empty((dmax * k) ** 2, dtype=f64, device=dev)
-            Wnew64 = [torch.empty_like(w) for w in W64_d]
-            xptr = (C.c_void_p * len(names))(*[x.data_ptr() for x in X_d])
-            wptr = (C.c_void_p * len(names))(*[w.data_ptr() for w in W_d])
-            dims = (C.c_int32 * len(names))(*[int(x.shape[1]) for x in X_d])
-
-        def compose(out, skip=-1):
-            check(lib.b200als_compose_z(ptr(V_d), ld, n, k, len(names), xptr, dims, wptr, ld, skip,
-                                        ptr(out), ld, stream), "compose_z")
-
-        def step(csr_ptr, csr_idx, csr_val, n_rows, rows, F, bias_other, reg, reg_row, lamb, X, bias_own, mode):
-            a = StepArgs()
-            a.struct_bytes = C.sizeof(StepArgs)
-            a.k, a.mode, a.path = k, mode, self.gram_path
-            a.n_rows = n_rows
-            a.indptr, a.indices, a.vals = ptr(csr_ptr), ptr(csr_idx), ptr(csr_val)
-            a.rows, a.n_list = ptr(rows), rows.numel()
-            a.F, a.ldf = ptr(F), ld
-            a.bias_other, a.mu = ptr(bias_other), ptr(mu_d)
-            a.reg, a.reg_row = reg, ptr(reg_row)
-            a.lam_bias, a.lam_bias_row = lamb, None
-            a.X, a.ldx = ptr(X), ld
-            a.bias_own = ptr(bias_own)
-            a.chol_out = ptr(chol_d) if mode == _lib.STEP_FACTOR else None
-            a.aux_out = ptr(aux_d) if mode == _lib.STEP_FACTOR else None
-            a.status = ptr(status)
-            a.workspace, a.workspace_bytes = ptr(ws), ws.numel()
-            check(lib.b200als_row_step(C.byref(a), stream), "row_step")
-            return lib.b200als_last_launch_count() + 1      # + the cursor memset
-
         if verbose > 0:
-            logger.info(f"Starting ALS training: n_factors={k}, n_iters={n_iters}, "
+            logger.info(f"Starting ALS training: n_factors={ses.k}, n_iters={n_iters}, "
                         f"lambda_u={self.lambda_u}, lambda_v={self.lambda_v}, "
-                        f"pop_reg_mode={self.pop_reg_mode}, features={names}, "
+                        f"pop_reg_mode={self.pop_reg_mode}, features={ses.names}, "
                         f"lambda_w={self.lambda_w}, random_state={self.random_state}, "
                         f"graph_alpha={self.alpha}, graph_topk={self.S_topk}, "
                         f"graph_eps={self.S_eps}, update_w_every={self.update_w_every}")
-
-        def raise_if_bad():
-            st = status.cpu().numpy()
-            if st[0] != 0:
-                raise np.linalg.LinAlgError(
-                    f"{int(st[0])} normal matrices were not positive definite (first row {int(st[1])})")
-
         done = 0
-        launches = 0
         for it in range(n_iters):                                       # als.py:408
-            launches = 0
-            if names:
-                compose(Z_d)                                            # als.py:411
-                launches += 1
-            # (1) users (als.py:414-433)
-            launches += step(rt.indptr, rt.indices, rt.vals, m, u_list, Z_d, b_i_d, reg_user, None, lam_bu,
-                             U_d, b_u_d, _lib.STEP_SOLVE)
-            if shard.active:
-                shard.all_gather_rows(U_d, m)
-                shard.all_gather_rows(b_u_d, m)
-            # (2) items (als.py:436-466); the item step ignores the feature term
-            if use_graph:
-                launches += step(rt.cindptr, rt.cindices, rt.cvals, n, i_list, U_d, b_u_d, 0.0, reg_item_d,
-                                 lam_bi, V_d, b_i_d, _lib.STEP_FACTOR)
-                for lv in range(level_ptr.size - 1):
-                    lo, hi = int(level_ptr[lv]), int(level_ptr[lv + 1])
-                    check(lib.b200als_graph_level_solve(
-                        k, level_rows_d.data_ptr() + 4 * lo, hi - lo, ptr(chol_d), ptr(aux_d),
-                        ptr(sptr_d), ptr(sidx_d), ptr(sval_d), float(self.alpha), lam_bi, None,
-                        ptr(V_d), ld, ptr(b_i_d), stream), "graph_level_solve")
-                    launches += 1
-            else:
-                launches += step(rt.cindptr, rt.cindices, rt.cvals, n, i_list, U_d, b_u_d, 0.0, reg_item_d,
-                                 lam_bi, V_d, b_i_d, _lib.STEP_SOLVE)
-                if shard.active:
-                    shard.all_gather_rows(V_d, n)
-                    shard.all_gather_rows(b_i_d, n)
-            # (3) W_f (als.py:468-501)
-            if names and ((it % self.update_w_every == 0) or (it == n_iters - 1)):
-                check(lib.b200als_item_gram_f64(n, ptr(rt.cindptr), ptr(rt.cindices), ptr(rt.cvals), k,
-                                                ptr(U_d), ld, ptr(b_u_d), ptr(b_i_d), ptr(mu_d),
-                                                ptr(G_d), ptr(cvec_d), stream), "item_gram_f64")
-                launches += 1
-                for f, nm in enumerate(names):
-                    d = int(X_d[f].shape[1])
-                    compose(Zmf_d, skip=f)        # all W still old: `residual` is never refreshed (als.py:474-489)
-                    lam = float(self.lambda_w.get(nm, 0.0)) + EPS
-                    check(lib.b200als_wstep_system(n, k, d, ptr(X_d[f]), ptr(G_d), ptr(cvec_d), ptr(Zmf_d), ld,
-                                                   lam, ptr(A_d), ptr(Wnew64[f]), stream), "wstep_system")
-                    check(lib.b200als_cholesky_solve_f64(ptr(A_d), ptr(Wnew64[f]), d * k, ptr(status), stream),
-                          "cholesky_solve_f64")
-                    launches += 7
-                for f in range(len(names)):
-                    W64_d[f].copy_(Wnew64[f])
-                    W_d[f][:, :k] = Wnew64[f].view(-1, k).to(f32)
-            # (4) mu, RMSE, norms (als.py:503-517)
-            if names:
-                compose(Z_d)
-                launches += 1
-            acc.zero_()
-            check(lib.b200als_residual_stats(uhi - ulo, rt.indptr.data_ptr() + 8 * ulo, ptr(rt.indices),
-                                             ptr(rt.vals), k, U_d.data_ptr() + 4 * ld * ulo, ld, ptr(Z_d), ld,
-                                             b_u_d.data_ptr() + 4 * ulo, ptr(b_i_d), ptr(acc), stream),
-                  "residual_stats")
-            if shard.active:
-                shard.all_reduce_sum(acc[:2])
-            check(lib.b200als_sumsq(ptr(U_d), m, k, ld, acc.data_ptr() + 16, stream), "sumsq")
-            check(lib.b200als_sumsq(ptr(V_d), n, k, ld, acc.data_ptr() + 24, stream), "sumsq")
-            check(lib.b200als_sumsq(ptr(b_u_d), 1, m, m, acc.data_ptr() + 32, stream), "sumsq")
-            check(lib.b200als_sumsq(ptr(b_i_d), 1, n, n, acc.data_ptr() + 40, stream), "sumsq")
-            check(lib.b200als_finalize_iter(ptr(acc), nnz, ptr(mu_d), hist.data_ptr() + 48 * it, stream),
-                  "finalize_iter")
-            launches += 7
+            ses.iteration(it)
             done = it + 1
             # early stopping needs this iteration's RMSE on the host (als.py:520-523)
             if tol is not None and it + 1 >= min_iters:
-                h = hist[:done].cpu().numpy()
-                raise_if_bad()
-                self._set_history(h)
+                self._set_history(ses.read_history(done))
                 if self._converged(tol):
                     if verbose > 0:
                         logger.info(f"Early stopping at iter {it + 1}; ΔRMSE ≤ {tol:.3g}")
                     break
-        self.launches_per_iter = launches
-
-        h = hist[:done].cpu().numpy()
-        raise_if_bad()
-        self._set_history(h)
-        if done:
-            self.mu = float(h[-1, 5])
-        self.U = U_d[:m, :k].double().cpu().numpy()
-        self.V = V_d[:n, :k].double().cpu().numpy()
-        self.b_u = b_u_d[:m].double().cpu().numpy()
-        self.b_i = b_i_d[:n].double().cpu().numpy()
-        for f, nm in enumerate(names):
-            self.W[nm] = W64_d[f].view(-1, k).cpu().numpy().copy()
-        # device-resident state for predict_pairs / evaluation without re-upload
-        self._dev_state = dict(U=U_d, V=V_d, Z=Z_d, b_u=b_u_d, b_i=b_i_d, mu=mu_d, ld=ld, m=m, n=n, k=k)
+        ses.finish(done)
         if verbose > 0 and self.history["train_rmse"]:
             logger.info(f"ALS training finished. Final train RMSE: {self.history['train_rmse'][-1]:.4f}")
         return self
@@ -502,3 +276,295 @@ class ALS:
         n = self.V.shape[0]
         pred = self.predict_pairs(flat_idx // n, flat_idx % n, features)
         return float(np.sqrt(np.mean((np.asarray(y_true, dtype=np.float64) - pred) ** 2)))
+
+
+class FitSession:
+    """Device state of one fit plus `iteration(it)`: one pass of als.py:408-517.
+
+    Everything is enqueued on torch's current CUDA stream and is asynchronous;
+    `read_history` / `finish` are the only host synchronisation points.
+    """
+
+    PHASES = ("compose", "user", "item", "wstep", "stats")
+
+    def __init__(self, model: ALS, rt: Ratings, mu0: float, features, init, profile: bool):
+        self.model = model
+        self.rt = rt
+        self.lib = lib = _lib.load()
+        self.profile = profile
+        self.phase_ms = {p: [] for p in self.PHASES}
+        self._events = []
+        dev = self.dev = rt.vals.device
+        m, n, nnz = rt.m, rt.n, rt.nnz
+        k = self.k = int(model.n_factors)
+        if not (1 <= k <= _lib.MAX_K):
+            raise ValueError(f"n_factors={k} outside the supported range [1, {_lib.MAX_K}]")
+        if nnz == 0:
+            raise ValueError("no observed ratings")
+        shard = self.shard = model.shard or Shard()
+        features = features or {}
+        model._check_features(features, n, "fit")                       # als.py:346-351
+        if len(features) > _lib.MAX_FEATURES:
+            raise ValueError(f"at most {_lib.MAX_FEATURES} feature matrices are supported")
+        names = self.names = list(features.keys())
+        ld = self.ld = _round4(k)
+        f32, f64 = torch.float32, torch.float64
+
+        # ---- graph (host build for argpartition tie parity, als.py:354-357) ----
+        use_graph = (model.alpha > 0.0) and (model.cfg.graph.sim is not None)
+        model.S = None
+        if use_graph:
+            fname = model.cfg.graph.sim.feature_name
+            Xg = features.get(fname)
+            if Xg is None:
+                logger.warning(f"GraphSim feature '{fname}' not found in features dict. "
+                               f"Graph regularization disabled.")
+            else:
+                model.S = _graph.similarity_topk(Xg, model.S_topk, model.S_eps)
+        use_graph = self.use_graph = model.S is not None
+        D = model.S.sum(axis=1) if use_graph else None                  # als.py:357 (S's dtype)
+
+        # ---- init (als.py:360-376): same PCG64 stream, order U, V, W_f ----------
+        m_pad, n_pad = shard.padded_rows(m), shard.padded_rows(n)
+        U_d = self.U_d = torch.zeros(m_pad, ld, dtype=f32, device=dev)
+        V_d = self.V_d = torch.zeros(n_pad, ld, dtype=f32, device=dev)
+        W_d = self.W_d = [torch.zeros(features[nm].shape[1], ld, dtype=f32, device=dev) for nm in names]
+        W64_d = self.W64_d = [torch.zeros(features[nm].shape[1] * k, dtype=f64, device=dev) for nm in names]
+        if init is None:
+            rng = np.random.default_rng(model.random_state)             # als.py:329
+            U_d[:m, :k] = torch.from_numpy(rng.normal(scale=SCALE_FACTOR, size=(m, k)).astype(np.float32)).to(dev)
+            V_d[:n, :k] = torch.from_numpy(rng.normal(scale=SCALE_FACTOR, size=(n, k)).astype(np.float32)).to(dev)
+            for f, nm in enumerate(names):
+                w0 = rng.normal(scale=SCALE_FACTOR, size=(features[nm].shape[1], k))
+                W64_d[f].copy_(torch.from_numpy(w0.reshape(-1)).to(dev))
+                W_d[f][:, :k] = torch.from_numpy(w0.astype(np.float32)).to(dev)
+        elif isinstance(init, str) and init == "device":
+            g = torch.Generator(device=dev)
+            g.manual_seed(int(model.random_state))
+            U_d[:m, :k].normal_(0.0, SCALE_FACTOR, generator=g)
+            V_d[:n, :k].normal_(0.0, SCALE_FACTOR, generator=g)
+            for f in range(len(names)):
+                W_d[f][:, :k].normal_(0.0, SCALE_FACTOR, generator=g)
+                W64_d[f].copy_(W_d[f][:, :k].reshape(-1).double())
+        else:
+            U_d[:m, :k] = torch.as_tensor(np.asarray(init["U"], dtype=np.float32)).to(dev)
+            V_d[:n, :k] = torch.as_tensor(np.asarray(init["V"], dtype=np.float32)).to(dev)
+            for f, nm in enumerate(names):
+                w0 = np.asarray(init["W"][nm], dtype=np.float64)
+                W64_d[f].copy_(torch.from_numpy(w0.reshape(-1)).to(dev))
+                W_d[f][:, :k] = torch.from_numpy(w0.astype(np.float32)).to(dev)
+        self.b_u_d = torch.zeros(m_pad, dtype=f32, device=dev)
+        self.b_i_d = torch.zeros(n_pad, dtype=f32, device=dev)
+        self.mu_d = torch.full((1,), float(mu0), dtype=f32, device=dev)
+        model.mu = float(mu0)
+        self.X_d = [torch.from_numpy(np.ascontiguousarray(features[nm], dtype=np.float32)).to(dev) for nm in names]
+        self.Z_d = torch.zeros(n_pad, ld, dtype=f32, device=dev) if names else V_d
+
+        # ---- regularisers (als.py:379-384, 426, 450-454), folded in float64 ------
+        item_counts = (rt.cindptr[1:] - rt.cindptr[:-1]).cpu().numpy().astype(float)
+        lambda_v_i = model._item_reg(item_counts).astype(float)
+        reg_item = lambda_v_i + EPS
+        if use_graph:
+            reg_item = reg_item + float(model.alpha) * D.astype(np.float64)
+        self.reg_item_d = torch.from_numpy(reg_item.astype(np.float32)).to(dev)
+        self.reg_user = float(np.float32(model.lambda_u + EPS))
+        self.lam_bu = float(np.float32(model.lambda_bu + EPS))
+        self.lam_bi = float(np.float32(float(model.lambda_bi) + EPS))
+
+        # ---- schedules: longest rows first; each rank keeps its contiguous slab ----
+        u_order, u_nonempty = row_schedule(rt.indptr)
+        i_order, i_nonempty = row_schedule(rt.cindptr)
+        if shard.active:
+            self.ulo, self.uhi = shard.my_range(m)
+            self.ilo, self.ihi = shard.my_range(n)
+            uo = u_order[:u_nonempty]
+            self.u_list = uo[(uo >= self.ulo) & (uo < self.uhi)].contiguous()
+            io = i_order[:i_nonempty]
+            self.i_list = io[(io >= self.ilo) & (io < self.ihi)].contiguous()
+        else:
+            self.ulo, self.uhi, self.ilo, self.ihi = 0, m, 0, n
+            self.u_list, self.i_list = u_order[:u_nonempty], i_order[:i_nonempty]
+        if use_graph:
+            self.i_list = i_order[:i_nonempty]      # the Gauss–Seidel sweep is not sharded (§8e)
+
+        need = C.c_size_t(0)
+        check(lib.b200als_step_workspace_bytes(k, model.gram_path, max(m, n), C.byref(need)), "step_workspace_bytes")
+        self.ws = torch.empty(need.value, dtype=torch.uint8, device=dev)
+        self.status = torch.zeros(_lib.STATUS_WORDS, dtype=torch.int32, device=dev)
+        self.n_iters = int(model.n_iters)
+        self.acc = torch.zeros(6, dtype=f64, device=dev)
+        self.hist = torch.zeros(max(self.n_iters, 1), 6, dtype=f64, device=dev)
+
+        if use_graph:
+            sptr, sidx, sval = _graph.to_csr(model.S)
+            self.level_ptr, level_rows = _graph.level_schedule(sptr, sidx, item_counts > 0)
+            self.sptr_d = torch.from_numpy(sptr).to(dev)
+            self.sidx_d = torch.from_numpy(sidx).to(dev)
+            self.sval_d = torch.from_numpy(sval).to(dev)
+            self.level_rows_d = torch.from_numpy(level_rows).to(dev)
+            self.chol_d = torch.empty(n * k * k, dtype=f32, device=dev)
+            self.aux_d = torch.empty(n * (2 * k + 2), dtype=f32, device=dev)
+        else:
+            self.chol_d = self.aux_d = None
+        if names:
+            self.G_d = torch.empty(n * k * k, dtype=f64, device=dev)
+            self.cvec_d = torch.empty(n * k, dtype=f64, device=dev)
+            self.Zmf_d = torch.empty(n_pad, ld, dtype=f32, device=dev)
+            dmax = max(int(x.shape[1]) for x in self.X_d)
+            self.A_d = torch.empty((dmax * k) ** 2, dtype=f64, device=dev)
+            self.Wnew64 = [torch.empty_like(w) for w in W64_d]
+            self.xptr = (C.c_void_p * len(names))(*[x.data_ptr() for x in self.X_d])
+            self.wptr = (C.c_void_p * len(names))(*[w.data_ptr() for w in W_d])
+            self.dims = (C.c_int32 * len(names))(*[int(x.shape[1]) for x in self.X_d])
+        self.launches = 0
+
+    # ---- small wrappers ---------------------------------------------------------
+    def _stream(self):
+        return torch.cuda.current_stream().cuda_stream
+
+    def _compose(self, out, skip=-1):
+        check(self.lib.b200als_compose_z(ptr(self.V_d), self.ld, self.rt.n, self.k, len(self.names), self.xptr,
+                                         self.dims, self.wptr, self.ld, skip, ptr(out), self.ld, self._stream()),
+              "compose_z")
+        self.launches += 1
+
+    def _step(self, indptr, indices, vals, n_rows, rows, F, bias_other, reg, reg_row, lamb, X, bias_own, mode):
+        a = StepArgs()
+        a.struct_bytes = C.sizeof(StepArgs)
+        a.k, a.mode, a.path = self.k, mode, self.model.gram_path
+        a.n_rows = n_rows
+        a.indptr, a.indices, a.vals = ptr(indptr), ptr(indices), ptr(vals)
+        a.rows, a.n_list = ptr(rows), rows.numel()
+        a.F, a.ldf = ptr(F), self.ld
+        a.bias_other, a.mu = ptr(bias_other), ptr(self.mu_d)
+        a.reg, a.reg_row = reg, ptr(reg_row)
+        a.lam_bias, a.lam_bias_row = lamb, None
+        a.X, a.ldx = ptr(X), self.ld
+        a.bias_own = ptr(bias_own)
+        a.chol_out = ptr(self.chol_d) if mode == _lib.STEP_FACTOR else None
+        a.aux_out = ptr(self.aux_d) if mode == _lib.STEP_FACTOR else None
+        a.status = ptr(self.status)
+        a.workspace, a.workspace_bytes = ptr(self.ws), self.ws.numel()
+        check(self.lib.b200als_row_step(C.byref(a), self._stream()), "row_step")
+        self.launches += self.lib.b200als_last_launch_count() + 1      # + the cursor memset
+
+    def _mark(self, phase):
+        """Profile mode: CUDA events on the launching stream around each phase."""
+        if self.profile:
+            ev = torch.cuda.Event(enable_timing=True)
+            ev.record()
+            self._events.append((phase, ev))
+
+    def collect_phase_times(self):
+        """Resolve recorded events into per-phase milliseconds (call after a sync)."""
+        for (p0, e0), (p1, e1) in zip(self._events[:-1], self._events[1:]):
+            if p0 != "end":
+                self.phase_ms[p0].append(e0.elapsed_time(e1))
+        self._events = []
+        return self.phase_ms
+
+    # ---- one ALS iteration (als.py:408-517) ------------------------------------------
+    def iteration(self, it: int) -> None:
+        lib, rt, model, shard = self.lib, self.rt, self.model, self.shard
+        m, n, k, ld = rt.m, rt.n, self.k, self.ld
+        names = self.names
+        stream = self._stream()
+        self.launches = 0
+        self._mark("compose")
+        if names:
+            self._compose(self.Z_d)                                     # als.py:411
+        # (1) users (als.py:414-433)
+        self._mark("user")
+        self._step(rt.indptr, rt.indices, rt.vals, m, self.u_list, self.Z_d, self.b_i_d, self.reg_user, None,
+                   self.lam_bu, self.U_d, self.b_u_d, _lib.STEP_SOLVE)
+        if shard.active:
+            shard.all_gather_rows(self.U_d, m)
+            shard.all_gather_rows(self.b_u_d, m)
+        # (2) items (als.py:436-466); the item step ignores the feature term
+        self._mark("item")
+        if self.use_graph:
+            self._step(rt.cindptr, rt.cindices, rt.cvals, n, self.i_list, self.U_d, self.b_u_d, 0.0,
+                       self.reg_item_d, self.lam_bi, self.V_d, self.b_i_d, _lib.STEP_FACTOR)
+            lp = self.level_ptr
+            for lv in range(lp.size - 1):
+                lo, hi = int(lp[lv]), int(lp[lv + 1])
+                check(lib.b200als_graph_level_solve(
+                    k, self.level_rows_d.data_ptr() + 4 * lo, hi - lo, ptr(self.chol_d), ptr(self.aux_d),
+                    ptr(self.sptr_d), ptr(self.sidx_d), ptr(self.sval_d), float(model.alpha), self.lam_bi, None,
+                    ptr(self.V_d), ld, ptr(self.b_i_d), stream), "graph_level_solve")
+                self.launches += 1
+        else:
+            self._step(rt.cindptr, rt.cindices, rt.cvals, n, self.i_list, self.U_d, self.b_u_d, 0.0,
+                       self.reg_item_d, self.lam_bi, self.V_d, self.b_i_d, _lib.STEP_SOLVE)
+            if shard.active:
+                shard.all_gather_rows(self.V_d, n)
+                shard.all_gather_rows(self.b_i_d, n)
+        # (3) W_f (als.py:468-501)
+        self._mark("wstep")
+        if names and ((it % model.update_w_every == 0) or (it == self.n_iters - 1)):
+            check(lib.b200als_item_gram_f64(n, ptr(rt.cindptr), ptr(rt.cindices), ptr(rt.cvals), k,
+                                            ptr(self.U_d), ld, ptr(self.b_u_d), ptr(self.b_i_d), ptr(self.mu_d),
+                                            ptr(self.G_d), ptr(self.cvec_d), stream), "item_gram_f64")
+            self.launches += 1
+            for f, nm in enumerate(names):
+                d = int(self.X_d[f].shape[1])
+                self._compose(self.Zmf_d, skip=f)   # every W still old: `residual` is never refreshed (als.py:474-489)
+                lam = float(model.lambda_w.get(nm, 0.0)) + EPS
+                check(lib.b200als_wstep_system(n, k, d, ptr(self.X_d[f]), ptr(self.G_d), ptr(self.cvec_d),
+                                               ptr(self.Zmf_d), ld, lam, ptr(self.A_d), ptr(self.Wnew64[f]), stream),
+                      "wstep_system")
+                check(lib.b200als_cholesky_solve_f64(ptr(self.A_d), ptr(self.Wnew64[f]), d * k, ptr(self.status),
+                                                     stream), "cholesky_solve_f64")
+                self.launches += 6
+            for f in range(len(names)):
+                self.W64_d[f].copy_(self.Wnew64[f])
+                self.W_d[f][:, :k] = self.Wnew64[f].view(-1, k).to(torch.float32)
+        # (4) mu, RMSE, norms (als.py:503-517)
+        self._mark("stats")
+        if names:
+            self._compose(self.Z_d)
+        acc = self.acc
+        acc.zero_()
+        ulo, uhi = self.ulo, self.uhi
+        check(lib.b200als_residual_stats(uhi - ulo, rt.indptr.data_ptr() + 8 * ulo, ptr(rt.indices), ptr(rt.vals), k,
+                                         self.U_d.data_ptr() + 4 * ld * ulo, ld, ptr(self.Z_d), ld,
+                                         self.b_u_d.data_ptr() + 4 * ulo, ptr(self.b_i_d), ptr(acc), stream),
+              "residual_stats")
+        if shard.active:
+            shard.all_reduce_sum(acc[:2])
+        check(lib.b200als_sumsq(ptr(self.U_d), m, k, ld, acc.data_ptr() + 16, stream), "sumsq")
+        check(lib.b200als_sumsq(ptr(self.V_d), n, k, ld, acc.data_ptr() + 24, stream), "sumsq")
+        check(lib.b200als_sumsq(ptr(self.b_u_d), 1, m, m, acc.data_ptr() + 32, stream), "sumsq")
+        check(lib.b200als_sumsq(ptr(self.b_i_d), 1, n, n, acc.data_ptr() + 40, stream), "sumsq")
+        slot = it % self.hist.shape[0]
+        check(lib.b200als_finalize_iter(ptr(acc), rt.nnz, ptr(self.mu_d), self.hist.data_ptr() + 48 * slot, stream),
+              "finalize_iter")
+        self.launches += 6
+        self._mark("end")
+
+    # ---- host sync points -----------------------------------------------------------------
+    def raise_if_bad(self) -> None:
+        st = self.status.cpu().numpy()
+        if st[0] != 0:
+            raise np.linalg.LinAlgError(
+                f"{int(st[0])} normal matrices were not positive definite (first row {int(st[1])})")
+
+    def read_history(self, done: int) -> np.ndarray:
+        h = self.hist[:done].cpu().numpy()
+        self.raise_if_bad()
+        return h
+
+    def finish(self, done: int) -> None:
+        """Copy the learned parameters back to the model's public float64 attributes."""
+        model, rt, k = self.model, self.rt, self.k
+        h = self.read_history(done)
+        model._set_history(h)
+        if done:
+            model.mu = float(h[-1, 5])
+        model.U = self.U_d[:rt.m, :k].double().cpu().numpy()
+        model.V = self.V_d[:rt.n, :k].double().cpu().numpy()
+        model.b_u = self.b_u_d[:rt.m].double().cpu().numpy()
+        model.b_i = self.b_i_d[:rt.n].double().cpu().numpy()
+        for f, nm in enumerate(self.names):
+            model.W[nm] = self.W64_d[f].view(-1, k).cpu().numpy().copy()
+        model.launches_per_iter = self.launches

@@ -156,8 +156,10 @@ class SparseALSOracle:
 
         on_iter(it, self) is called after each iteration's history append.
         init: optional dict(U=, V=, W={}) to skip RNG draws (big shapes).
-        max_rows: (CPU-baseline sampling only) process at most this many user
-        rows and item rows per sweep; never used for parity.
+        max_rows: (CPU-baseline sampling only) int or (users, items): process only
+        the first so-many user rows and item rows per sweep and skip the W / mu
+        steps; `self.sampled_ratings` reports the ratings touched.  Never used
+        for parity.
         """
         rng = np.random.default_rng(self.random_state)                 # als.py:329
         indptr, indices, vals = sp["indptr"], sp["indices"], sp["vals"]
@@ -201,8 +203,12 @@ class SparseALSOracle:
         lambda_v_i = item_reg(item_counts, self.lambda_v, self.pop_reg_mode).astype(float)
         lambda_bi_i = np.full(n, float(self.lambda_bi), dtype=float)   # als.py:384
 
-        mu_rows = m if max_rows is None else min(m, max_rows)
-        mi_rows = n if max_rows is None else min(n, max_rows)
+        if max_rows is None:
+            mu_rows, mi_rows = m, n
+        else:
+            mr_u, mr_i = (max_rows, max_rows) if np.isscalar(max_rows) else max_rows
+            mu_rows, mi_rows = min(m, int(mr_u)), min(n, int(mr_i))
+        self.sampled_ratings = (int(indptr[mu_rows] - indptr[0]), int(cindptr[mi_rows] - cindptr[0]))
 
         for it in range(self.n_iters):                                 # als.py:408
             Z_full = self._compose_Z(self.V, features)                 # als.py:411

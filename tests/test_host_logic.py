@@ -1,0 +1,209 @@
+"""CPU: host-side logic — config surface, drop-in shim, C-ABI symbol table, graph
+schedule, row sharding over gloo (world_size 2), loud failure without a GPU."""
+import ctypes
+import dataclasses
+import os
+import re
+import subprocess
+import sys
+
+import numpy as np
+import pytest
+
+from _util import REPO, load_case, make_cfg
+
+
+def test_config_surface_matches_reference_fields():
+    import b200als
+    core = [f.name for f in dataclasses.fields(b200als.CoreConfig)]
+    assert core == ["n_factors", "n_iters", "lambda_u", "lambda_v", "pop_reg_mode", "random_state", "update_w_every"]
+    c = b200als.CoreConfig(8, 3, 1.0, 2.0)                      # positional, als_config.py:57-66
+    assert (c.pop_reg_mode, c.random_state, c.update_w_every) == (None, 42, 5)
+    assert [f.name for f in dataclasses.fields(b200als.BiasesConfig)] == ["lambda_bu", "lambda_bi"]
+    s = b200als.GraphSimConfig()
+    assert (s.source, s.feature_name, s.metric, s.topk, s.eps) == ("feature", "genres", "cosine", 50, 1e-8)
+    g = b200als.GraphConfig()
+    assert g.alpha == 0.0 and g.sim is None
+    a = b200als.ALSConfig(core=c)
+    assert a.biases.lambda_bu is None and a.graph.alpha == 0.0
+
+
+def test_constructor_semantics():
+    import b200als
+    cfg = b200als.ALSConfig(core=b200als.CoreConfig(8, 3, 1.5, 2.5), biases=b200als.BiasesConfig(0.0, None))
+    m = b200als.ALS(cfg, lambda_w={"g": 1.0})
+    assert m.lambda_bu == 1.5 and m.lambda_bi == 2.5            # falsy → fallback (als.py:166-167)
+    assert m.S_topk is None and m.S_eps == 1e-10                # EPS default (als.py:173-174)
+    assert set(m.history) == {"train_rmse", "U_norm", "V_norm", "bu_norm", "bi_norm"}
+    assert m.U is None and m.mu == 0.0 and m.W == {} and m.lambda_w == {"g": 1.0}
+    with pytest.raises(ValueError):
+        b200als.ALS(None)
+    with pytest.raises(RuntimeError):
+        m.predict()
+
+
+def test_scripts_shim_resolves_to_b200():
+    from scripts.als import ALS
+    from scripts.als_config import ALSConfig, CoreConfig, BiasesConfig, GraphConfig, GraphSimConfig  # noqa: F401
+    import b200als
+    assert ALS is b200als.ALS and ALSConfig is b200als.ALSConfig
+
+
+def test_c_abi_exports_every_declared_symbol():
+    """The library loads without a GPU and exports exactly what include/b200als.h declares."""
+    import b200als
+    hdr = open(os.path.join(REPO, "include", "b200als.h")).read()
+    hdr = re.sub(r"/\*.*?\*/", "", hdr, flags=re.S)
+    declared = set(re.findall(r"\b(b200als_[a-z0-9_]+)\s*\(", hdr))
+    assert declared, "no declarations parsed"
+    lib = ctypes.CDLL(b200als._lib.LIB_PATH)
+    for sym in declared:
+        assert hasattr(lib, sym), f"{sym} declared in b200als.h but not exported"
+    assert declared == set(b200als._lib.EXPORTED_SYMBOLS), declared ^ set(b200als._lib.EXPORTED_SYMBOLS)
+    assert b200als._lib.load().b200als_abi_version() == b200als._lib.ABI_VERSION
+    m = re.search(r"#define\s+B200ALS_ABI_VERSION\s+(\d+)", hdr)
+    assert int(m.group(1)) == b200als._lib.ABI_VERSION
+    # struct layout agreed between C and ctypes: size is checked by the library at call time
+    assert ctypes.sizeof(b200als._lib.StepArgs) % 8 == 0
+
+
+def test_invalid_arguments_are_rejected_without_a_gpu():
+    import b200als
+    lib = b200als._lib.load()
+    need = ctypes.c_size_t(0)
+    assert lib.b200als_step_workspace_bytes(0, 0, 10, ctypes.byref(need)) == -1
+    assert b"k out of range" in lib.b200als_last_error()
+    a = b200als._lib.StepArgs()
+    a.struct_bytes = 4
+    assert lib.b200als_row_step(ctypes.byref(a), None) == -1
+    assert b"ABI" in lib.b200als_last_error()
+
+
+def test_product_fails_loudly_without_gpu():
+    import torch
+    if torch.cuda.is_available():
+        pytest.skip("GPU present")
+    import b200als
+    c = load_case("small_plain")
+    model = b200als.ALS(make_cfg(c.cfgd))
+    with pytest.raises(b200als._lib.B200ALSError):
+        model.fit_coo(c.flat, c.vals, (c.m, c.n), verbose=0)
+    assert model.U is None
+
+
+def test_product_never_imports_oracle():
+    pkg = os.path.join(REPO, "collaborative-filtering_b200")
+    for root, _, files in os.walk(pkg):
+        for fn in files:
+            if fn.endswith((".py", ".cu", ".cuh", ".h")):
+                src = open(os.path.join(root, fn)).read()
+                assert "als_oracle" not in src, f"{fn} references the oracle module"
+                assert not re.search(r"^\s*(from|import)\s+[\w.]*oracle", src, flags=re.M), fn
+                assert not re.search(r"#include\s+[\"<][^\n]*oracle", src), fn
+
+
+def test_similarity_graph_matches_reference_fixture():
+    from b200als import graph
+    for name in ("small_graph_topk5", "small_graph_topk40"):
+        c = load_case(name)
+        sim = c.cfgd["sim"]
+        S = graph.similarity_topk(c.features["genres"], sim["topk"], sim["eps"])
+        assert S.dtype == c.z["S"].dtype and np.array_equal(S, c.z["S"])
+        sptr, sidx, sval = graph.to_csr(S)
+        dense = np.zeros_like(S)
+        for i in range(S.shape[0]):
+            dense[i, sidx[sptr[i]:sptr[i + 1]]] = sval[sptr[i]:sptr[i + 1]]
+        assert np.array_equal(dense, S.astype(np.float32))
+
+
+def test_level_schedule_reproduces_gauss_seidel():
+    """Level-parallel execution (all items of a level read, then write) == sequential sweep."""
+    from b200als import graph
+    rng = np.random.default_rng(1)
+    n, k = 120, 5
+    X = (rng.random((n, 6)) < 0.35).astype(np.float32)
+    S = graph.similarity_topk(X, 7, 1e-8)
+    rated = rng.random(n) < 0.85
+    sptr, sidx, sval = graph.to_csr(S)
+    lp, rows = graph.level_schedule(sptr, sidx, rated)
+    assert sorted(rows.tolist()) == np.flatnonzero(rated).tolist()
+    V0 = rng.normal(size=(n, k))
+    Vs = V0.copy()
+    for i in range(n):                                   # als.py:436-461 shape of the dependency
+        if rated[i]:
+            Vs[i] = 0.5 * (S[i] @ Vs) + 0.1
+    Vl = V0.copy()
+    for lv in range(lp.size - 1):
+        lvl = rows[lp[lv]:lp[lv + 1]]
+        new = [0.5 * (S[i] @ Vl) + 0.1 for i in lvl]     # whole level reads before any write
+        for i, v in zip(lvl, new):
+            Vl[i] = v
+    assert np.allclose(Vs, Vl, rtol=0, atol=1e-12)
+
+
+def test_synth_is_deterministic_and_well_formed():
+    from b200als.synth import synth_ratings
+    f1, v1 = synth_ratings(50, 80, 700, seed=3)
+    f2, v2 = synth_ratings(50, 80, 700, seed=3)
+    assert np.array_equal(f1, f2) and np.array_equal(v1, v2)
+    assert f1.size == 700 and np.unique(f1).size == 700 and np.all(np.diff(f1) > 0)
+    assert f1.min() >= 0 and f1.max() < 50 * 80
+    assert np.all((v1 * 2) == np.round(v1 * 2)) and v1.min() >= 0.5 and v1.max() <= 5.0
+
+
+def test_shard_partition_covers_rows():
+    from b200als import Shard
+    for n_rows in (1, 7, 8, 9, 1000):
+        for world in (1, 2, 3, 8):
+            seen = []
+            for r in range(world):
+                s = Shard(r, world)
+                lo, hi = s.my_range(n_rows)
+                seen += list(range(lo, hi))
+                assert s.padded_rows(n_rows) % world == 0 and s.padded_rows(n_rows) >= n_rows
+            assert seen == list(range(n_rows))
+
+
+_GLOO_WORKER = r'''
+import os, sys
+sys.path.insert(0, os.environ["B200ALS_REPO"])
+import torch, torch.distributed as td
+import b200als
+td.init_process_group("gloo", init_method="tcp://127.0.0.1:" + os.environ["PORT"],
+                      rank=int(os.environ["RANK"]), world_size=2)
+s = b200als.Shard.from_env()
+m, ld = 7, 4
+full = torch.zeros(s.padded_rows(m), ld)
+lo, hi = s.my_range(m)
+full[lo:hi] = torch.arange(lo, hi, dtype=torch.float32)[:, None] + 0.25 * s.rank
+s.all_gather_rows(full, m)
+want = torch.zeros_like(full)
+for r in range(2):
+    rl, rh = b200als.Shard(r, 2).my_range(m)
+    want[rl:rh] = torch.arange(rl, rh, dtype=torch.float32)[:, None] + 0.25 * r
+assert torch.equal(full, want), (full, want)
+acc = torch.tensor([1.0 + s.rank, 10.0], dtype=torch.float64)
+s.all_reduce_sum(acc)
+assert acc.tolist() == [3.0, 20.0]
+s.barrier()
+td.destroy_process_group()
+print("ok", s.rank)
+'''
+
+
+def test_row_sharding_collectives_gloo_world2(tmp_path):
+    import socket
+    sock = socket.socket()
+    sock.bind(("127.0.0.1", 0))
+    port = sock.getsockname()[1]
+    sock.close()
+    script = tmp_path / "worker.py"
+    script.write_text(_GLOO_WORKER)
+    procs = []
+    for r in range(2):
+        env = dict(os.environ, RANK=str(r), PORT=str(port), B200ALS_REPO=REPO)
+        procs.append(subprocess.Popen([sys.executable, str(script)], env=env,
+                                      stdout=subprocess.PIPE, stderr=subprocess.STDOUT))
+    for p in procs:
+        out, _ = p.communicate(timeout=180)
+        assert p.returncode == 0, out.decode()
