@@ -10,7 +10,7 @@ import os
 
 _HERE = os.path.dirname(os.path.abspath(__file__))
 LIB_PATH = os.path.join(_HERE, "libb200als.so")
-ABI_VERSION = 3
+ABI_VERSION = 4
 MAX_K = 160
 MAX_FEATURES = 8
 STATUS_WORDS = 4
@@ -33,7 +33,7 @@ class StepArgs(C.Structure):
         ("n_rows", C.c_int64),
         ("indptr", vp), ("indices", vp), ("vals", vp),
         ("rows", vp), ("n_list", C.c_int64),
-        ("F", vp), ("ldf", C.c_int64),
+        ("F", vp), ("ldf", C.c_int64), ("n_f_rows", C.c_int64),
         ("bias_other", vp), ("mu", vp),
         ("reg", C.c_float), ("reg_row", vp),
         ("lam_bias", C.c_float), ("lam_bias_row", vp),

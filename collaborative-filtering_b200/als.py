@@ -428,14 +428,15 @@ class FitSession:
               "compose_z")
         self.launches += 1
 
-    def _step(self, indptr, indices, vals, n_rows, rows, F, bias_other, reg, reg_row, lamb, X, bias_own, mode):
+    def _step(self, indptr, indices, vals, n_rows, rows, F, n_f_rows, bias_other, reg, reg_row, lamb, X, bias_own,
+              mode):
         a = StepArgs()
         a.struct_bytes = C.sizeof(StepArgs)
         a.k, a.mode, a.path = self.k, mode, self.model.gram_path
         a.n_rows = n_rows
         a.indptr, a.indices, a.vals = ptr(indptr), ptr(indices), ptr(vals)
         a.rows, a.n_list = ptr(rows), rows.numel()
-        a.F, a.ldf = ptr(F), self.ld
+        a.F, a.ldf, a.n_f_rows = ptr(F), self.ld, n_f_rows
         a.bias_other, a.mu = ptr(bias_other), ptr(self.mu_d)
         a.reg, a.reg_row = reg, ptr(reg_row)
         a.lam_bias, a.lam_bias_row = lamb, None
@@ -475,7 +476,7 @@ class FitSession:
             self._compose(self.Z_d)                                     # als.py:411
         # (1) users (als.py:414-433)
         self._mark("user")
-        self._step(rt.indptr, rt.indices, rt.vals, m, self.u_list, self.Z_d, self.b_i_d, self.reg_user, None,
+        self._step(rt.indptr, rt.indices, rt.vals, m, self.u_list, self.Z_d, n, self.b_i_d, self.reg_user, None,
                    self.lam_bu, self.U_d, self.b_u_d, _lib.STEP_SOLVE)
         if shard.active:
             shard.all_gather_rows(self.U_d, m)
@@ -483,7 +484,7 @@ class FitSession:
         # (2) items (als.py:436-466); the item step ignores the feature term
         self._mark("item")
         if self.use_graph:
-            self._step(rt.cindptr, rt.cindices, rt.cvals, n, self.i_list, self.U_d, self.b_u_d, 0.0,
+            self._step(rt.cindptr, rt.cindices, rt.cvals, n, self.i_list, self.U_d, m, self.b_u_d, 0.0,
                        self.reg_item_d, self.lam_bi, self.V_d, self.b_i_d, _lib.STEP_FACTOR)
             lp = self.level_ptr
             for lv in range(lp.size - 1):
@@ -494,7 +495,7 @@ class FitSession:
                     ptr(self.V_d), ld, ptr(self.b_i_d), stream), "graph_level_solve")
                 self.launches += 1
         else:
-            self._step(rt.cindptr, rt.cindices, rt.cvals, n, self.i_list, self.U_d, self.b_u_d, 0.0,
+            self._step(rt.cindptr, rt.cindices, rt.cvals, n, self.i_list, self.U_d, m, self.b_u_d, 0.0,
                        self.reg_item_d, self.lam_bi, self.V_d, self.b_i_d, _lib.STEP_SOLVE)
             if shard.active:
                 shard.all_gather_rows(self.V_d, n)

@@ -1,67 +1,285 @@
 // row_solve.cuh — the per-row epilogue shared by every Gram path (A6/A7/A11):
-// in-shared-memory Cholesky of the k x k normal matrix, forward substitution
-// folded in as an augmented row, back substitution, closed-form bias.
+// blocked in-shared-memory Cholesky of the k x k normal matrix, forward
+// substitution folded in as an augmented row, blocked back substitution,
+// closed-form bias.
 //
-// Layout: G is (KP+1) rows x LD floats, LD = KP+1 (odd → column walks are
-// bank-conflict free).  Rows 0..KP-1 hold the lower triangle of A (diagonal
-// already regularised; padded columns k..KP-1 carry a unit diagonal so they
-// factor to the identity).  Row KP holds the right-hand side b, which the
-// right-looking factorisation turns into y = L^-1 b for free.
+// Storage: 4x4 tiles of the LOWER triangle only.  Tile (ti, tj), ti >= tj,
+// lives at Gt + (ti(ti+1)/2 + tj) * 16, row-major inside the tile, so a tile
+// is four 16-byte vectors and consecutive tiles are consecutive in memory
+// (conflict-free LDS.128 / STS.128).  kt = ceil(k/4) tile rows hold A; tile
+// row kt holds the right-hand side in its first row (other rows zero), so the
+// right-looking update turns it into y = L^-1 b.  k=128 needs 36 KB (vs 66 KB
+// dense), which is what lets 3 CTAs share an SM and hide each other's
+// pivot chains.
+//
+// Algorithm: panels of 8 columns (two tile columns).  Per panel:
+//   (a) one thread factors the 8x8 diagonal block in registers (rsqrt+Newton);
+//   (b) every remaining row solves its 8 entries against it (thread per row);
+//   (c) all threads apply the rank-8 update to the trailing tiles (thread per
+//       4x4 tile, 128 FMA per 12 vector loads; rows of the panel are shared
+//       by neighbouring threads, so the loads broadcast).
+// Three barriers per panel instead of two per column.
 #pragma once
 #include "common.cuh"
 
 namespace b200als {
 
-// Right-looking Cholesky on the lower triangle, all `nthr` threads of the CTA.
-// Returns false (uniformly) on a non-positive / NaN pivot.
-template <int KP>
-__device__ __forceinline__ bool chol_factor_smem(float* __restrict__ G, int kk, int tid, int nthr,
-                                                 int* __restrict__ flag_s) {
-    constexpr int LD = KP + 1;
-    const int lane = tid & 31, wid = tid >> 5, nw = nthr >> 5;
-    if (tid == 0) *flag_s = 0;
-    for (int j = 0; j < kk; ++j) {
-        __syncthreads();
-        const float d = G[j * LD + j];
-        if (!(d > 0.0f)) {           // uniform: every thread reads the same word
-            if (tid == 0) *flag_s = 1;
-            break;
-        }
-        const float sd = sqrtf(d);
-        const float inv = 1.0f / sd;
-        // scale column j (rows j+1..kk-1 and the rhs row KP)
-        for (int i = j + 1 + tid; i <= kk; i += nthr) {
-            const int row = (i == kk) ? KP : i;
-            G[row * LD + j] *= inv;
-        }
-        __syncthreads();
-        if (tid == 0) G[j * LD + j] = sd;
-        // trailing update: rows i in (j, kk) plus rhs row; cols c in (j, min(i, kk-1)]
-        for (int i = j + 1 + wid; i <= kk; i += nw) {
-            const int row = (i == kk) ? KP : i;
-            const float lij = G[row * LD + j];
-            const int cmax = (i == kk) ? kk - 1 : i;
-            for (int c = j + 1 + lane; c <= cmax; c += 32) G[row * LD + c] -= lij * G[c * LD + j];
-        }
-    }
-    __syncthreads();
-    return *flag_s == 0;
+constexpr int SOLVE_NB = 8;
+
+__host__ __device__ constexpr int tri_tiles(int kt) { return (kt + 1) * (kt + 2) / 2; }   // incl. rhs tile row
+__host__ __device__ constexpr size_t solve_smem_floats(int KP) {
+    // tiles (+rhs tile row) + panel buffer Lp[(KP+4)][8] + Ld[64] + invd[KP+4] + x[KP+4] + 8 misc
+    return (size_t)tri_tiles(KP / 4) * 16 + (size_t)(KP + 4) * SOLVE_NB + 64 + 2 * (KP + 4) + 8;
 }
 
-// Back substitution L^T x = y with y in row KP; x overwrites row KP.
-template <int KP>
-__device__ __forceinline__ void chol_backsolve_smem(float* __restrict__ G, int kk, int tid, int nthr) {
-    constexpr int LD = KP + 1;
-    float* y = G + KP * LD;
-    for (int j = kk - 1; j >= 0; --j) {
-        __syncthreads();
-        const float xj = y[j] / G[j * LD + j];
-        // y[i] -= L[j][i] * x[j] for i < j   (row j of L is contiguous)
-        for (int i = tid; i < j; i += nthr) y[i] -= G[j * LD + i] * xj;
-        __syncthreads();
-        if (tid == 0) y[j] = xj;
+__device__ __forceinline__ int tile_off(int ti, int tj) { return ((ti * (ti + 1)) / 2 + tj) * 16; }
+
+// barrier among the `nthr` threads that solve one matrix: a named barrier, or just the warp
+__device__ __forceinline__ void bar_sync(int id, int nthr) {
+    if (nthr == 32) __syncwarp();
+    else asm volatile("bar.sync %0, %1;" ::"r"(id), "r"(nthr) : "memory");
+}
+
+// decode a linear index over the lower triangle: q -> (a, b), a >= b
+__device__ __forceinline__ void tri_decode(int q, int& a, int& b) {
+    a = (int)((sqrtf(8.0f * (float)q + 1.0f) - 1.0f) * 0.5f);
+    while ((a + 1) * (a + 2) / 2 <= q) ++a;
+    while (a * (a + 1) / 2 > q) --a;
+    b = q - a * (a + 1) / 2;
+}
+
+struct SolveSmem {
+    float* Gt;     // tiles
+    float* Lp;     // [(KP+4)][8] current panel, by global row
+    float* Ld;     // [8][8] diagonal block of the current panel
+    float* invd;   // [KP+4] 1 / L[j][j]
+    float* x;      // [KP+4] solution / scratch
+    int* flag;     // [0] = bad pivot
+    template <int KP>
+    __device__ __forceinline__ void carve(float* base) {
+        Gt = base;
+        Lp = Gt + tri_tiles(KP / 4) * 16;
+        Ld = Lp + (KP + 4) * SOLVE_NB;
+        invd = Ld + 64;
+        x = invd + (KP + 4);
+        flag = reinterpret_cast<int*>(x + (KP + 4));
     }
-    __syncthreads();
+};
+
+// Factor + forward substitution.  kt = ceil(k/4).  All `nthr` threads of barrier `bar`.
+// Returns false (uniformly) on a non-positive / NaN pivot.
+__device__ __forceinline__ bool chol_factor_tiles(const SolveSmem& S, int kt, int tid, int nthr, int bar) {
+    float* __restrict__ Gt = S.Gt;
+    float* __restrict__ Lp = S.Lp;
+    float* __restrict__ Ld = S.Ld;
+    if (tid == 0) *S.flag = 0;
+    for (int tc0 = 0; tc0 < kt; tc0 += 2) {
+        const int ntc = (kt - tc0) >= 2 ? 2 : 1;
+        const int nb = ntc * 4;
+        bar_sync(bar, nthr);
+        // ---- (a) diagonal block, one thread, registers ----------------------------------
+        if (tid == 0) {
+            float a[8][8];
+#pragma unroll
+            for (int r = 0; r < 8; ++r)
+#pragma unroll
+                for (int c = 0; c < 8; ++c) a[r][c] = (r == c) ? 1.0f : 0.0f;
+            {
+                const float4* t00 = reinterpret_cast<const float4*>(Gt + tile_off(tc0, tc0));
+#pragma unroll
+                for (int r = 0; r < 4; ++r) {
+                    float4 v = t00[r];
+                    a[r][0] = v.x; a[r][1] = v.y; a[r][2] = v.z; a[r][3] = v.w;
+                }
+                if (ntc == 2) {
+                    const float4* t10 = reinterpret_cast<const float4*>(Gt + tile_off(tc0 + 1, tc0));
+                    const float4* t11 = reinterpret_cast<const float4*>(Gt + tile_off(tc0 + 1, tc0 + 1));
+#pragma unroll
+                    for (int r = 0; r < 4; ++r) {
+                        float4 v = t10[r], w = t11[r];
+                        a[4 + r][0] = v.x; a[4 + r][1] = v.y; a[4 + r][2] = v.z; a[4 + r][3] = v.w;
+                        a[4 + r][4] = w.x; a[4 + r][5] = w.y; a[4 + r][6] = w.z; a[4 + r][7] = w.w;
+                    }
+                }
+            }
+            bool ok = true;
+            float inv[8];
+#pragma unroll
+            for (int p = 0; p < 8; ++p) {
+                const float d = a[p][p];
+                ok = ok && (d > 0.0f);
+                float iv = rsqrtf(d);
+                iv = iv * (1.5f - 0.5f * d * iv * iv);      // one Newton step: ~1 ulp
+                inv[p] = iv;
+                a[p][p] = d * iv;
+#pragma unroll
+                for (int r = p + 1; r < 8; ++r) a[r][p] *= iv;
+#pragma unroll
+                for (int r = p + 1; r < 8; ++r)
+#pragma unroll
+                    for (int c = p + 1; c <= r; ++c) a[r][c] = fmaf(-a[r][p], a[c][p], a[r][c]);
+            }
+            if (!ok) *S.flag = 1;
+            // write back: tiles, Ld (row-major 8x8, strictly-lower + diag), invd
+            float4* t00 = reinterpret_cast<float4*>(Gt + tile_off(tc0, tc0));
+#pragma unroll
+            for (int r = 0; r < 4; ++r) t00[r] = make_float4(a[r][0], a[r][1], a[r][2], a[r][3]);
+            if (ntc == 2) {
+                float4* t10 = reinterpret_cast<float4*>(Gt + tile_off(tc0 + 1, tc0));
+                float4* t11 = reinterpret_cast<float4*>(Gt + tile_off(tc0 + 1, tc0 + 1));
+#pragma unroll
+                for (int r = 0; r < 4; ++r) {
+                    t10[r] = make_float4(a[4 + r][0], a[4 + r][1], a[4 + r][2], a[4 + r][3]);
+                    t11[r] = make_float4(a[4 + r][4], a[4 + r][5], a[4 + r][6], a[4 + r][7]);
+                }
+            }
+#pragma unroll
+            for (int r = 0; r < 8; ++r) {
+                reinterpret_cast<float4*>(Ld + r * 8)[0] = make_float4(a[r][0], a[r][1], a[r][2], a[r][3]);
+                reinterpret_cast<float4*>(Ld + r * 8)[1] = make_float4(a[r][4], a[r][5], a[r][6], a[r][7]);
+                S.invd[tc0 * 4 + r] = inv[r];
+            }
+        }
+        bar_sync(bar, nthr);
+        if (*S.flag) break;
+        // ---- (b) panel rows below the block (+ rhs row): a <- a * Ld^-T ------------------
+        const int row0 = (tc0 + ntc) * 4;
+        const int nrows = (kt * 4 - row0) + 1;            // + the rhs row (tile row kt, local row 0)
+        for (int t = tid; t < nrows; t += nthr) {
+            const int i = row0 + t;                        // i == kt*4 → rhs row
+            const int ti = i >> 2, li = i & 3;
+            float4* p0 = reinterpret_cast<float4*>(Gt + tile_off(ti, tc0) + li * 4);
+            float4* p1 = reinterpret_cast<float4*>(Gt + tile_off(ti, tc0 + 1) + li * 4);
+            float a[8];
+            {
+                float4 v = *p0;
+                a[0] = v.x; a[1] = v.y; a[2] = v.z; a[3] = v.w;
+                if (ntc == 2) { float4 w = *p1; a[4] = w.x; a[5] = w.y; a[6] = w.z; a[7] = w.w; }
+                else { a[4] = a[5] = a[6] = a[7] = 0.0f; }
+            }
+#pragma unroll
+            for (int p = 0; p < 8; ++p) {
+                float s = a[p];
+#pragma unroll
+                for (int q = 0; q < p; ++q) s = fmaf(-a[q], Ld[p * 8 + q], s);
+                a[p] = s * S.invd[tc0 * 4 + p];
+            }
+            *p0 = make_float4(a[0], a[1], a[2], a[3]);
+            if (ntc == 2) *p1 = make_float4(a[4], a[5], a[6], a[7]);
+            reinterpret_cast<float4*>(Lp + i * 8)[0] = make_float4(a[0], a[1], a[2], a[3]);
+            reinterpret_cast<float4*>(Lp + i * 8)[1] = make_float4(a[4], a[5], a[6], a[7]);
+        }
+        bar_sync(bar, nthr);
+        // ---- (c) trailing update: tile(ti,tj) -= Lp[ti rows] * Lp[tj rows]^T ---------------
+        const int ta0 = tc0 + ntc;
+        const int na = kt - ta0;
+        const int ntri = na * (na + 1) / 2;
+        const int ntiles = ntri + na;                      // + rhs tile row
+        for (int q = tid; q < ntiles; q += nthr) {
+            int ti, tj;
+            if (q < ntri) {
+                int aa, bb;
+                tri_decode(q, aa, bb);
+                ti = ta0 + aa; tj = ta0 + bb;
+            } else {
+                ti = kt; tj = ta0 + (q - ntri);
+            }
+            float4* tp = reinterpret_cast<float4*>(Gt + tile_off(ti, tj));
+            float4 acc[4];
+#pragma unroll
+            for (int r = 0; r < 4; ++r) acc[r] = tp[r];
+            const float4* lr = reinterpret_cast<const float4*>(Lp + ti * 32);
+            const float4* lc = reinterpret_cast<const float4*>(Lp + tj * 32);
+#pragma unroll
+            for (int h = 0; h < 2; ++h) {                 // two halves of the 8-wide panel
+                float4 rr[4], cc[4];
+#pragma unroll
+                for (int r = 0; r < 4; ++r) { rr[r] = lr[r * 2 + h]; cc[r] = lc[r * 2 + h]; }
+#pragma unroll
+                for (int r = 0; r < 4; ++r) {
+                    const float4 a4 = rr[r];
+                    acc[r].x = fmaf(-a4.x, cc[0].x, fmaf(-a4.y, cc[0].y, fmaf(-a4.z, cc[0].z, fmaf(-a4.w, cc[0].w, acc[r].x))));
+                    acc[r].y = fmaf(-a4.x, cc[1].x, fmaf(-a4.y, cc[1].y, fmaf(-a4.z, cc[1].z, fmaf(-a4.w, cc[1].w, acc[r].y))));
+                    acc[r].z = fmaf(-a4.x, cc[2].x, fmaf(-a4.y, cc[2].y, fmaf(-a4.z, cc[2].z, fmaf(-a4.w, cc[2].w, acc[r].z))));
+                    acc[r].w = fmaf(-a4.x, cc[3].x, fmaf(-a4.y, cc[3].y, fmaf(-a4.z, cc[3].z, fmaf(-a4.w, cc[3].w, acc[r].w))));
+                }
+            }
+#pragma unroll
+            for (int r = 0; r < 4; ++r) tp[r] = acc[r];
+        }
+    }
+    bar_sync(bar, nthr);
+    return *S.flag == 0;
+}
+
+// Back substitution L^T x = y.  y sits in the rhs tile row; x ends in S.x[0..kt*4).
+__device__ __forceinline__ void chol_backsolve_tiles(const SolveSmem& S, int kt, int tid, int nthr, int bar) {
+    float* __restrict__ Gt = S.Gt;
+    float* __restrict__ x = S.x;
+    for (int j = tid; j < kt * 4; j += nthr) x[j] = Gt[tile_off(kt, j >> 2) + (j & 3)];
+    const int last_tc0 = ((kt - 1) >> 1) << 1;
+    for (int tc0 = last_tc0; tc0 >= 0; tc0 -= 2) {
+        const int ntc = (kt - tc0) >= 2 ? 2 : 1;
+        const int nb = ntc * 4;
+        bar_sync(bar, nthr);
+        if (tid == 0) {
+            // 8x8 (or 4x4) lower block, transposed solve from the bottom row up
+            float l[8][8];
+#pragma unroll
+            for (int r = 0; r < 8; ++r)
+#pragma unroll
+                for (int c = 0; c < 8; ++c) l[r][c] = 0.0f;
+            const float4* t00 = reinterpret_cast<const float4*>(Gt + tile_off(tc0, tc0));
+#pragma unroll
+            for (int r = 0; r < 4; ++r) {
+                float4 v = t00[r];
+                l[r][0] = v.x; l[r][1] = v.y; l[r][2] = v.z; l[r][3] = v.w;
+            }
+            float y[8];
+#pragma unroll
+            for (int r = 0; r < 8; ++r) y[r] = 0.0f;
+#pragma unroll
+            for (int r = 0; r < 4; ++r) y[r] = x[tc0 * 4 + r];
+            if (ntc == 2) {
+                const float4* t10 = reinterpret_cast<const float4*>(Gt + tile_off(tc0 + 1, tc0));
+                const float4* t11 = reinterpret_cast<const float4*>(Gt + tile_off(tc0 + 1, tc0 + 1));
+#pragma unroll
+                for (int r = 0; r < 4; ++r) {
+                    float4 v = t10[r], w = t11[r];
+                    l[4 + r][0] = v.x; l[4 + r][1] = v.y; l[4 + r][2] = v.z; l[4 + r][3] = v.w;
+                    l[4 + r][4] = w.x; l[4 + r][5] = w.y; l[4 + r][6] = w.z; l[4 + r][7] = w.w;
+                    y[4 + r] = x[tc0 * 4 + 4 + r];
+                }
+            }
+#pragma unroll
+            for (int j = 7; j >= 0; --j) {
+                if (j < nb) {
+                    const float xj = y[j] * S.invd[tc0 * 4 + j];
+                    y[j] = xj;
+#pragma unroll
+                    for (int i = 0; i < j; ++i) y[i] = fmaf(-l[j][i], xj, y[i]);
+                }
+            }
+#pragma unroll
+            for (int r = 0; r < 8; ++r)
+                if (r < nb) x[tc0 * 4 + r] = y[r];
+        }
+        bar_sync(bar, nthr);
+        // y_i -= sum_{c in panel} L[c][i] * x_c  for i < tc0*4  (row c of L is contiguous in tiles)
+        for (int i = tid; i < tc0 * 4; i += nthr) {
+            const int tj = i >> 2, lj = i & 3;
+            float acc = x[i];
+#pragma unroll
+            for (int c = 0; c < 8; ++c) {
+                if (c < nb) {
+                    const int row = tc0 * 4 + c;
+                    acc = fmaf(-Gt[tile_off(row >> 2, tj) + (row & 3) * 4 + lj], x[row], acc);
+                }
+            }
+            x[i] = acc;
+        }
+    }
+    bar_sync(bar, nthr);
 }
 
 struct RowEpilogueArgs {
@@ -74,23 +292,27 @@ struct RowEpilogueArgs {
     int32_t* status;
 };
 
-// G lower triangle + c (F^T q), s (F^T 1) in smem, t = sum q, cnt.
-// Applies regularisation, builds b = c - bias_old * s, solves, writes outputs.
-template <int KP>
-__device__ __forceinline__ void row_epilogue(float* __restrict__ G, const float* __restrict__ c_s,
-                                             const float* __restrict__ s_s, float t_sum, int64_t cnt, int64_t r,
-                                             const RowEpilogueArgs& a, int tid, int nthr, int* flag_s,
-                                             float* red_s) {
-    constexpr int LD = KP + 1;
+// Preconditions: the lower-triangle tiles of F^T F are in S.Gt (tile rows 0..kt-1), c_s = F^T q
+// and s_s = F^T 1 hold k entries, all visible to the `nthr` threads (barrier done by caller).
+// Adds the ridge, builds b = c - bias_old * s, factors, solves, writes X[r], bias_own[r]
+// (or the factor + aux in FACTOR mode).
+__device__ __forceinline__ void row_epilogue_tiles(const SolveSmem& S, const float* __restrict__ c_s,
+                                                   const float* __restrict__ s_s, float t_sum, int64_t cnt,
+                                                   int64_t r, const RowEpilogueArgs& a, int tid, int nthr, int bar) {
     const int k = a.k;
+    const int kt = (k + 3) >> 2;
+    float* __restrict__ Gt = S.Gt;
     const float bias_old = a.bias_own[r];
-    __syncthreads();
-    for (int i = tid; i < KP; i += nthr) {
-        G[i * LD + i] = (i < k) ? G[i * LD + i] + a.reg : 1.0f;
-        G[KP * LD + i] = (i < k) ? c_s[i] - bias_old * s_s[i] : 0.0f;
+    // ridge on the diagonal; identity on padded rows; rhs tile row
+    for (int i = tid; i < kt * 4; i += nthr) {
+        float* d = Gt + tile_off(i >> 2, i >> 2) + (i & 3) * 5;
+        *d = (i < k) ? *d + a.reg : 1.0f;
+        float* rt = Gt + tile_off(kt, i >> 2);
+        rt[i & 3] = (i < k) ? c_s[i] - bias_old * s_s[i] : 0.0f;
+        rt[4 + (i & 3)] = 0.0f; rt[8 + (i & 3)] = 0.0f; rt[12 + (i & 3)] = 0.0f;
     }
-    // (chol_factor_smem starts with a barrier)
-    const bool ok = chol_factor_smem<KP>(G, k, tid, nthr, flag_s);
+    if (tid < 24) S.Lp[(kt * 4 + 1) * 8 + tid] = 0.0f;       // rows kt*4+1..+3 of the panel buffer stay zero
+    const bool ok = chol_factor_tiles(S, kt, tid, nthr, bar);   // starts with a barrier
     if (!ok) {
         if (tid == 0 && a.status) {
             if (atomicAdd(&a.status[0], 1) == 0) a.status[1] = (int32_t)r;
@@ -100,8 +322,8 @@ __device__ __forceinline__ void row_epilogue(float* __restrict__ G, const float*
     if (a.mode == B200ALS_STEP_FACTOR) {
         float* Lo = a.chol_out + (size_t)r * k * k;
         for (int e = tid; e < k * k; e += nthr) {
-            int i = e / k, j = e - i * k;
-            Lo[e] = (j <= i) ? G[i * LD + j] : 0.0f;
+            const int i = e / k, j = e - i * k;
+            Lo[e] = (j <= i) ? Gt[tile_off(i >> 2, j >> 2) + (i & 3) * 4 + (j & 3)] : 0.0f;
         }
         float* ao = a.aux_out + (size_t)r * (2 * k + 2);
         for (int i = tid; i < k; i += nthr) {
@@ -114,18 +336,14 @@ __device__ __forceinline__ void row_epilogue(float* __restrict__ G, const float*
         }
         return;
     }
-    chol_backsolve_smem<KP>(G, k, tid, nthr);
-    const float* x = G + KP * LD;
-    // bias_own = (t - s·x) / (cnt + lam_bias)        (als.py:431-433, 464-466)
-    float part = 0.0f;
-    for (int i = tid; i < k; i += nthr) part += s_s[i] * x[i];
-    part = warp_sum(part);
-    if ((tid & 31) == 0) red_s[tid >> 5] = part;
-    __syncthreads();
-    if (tid == 0) {
-        float dot = 0.0f;
-        for (int w = 0; w < (nthr >> 5); ++w) dot += red_s[w];
-        a.bias_own[r] = (t_sum - dot) / ((float)cnt + a.lam_bias);
+    chol_backsolve_tiles(S, kt, tid, nthr, bar);
+    const float* x = S.x;
+    // bias_own = (t - s·x) / (cnt + lam_bias)        (als.py:431-433, 464-466); first warp reduces
+    if (tid < 32) {
+        float part = 0.0f;
+        for (int i = tid; i < k; i += 32) part = fmaf(s_s[i], x[i], part);
+        part = warp_sum(part);
+        if (tid == 0) a.bias_own[r] = (t_sum - part) / ((float)cnt + a.lam_bias);
     }
     float* xo = a.X + (size_t)r * a.ldx;
     for (int i = tid; i < k; i += nthr) xo[i] = x[i];

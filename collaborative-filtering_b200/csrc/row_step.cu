@@ -105,12 +105,11 @@ using namespace b200als;
 
 extern "C" {
 
-int b200als_step_workspace_bytes(int32_t k, int32_t path, int64_t n_list, size_t* bytes_host) {
+int b200als_step_workspace_bytes(int32_t k, int32_t path, int64_t n_f_rows, size_t* bytes_host) {
     ALS_CHECK_ARG(bytes_host, "null");
     ALS_CHECK_ARG(k >= 1 && k <= B200ALS_MAX_K, "k out of range");
-    (void)path;
-    (void)n_list;
-    *bytes_host = umma_workspace_bytes(k, n_list);
+    ALS_CHECK_ARG(n_f_rows >= 0, "negative row count");
+    *bytes_host = (path == B200ALS_PATH_FFMA) ? 256 : umma_workspace_bytes(k, n_f_rows);
     return B200ALS_OK;
 }
 
@@ -129,8 +128,14 @@ int b200als_row_step(const b200als_step_args* a, b200als_stream_t stream) {
     } else {
         ALS_CHECK_ARG(false, "unknown mode");
     }
-    size_t need = 0;
-    b200als_step_workspace_bytes(a->k, a->path, a->n_list, &need);
+    int path = a->path;
+    if (path == B200ALS_PATH_AUTO)
+        path = umma_supported(a->k, a->ldf) ? B200ALS_PATH_UMMA : B200ALS_PATH_FFMA;
+    size_t need = 256;
+    if (path == B200ALS_PATH_UMMA) {
+        ALS_CHECK_ARG(a->n_f_rows > 0, "n_f_rows must be set for the tcgen05 path");
+        need = umma_workspace_bytes(a->k, a->n_f_rows);
+    }
     if (!a->workspace || a->workspace_bytes < need) {
         set_error("b200als_row_step: workspace %zu < required %zu", a->workspace_bytes, need);
         return B200ALS_E_WORKSPACE;
@@ -147,16 +152,13 @@ int b200als_row_step(const b200als_step_args* a, b200als_stream_t stream) {
     p.cursor = reinterpret_cast<unsigned long long*>(a->workspace);
     ALS_CUDA(cudaMemsetAsync(a->workspace, 0, 256, s));
 
-    int path = a->path;
-    if (path == B200ALS_PATH_AUTO)
-        path = umma_supported(a->k, a->ldf) ? B200ALS_PATH_UMMA : B200ALS_PATH_FFMA;
     if (path == B200ALS_PATH_UMMA) {
         if (!umma_supported(a->k, a->ldf)) {
             set_error("b200als_row_step: tcgen05 path needs k in {64,128} and ldf == k (got k=%d ldf=%lld)", a->k,
                       (long long)a->ldf);
             return B200ALS_E_UNSUPPORTED;
         }
-        return launch_umma(p, static_cast<char*>(a->workspace) + 256, a->workspace_bytes - 256, s);
+        return launch_umma(p, a->n_f_rows, static_cast<char*>(a->workspace) + 256, a->workspace_bytes - 256, s);
     }
     return dispatch_ffma(p, s);
 }

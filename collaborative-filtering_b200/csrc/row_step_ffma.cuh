@@ -15,7 +15,7 @@ namespace b200als {
 
 constexpr int FF_TR = 16;       // ratings per pipeline tile
 constexpr int FF_STAGES = 3;
-constexpr int FF_CHUNK = 512;   // ratings whose (idx, q) are staged at once
+constexpr int FF_CHUNK = 256;   // ratings whose (idx, q) are staged at once
 
 struct RowStepParams {
     int k;
@@ -43,10 +43,9 @@ struct FfmaCfg {
     static constexpr int NLOW = NT * (NT + 1) / 2;
     static constexpr int THREADS = (round_up(NLOW, 32) > round_up(KP, 32)) ? round_up(NLOW, 32) : round_up(KP, 32);
     static constexpr int LDT = KP + 4;   // tile row stride (floats): 16B aligned, staggers banks
-    static constexpr int LDG = KP + 1;
     static constexpr size_t smem_bytes =
-        sizeof(float) * ((size_t)FF_STAGES * FF_TR * LDT     // tiles
-                         + (size_t)(KP + 1) * LDG            // G + rhs row
+        sizeof(float) * ((size_t)FF_STAGES * FF_TR * LDT     // gather ring
+                         + solve_smem_floats(KP)             // tile-format Gram + solver scratch
                          + 2 * KP                            // c, s
                          + 2 * FF_CHUNK                      // q ring (2 chunks)
                          + 32)                               // reductions
@@ -58,11 +57,11 @@ __global__ void __launch_bounds__(FfmaCfg<KP, T>::THREADS) row_step_ffma_kernel(
     using C = FfmaCfg<KP, T>;
     constexpr int NTHR = C::THREADS;
     constexpr int LDT = C::LDT;
-    constexpr int LDG = C::LDG;
     extern __shared__ __align__(16) unsigned char smem_raw[];
     float* tiles = reinterpret_cast<float*>(smem_raw);
-    float* G = tiles + FF_STAGES * FF_TR * LDT;
-    float* c_s = G + (KP + 1) * LDG;
+    SolveSmem S;
+    S.carve<KP>(tiles + FF_STAGES * FF_TR * LDT);
+    float* c_s = tiles + FF_STAGES * FF_TR * LDT + solve_smem_floats(KP);
     float* s_s = c_s + KP;
     float* q_s = s_s + KP;                 // [2][FF_CHUNK]
     float* red_s = q_s + 2 * FF_CHUNK;     // [32]
@@ -219,13 +218,23 @@ __global__ void __launch_bounds__(FfmaCfg<KP, T>::THREADS) row_step_ffma_kernel(
         // note: q ring entries past cnt in the last chunk are zero only for chunk 0's
         // staging and the publish above (both write all FF_CHUNK entries).
 
-        // ---- epilogue: lower triangle → smem, solve -------------------------
+        // ---- epilogue: lower triangle → 4x4 tiles in smem, solve ---------------
         __syncthreads();
+        const int kt = (k + 3) >> 2;
         if (has_tile) {
 #pragma unroll
-            for (int a = 0; a < T; ++a)
+            for (int a = 0; a < T / 4; ++a)
 #pragma unroll
-                for (int b = 0; b < T; ++b) G[(ti * T + a) * LDG + tj * T + b] = acc[a][b];
+                for (int b = 0; b < T / 4; ++b) {
+                    const int sti = ti * (T / 4) + a, stj = tj * (T / 4) + b;
+                    if (stj <= sti && sti < kt) {
+                        float4* dst = reinterpret_cast<float4*>(S.Gt + tile_off(sti, stj));
+#pragma unroll
+                        for (int rr = 0; rr < 4; ++rr)
+                            dst[rr] = make_float4(acc[a * 4 + rr][b * 4 + 0], acc[a * 4 + rr][b * 4 + 1],
+                                                  acc[a * 4 + rr][b * 4 + 2], acc[a * 4 + rr][b * 4 + 3]);
+                    }
+                }
         }
         if (tid < KP) { c_s[tid] = c_acc; s_s[tid] = s_acc; }
         if (tid == 0) red_s[31] = t_acc;
@@ -237,7 +246,7 @@ __global__ void __launch_bounds__(FfmaCfg<KP, T>::THREADS) row_step_ffma_kernel(
         ea.X = p.X; ea.ldx = p.ldx; ea.bias_own = p.bias_own;
         ea.chol_out = p.chol_out; ea.aux_out = p.aux_out; ea.status = p.status;
         const float t_sum = red_s[31];
-        row_epilogue<KP>(G, c_s, s_s, t_sum, cnt, r, ea, tid, NTHR, misc_s, red_s);
+        row_epilogue_tiles(S, c_s, s_s, t_sum, cnt, r, ea, tid, NTHR, 1);
     }
 }
 

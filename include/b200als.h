@@ -31,7 +31,7 @@
 extern "C" {
 #endif
 
-#define B200ALS_ABI_VERSION 3
+#define B200ALS_ABI_VERSION 4
 
 #define B200ALS_OK            0
 #define B200ALS_E_INVALID    -1   /* bad argument */
@@ -147,6 +147,7 @@ typedef struct b200als_step_args {
     const int32_t* rows;         /* optional row list (e.g. b200als_row_order output) */
     int64_t  n_list;             /* entries of rows[] to process (or n_rows if rows==NULL) */
     const float* F;  int64_t ldf;
+    int64_t  n_f_rows;           /* rows of F (every index < n_f_rows); sizes the tcgen05 path's bf16 copy */
     const float* bias_other;
     const float* mu;             /* device scalar */
     float  reg;        const float* reg_row;
@@ -159,7 +160,8 @@ typedef struct b200als_step_args {
     void*  workspace; size_t workspace_bytes;   /* see b200als_step_workspace_bytes */
 } b200als_step_args;
 
-int b200als_step_workspace_bytes(int32_t k, int32_t path, int64_t n_list, size_t* bytes_host);
+/* workspace for one b200als_row_step call gathering from an F of n_f_rows rows */
+int b200als_step_workspace_bytes(int32_t k, int32_t path, int64_t n_f_rows, size_t* bytes_host);
 int b200als_row_step(const b200als_step_args* args_host, b200als_stream_t stream);
 /* Number of kernel launches the last b200als_row_step on this thread issued. */
 int b200als_last_launch_count(void);
