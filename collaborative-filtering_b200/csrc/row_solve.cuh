@@ -27,12 +27,28 @@ namespace b200als {
 constexpr int SOLVE_NB = 8;
 
 __host__ __device__ constexpr int tri_tiles(int kt) { return (kt + 1) * (kt + 2) / 2; }   // incl. rhs tile row
+// tiles are stored in groups of 8: [group][row 0..3][tile 0..7][4 floats], so that row r of 8
+// consecutive tiles is one 128-byte line (conflict-free LDS.128 for thread-per-tile loops)
+__host__ __device__ constexpr int tile_store_floats(int kt) { return ((tri_tiles(kt) + 7) / 8) * 128; }
 __host__ __device__ constexpr size_t solve_smem_floats(int KP) {
-    // tiles (+rhs tile row) + panel buffer Lp[(KP+4)][8] + Ld[64] + invd[KP+4] + x[KP+4] + 8 misc
-    return (size_t)tri_tiles(KP / 4) * 16 + (size_t)(KP + 4) * SOLVE_NB + 64 + 2 * (KP + 4) + 8;
+    // tiles (+rhs tile row) + panel buffer Lp[8][KP/4+1][4] + Ld[64] + invd[KP+4] + x[KP+4] + 8 misc
+    return (size_t)tile_store_floats(KP / 4) + (size_t)(KP + 4) * SOLVE_NB + 64 + 2 * (KP + 4) + 8;
 }
 
-__device__ __forceinline__ int tile_off(int ti, int tj) { return ((ti * (ti + 1)) / 2 + tj) * 16; }
+__device__ __forceinline__ int tile_base(int ti, int tj) {
+    const int T = (ti * (ti + 1)) / 2 + tj;
+    return ((T >> 3) << 7) + ((T & 7) << 2);
+}
+__device__ __forceinline__ float4* tile_row(float* Gt, int ti, int tj, int r) {
+    return reinterpret_cast<float4*>(Gt + tile_base(ti, tj) + (r << 5));
+}
+__device__ __forceinline__ float* tile_elem(float* Gt, int i, int j) {     // i >= j
+    return Gt + tile_base(i >> 2, j >> 2) + ((i & 3) << 5) + (j & 3);
+}
+// panel buffer: Lp[h][r][t] (float4) = entries 4h..4h+3 of the panel row 4t+r
+__device__ __forceinline__ float4* lp_vec(float* Lp, int NTP, int t, int r, int h) {
+    return reinterpret_cast<float4*>(Lp) + ((h * 4 + r) * NTP + t);
+}
 
 // barrier among the `nthr` threads that solve one matrix: a named barrier, or just the warp
 __device__ __forceinline__ void bar_sync(int id, int nthr) {
@@ -50,7 +66,8 @@ __device__ __forceinline__ void tri_decode(int q, int& a, int& b) {
 
 struct SolveSmem {
     float* Gt;     // tiles
-    float* Lp;     // [(KP+4)][8] current panel, by global row
+    float* Lp;     // current panel, [half][row in tile][tile row] float4 (see lp_vec)
+    int NTP;       // tile rows in Lp (= KP/4 + 1)
     float* Ld;     // [8][8] diagonal block of the current panel
     float* invd;   // [KP+4] 1 / L[j][j]
     float* x;      // [KP+4] solution / scratch
@@ -58,7 +75,8 @@ struct SolveSmem {
     template <int KP>
     __device__ __forceinline__ void carve(float* base) {
         Gt = base;
-        Lp = Gt + tri_tiles(KP / 4) * 16;
+        NTP = KP / 4 + 1;
+        Lp = Gt + tile_store_floats(KP / 4);
         Ld = Lp + (KP + 4) * SOLVE_NB;
         invd = Ld + 64;
         x = invd + (KP + 4);
@@ -85,18 +103,15 @@ __device__ __forceinline__ bool chol_factor_tiles(const SolveSmem& S, int kt, in
 #pragma unroll
                 for (int c = 0; c < 8; ++c) a[r][c] = (r == c) ? 1.0f : 0.0f;
             {
-                const float4* t00 = reinterpret_cast<const float4*>(Gt + tile_off(tc0, tc0));
 #pragma unroll
                 for (int r = 0; r < 4; ++r) {
-                    float4 v = t00[r];
+                    float4 v = *tile_row(Gt, tc0, tc0, r);
                     a[r][0] = v.x; a[r][1] = v.y; a[r][2] = v.z; a[r][3] = v.w;
                 }
                 if (ntc == 2) {
-                    const float4* t10 = reinterpret_cast<const float4*>(Gt + tile_off(tc0 + 1, tc0));
-                    const float4* t11 = reinterpret_cast<const float4*>(Gt + tile_off(tc0 + 1, tc0 + 1));
 #pragma unroll
                     for (int r = 0; r < 4; ++r) {
-                        float4 v = t10[r], w = t11[r];
+                        float4 v = *tile_row(Gt, tc0 + 1, tc0, r), w = *tile_row(Gt, tc0 + 1, tc0 + 1, r);
                         a[4 + r][0] = v.x; a[4 + r][1] = v.y; a[4 + r][2] = v.z; a[4 + r][3] = v.w;
                         a[4 + r][4] = w.x; a[4 + r][5] = w.y; a[4 + r][6] = w.z; a[4 + r][7] = w.w;
                     }
@@ -121,16 +136,13 @@ __device__ __forceinline__ bool chol_factor_tiles(const SolveSmem& S, int kt, in
             }
             if (!ok) *S.flag = 1;
             // write back: tiles, Ld (row-major 8x8, strictly-lower + diag), invd
-            float4* t00 = reinterpret_cast<float4*>(Gt + tile_off(tc0, tc0));
 #pragma unroll
-            for (int r = 0; r < 4; ++r) t00[r] = make_float4(a[r][0], a[r][1], a[r][2], a[r][3]);
+            for (int r = 0; r < 4; ++r) *tile_row(Gt, tc0, tc0, r) = make_float4(a[r][0], a[r][1], a[r][2], a[r][3]);
             if (ntc == 2) {
-                float4* t10 = reinterpret_cast<float4*>(Gt + tile_off(tc0 + 1, tc0));
-                float4* t11 = reinterpret_cast<float4*>(Gt + tile_off(tc0 + 1, tc0 + 1));
 #pragma unroll
                 for (int r = 0; r < 4; ++r) {
-                    t10[r] = make_float4(a[4 + r][0], a[4 + r][1], a[4 + r][2], a[4 + r][3]);
-                    t11[r] = make_float4(a[4 + r][4], a[4 + r][5], a[4 + r][6], a[4 + r][7]);
+                    *tile_row(Gt, tc0 + 1, tc0, r) = make_float4(a[4 + r][0], a[4 + r][1], a[4 + r][2], a[4 + r][3]);
+                    *tile_row(Gt, tc0 + 1, tc0 + 1, r) = make_float4(a[4 + r][4], a[4 + r][5], a[4 + r][6], a[4 + r][7]);
                 }
             }
 #pragma unroll
@@ -143,13 +155,14 @@ __device__ __forceinline__ bool chol_factor_tiles(const SolveSmem& S, int kt, in
         bar_sync(bar, nthr);
         if (*S.flag) break;
         // ---- (b) panel rows below the block (+ rhs row): a <- a * Ld^-T ------------------
-        const int row0 = (tc0 + ntc) * 4;
-        const int nrows = (kt * 4 - row0) + 1;            // + the rhs row (tile row kt, local row 0)
-        for (int t = tid; t < nrows; t += nthr) {
-            const int i = row0 + t;                        // i == kt*4 → rhs row
-            const int ti = i >> 2, li = i & 3;
-            float4* p0 = reinterpret_cast<float4*>(Gt + tile_off(ti, tc0) + li * 4);
-            float4* p1 = reinterpret_cast<float4*>(Gt + tile_off(ti, tc0 + 1) + li * 4);
+        const int tr0 = tc0 + ntc;                        // first tile row below the block
+        const int ntr = kt - tr0 + 1;                      // tile rows incl. the rhs tile row (only its row 0 is real)
+        for (int t = tid; t < ntr * 4; t += nthr) {
+            // lanes walk tile rows first (same row-in-tile), so panel-buffer stores are contiguous
+            const int ti = tr0 + (t % ntr), li = t / ntr;
+            if (ti == kt && li != 0) continue;
+            float4* p0 = tile_row(Gt, ti, tc0, li);
+            float4* p1 = tile_row(Gt, ti, tc0 + 1, li);
             float a[8];
             {
                 float4 v = *p0;
@@ -166,8 +179,8 @@ __device__ __forceinline__ bool chol_factor_tiles(const SolveSmem& S, int kt, in
             }
             *p0 = make_float4(a[0], a[1], a[2], a[3]);
             if (ntc == 2) *p1 = make_float4(a[4], a[5], a[6], a[7]);
-            reinterpret_cast<float4*>(Lp + i * 8)[0] = make_float4(a[0], a[1], a[2], a[3]);
-            reinterpret_cast<float4*>(Lp + i * 8)[1] = make_float4(a[4], a[5], a[6], a[7]);
+            *lp_vec(Lp, S.NTP, ti, li, 0) = make_float4(a[0], a[1], a[2], a[3]);
+            *lp_vec(Lp, S.NTP, ti, li, 1) = make_float4(a[4], a[5], a[6], a[7]);
         }
         bar_sync(bar, nthr);
         // ---- (c) trailing update: tile(ti,tj) -= Lp[ti rows] * Lp[tj rows]^T ---------------
@@ -184,17 +197,15 @@ __device__ __forceinline__ bool chol_factor_tiles(const SolveSmem& S, int kt, in
             } else {
                 ti = kt; tj = ta0 + (q - ntri);
             }
-            float4* tp = reinterpret_cast<float4*>(Gt + tile_off(ti, tj));
+            float* tb = Gt + tile_base(ti, tj);
             float4 acc[4];
 #pragma unroll
-            for (int r = 0; r < 4; ++r) acc[r] = tp[r];
-            const float4* lr = reinterpret_cast<const float4*>(Lp + ti * 32);
-            const float4* lc = reinterpret_cast<const float4*>(Lp + tj * 32);
+            for (int r = 0; r < 4; ++r) acc[r] = *reinterpret_cast<float4*>(tb + (r << 5));
 #pragma unroll
             for (int h = 0; h < 2; ++h) {                 // two halves of the 8-wide panel
                 float4 rr[4], cc[4];
 #pragma unroll
-                for (int r = 0; r < 4; ++r) { rr[r] = lr[r * 2 + h]; cc[r] = lc[r * 2 + h]; }
+                for (int r = 0; r < 4; ++r) { rr[r] = *lp_vec(Lp, S.NTP, ti, r, h); cc[r] = *lp_vec(Lp, S.NTP, tj, r, h); }
 #pragma unroll
                 for (int r = 0; r < 4; ++r) {
                     const float4 a4 = rr[r];
@@ -205,7 +216,7 @@ __device__ __forceinline__ bool chol_factor_tiles(const SolveSmem& S, int kt, in
                 }
             }
 #pragma unroll
-            for (int r = 0; r < 4; ++r) tp[r] = acc[r];
+            for (int r = 0; r < 4; ++r) *reinterpret_cast<float4*>(tb + (r << 5)) = acc[r];
         }
     }
     bar_sync(bar, nthr);
@@ -216,7 +227,7 @@ __device__ __forceinline__ bool chol_factor_tiles(const SolveSmem& S, int kt, in
 __device__ __forceinline__ void chol_backsolve_tiles(const SolveSmem& S, int kt, int tid, int nthr, int bar) {
     float* __restrict__ Gt = S.Gt;
     float* __restrict__ x = S.x;
-    for (int j = tid; j < kt * 4; j += nthr) x[j] = Gt[tile_off(kt, j >> 2) + (j & 3)];
+    for (int j = tid; j < kt * 4; j += nthr) x[j] = Gt[tile_base(kt, j >> 2) + (j & 3)];
     const int last_tc0 = ((kt - 1) >> 1) << 1;
     for (int tc0 = last_tc0; tc0 >= 0; tc0 -= 2) {
         const int ntc = (kt - tc0) >= 2 ? 2 : 1;
@@ -229,10 +240,9 @@ __device__ __forceinline__ void chol_backsolve_tiles(const SolveSmem& S, int kt,
             for (int r = 0; r < 8; ++r)
 #pragma unroll
                 for (int c = 0; c < 8; ++c) l[r][c] = 0.0f;
-            const float4* t00 = reinterpret_cast<const float4*>(Gt + tile_off(tc0, tc0));
 #pragma unroll
             for (int r = 0; r < 4; ++r) {
-                float4 v = t00[r];
+                float4 v = *tile_row(Gt, tc0, tc0, r);
                 l[r][0] = v.x; l[r][1] = v.y; l[r][2] = v.z; l[r][3] = v.w;
             }
             float y[8];
@@ -241,11 +251,9 @@ __device__ __forceinline__ void chol_backsolve_tiles(const SolveSmem& S, int kt,
 #pragma unroll
             for (int r = 0; r < 4; ++r) y[r] = x[tc0 * 4 + r];
             if (ntc == 2) {
-                const float4* t10 = reinterpret_cast<const float4*>(Gt + tile_off(tc0 + 1, tc0));
-                const float4* t11 = reinterpret_cast<const float4*>(Gt + tile_off(tc0 + 1, tc0 + 1));
 #pragma unroll
                 for (int r = 0; r < 4; ++r) {
-                    float4 v = t10[r], w = t11[r];
+                    float4 v = *tile_row(Gt, tc0 + 1, tc0, r), w = *tile_row(Gt, tc0 + 1, tc0 + 1, r);
                     l[4 + r][0] = v.x; l[4 + r][1] = v.y; l[4 + r][2] = v.z; l[4 + r][3] = v.w;
                     l[4 + r][4] = w.x; l[4 + r][5] = w.y; l[4 + r][6] = w.z; l[4 + r][7] = w.w;
                     y[4 + r] = x[tc0 * 4 + 4 + r];
@@ -273,7 +281,7 @@ __device__ __forceinline__ void chol_backsolve_tiles(const SolveSmem& S, int kt,
             for (int c = 0; c < 8; ++c) {
                 if (c < nb) {
                     const int row = tc0 * 4 + c;
-                    acc = fmaf(-Gt[tile_off(row >> 2, tj) + (row & 3) * 4 + lj], x[row], acc);
+                    acc = fmaf(-Gt[tile_base(row >> 2, tj) + ((row & 3) << 5) + lj], x[row], acc);
                 }
             }
             x[i] = acc;
@@ -305,13 +313,13 @@ __device__ __forceinline__ void row_epilogue_tiles(const SolveSmem& S, const flo
     const float bias_old = a.bias_own[r];
     // ridge on the diagonal; identity on padded rows; rhs tile row
     for (int i = tid; i < kt * 4; i += nthr) {
-        float* d = Gt + tile_off(i >> 2, i >> 2) + (i & 3) * 5;
+        float* d = tile_elem(Gt, i, i);
         *d = (i < k) ? *d + a.reg : 1.0f;
-        float* rt = Gt + tile_off(kt, i >> 2);
-        rt[i & 3] = (i < k) ? c_s[i] - bias_old * s_s[i] : 0.0f;
-        rt[4 + (i & 3)] = 0.0f; rt[8 + (i & 3)] = 0.0f; rt[12 + (i & 3)] = 0.0f;
+        float* rt = Gt + tile_base(kt, i >> 2) + (i & 3);
+        rt[0] = (i < k) ? c_s[i] - bias_old * s_s[i] : 0.0f;
+        rt[32] = 0.0f; rt[64] = 0.0f; rt[96] = 0.0f;
     }
-    if (tid < 24) S.Lp[(kt * 4 + 1) * 8 + tid] = 0.0f;       // rows kt*4+1..+3 of the panel buffer stay zero
+    if (tid < 6) *lp_vec(S.Lp, S.NTP, kt, 1 + (tid >> 1), tid & 1) = make_float4(0.f, 0.f, 0.f, 0.f);   // rows 1..3 of the rhs tile row stay zero
     const bool ok = chol_factor_tiles(S, kt, tid, nthr, bar);   // starts with a barrier
     if (!ok) {
         if (tid == 0 && a.status) {
@@ -323,7 +331,7 @@ __device__ __forceinline__ void row_epilogue_tiles(const SolveSmem& S, const flo
         float* Lo = a.chol_out + (size_t)r * k * k;
         for (int e = tid; e < k * k; e += nthr) {
             const int i = e / k, j = e - i * k;
-            Lo[e] = (j <= i) ? Gt[tile_off(i >> 2, j >> 2) + (i & 3) * 4 + (j & 3)] : 0.0f;
+            Lo[e] = (j <= i) ? *tile_elem(Gt, i, j) : 0.0f;
         }
         float* ao = a.aux_out + (size_t)r * (2 * k + 2);
         for (int i = tid; i < k; i += nthr) {

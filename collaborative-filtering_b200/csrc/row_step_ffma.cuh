@@ -228,10 +228,9 @@ __global__ void __launch_bounds__(FfmaCfg<KP, T>::THREADS) row_step_ffma_kernel(
                 for (int b = 0; b < T / 4; ++b) {
                     const int sti = ti * (T / 4) + a, stj = tj * (T / 4) + b;
                     if (stj <= sti && sti < kt) {
-                        float4* dst = reinterpret_cast<float4*>(S.Gt + tile_off(sti, stj));
 #pragma unroll
                         for (int rr = 0; rr < 4; ++rr)
-                            dst[rr] = make_float4(acc[a * 4 + rr][b * 4 + 0], acc[a * 4 + rr][b * 4 + 1],
+                            *tile_row(S.Gt, sti, stj, rr) = make_float4(acc[a * 4 + rr][b * 4 + 0], acc[a * 4 + rr][b * 4 + 1],
                                                   acc[a * 4 + rr][b * 4 + 2], acc[a * 4 + rr][b * 4 + 3]);
                     }
                 }

@@ -37,13 +37,12 @@ struct UmmaCfg {
     static constexpr int REC_BYTES = 4 * K;                 // [hi | lo] bf16
     static constexpr int N_MB = REC_BYTES / 128;            // 128-byte atoms per record
     static constexpr int STAGE_DATA = UM_R * REC_BYTES;
-    static constexpr int STAGE_STRIDE = STAGE_DATA + 2048;  // + B2 (1 KB) + idx/val/bias (3 x 128 B)
-    static constexpr int OFF_B2 = STAGE_DATA;
-    static constexpr int OFF_IDX = STAGE_DATA + 1024;
-    static constexpr int OFF_VAL = OFF_IDX + 128;
-    static constexpr int OFF_BIAS = OFF_VAL + 128;
+    static constexpr int STAGE_STRIDE = STAGE_DATA;         // data ring (1024-byte aligned atoms)
+    static constexpr int B2_BYTES = 1024;                   // per stage: [q_hi,q_lo,1] operand, 32 ratings x 32 B
+    static constexpr int META = 32;                         // (index, rating) ring: runs far ahead of the data ring
+    static constexpr int META_BYTES = 256;                  // idx[32] int32 + val[32] float
     static constexpr int NG = 3;                            // solver groups (4 warps each)
-    static constexpr int STAGES = (K == 64) ? 6 : 5;
+    static constexpr int STAGES = 5;
     static constexpr int MATS = (K == 64) ? NG * 4 : NG;    // matrices being solved at once
     static constexpr int ACC_BUFS = (K == 64) ? 4 : 1;
     static constexpr int ACC_STRIDE = (K == 64) ? 128 : 512;  // TMEM columns per accumulator
@@ -55,9 +54,11 @@ struct UmmaCfg {
     static constexpr int WARP_MMA = SOLVER_WARPS + 1 + UM_GATHER_WARPS;
     static constexpr int THREADS = (WARP_MMA + 1) * 32;
     static constexpr size_t MAT_FLOATS = solve_smem_floats(K) + 2 * K;
-    static constexpr int NBAR = 3 * STAGES + 2 * ACC_BUFS + 2 * UM_RD;
-    static constexpr size_t smem_bytes = 1024 /*align slack*/ + (size_t)STAGES * STAGE_STRIDE +
+    static constexpr int NBAR = 2 * STAGES + 2 * META + MATS + ACC_BUFS + 2 * UM_RD;
+    static constexpr size_t smem_bytes = 1024 /*align slack*/ + (size_t)STAGES * (STAGE_STRIDE + B2_BYTES + 128) +
+                                         (size_t)META * META_BYTES +
                                          (size_t)MATS * MAT_FLOATS * 4 + (size_t)NBAR * 8 + UM_RD * 4 + 128;
+    static_assert(smem_bytes <= 232448, "tcgen05 Gram kernel exceeds 227 KB of shared memory");
 };
 
 // Warp-level walker over this CTA's rows: row(n) = rows[b + n*G]; bounds prefetched 32 rows at a time.
@@ -124,12 +125,14 @@ __global__ void __launch_bounds__(256) split_bf16_kernel(const float* __restrict
 }
 
 struct UmmaSmem {
-    unsigned char* stages;
+    unsigned char* stages;   // [STAGES][STAGE_DATA]
+    unsigned char* b2;       // [STAGES][1024]
+    unsigned char* bias;     // [STAGES][128]
+    unsigned char* meta;     // [META][256]
     float* mats;
-    uint64_t *meta_full, *full, *empty, *acc_full, *acc_empty, *rd_full, *rd_empty;
+    uint64_t *meta_full, *meta_empty, *full, *empty, *acc_full, *acc_empty, *rd_full, *rd_empty;
     float* tsum;
     uint32_t* tmem_base;
-    volatile int* seen;      // [ACC_BUFS] last row sequence whose acc_full phase a solver group has observed
 };
 
 template <int K>
@@ -137,18 +140,36 @@ __device__ __forceinline__ void umma_carve(unsigned char* raw, UmmaSmem& s) {
     using C = UmmaCfg<K>;
     unsigned char* base = reinterpret_cast<unsigned char*>((reinterpret_cast<uintptr_t>(raw) + 1023) & ~(uintptr_t)1023);
     s.stages = base;
-    s.mats = reinterpret_cast<float*>(base + (size_t)C::STAGES * C::STAGE_STRIDE);
+    s.b2 = s.stages + (size_t)C::STAGES * C::STAGE_STRIDE;
+    s.bias = s.b2 + (size_t)C::STAGES * C::B2_BYTES;
+    s.meta = s.bias + (size_t)C::STAGES * 128;
+    s.mats = reinterpret_cast<float*>(s.meta + (size_t)C::META * C::META_BYTES);
     uint64_t* bars = reinterpret_cast<uint64_t*>(s.mats + (size_t)C::MATS * C::MAT_FLOATS);
     s.meta_full = bars;
-    s.full = s.meta_full + C::STAGES;
+    s.meta_empty = s.meta_full + C::META;
+    s.full = s.meta_empty + C::META;
     s.empty = s.full + C::STAGES;
     s.acc_full = s.empty + C::STAGES;
-    s.acc_empty = s.acc_full + C::ACC_BUFS;
+    s.acc_empty = s.acc_full + C::MATS;
     s.rd_full = s.acc_empty + C::ACC_BUFS;
     s.rd_empty = s.rd_full + UM_RD;
     s.tsum = reinterpret_cast<float*>(s.rd_empty + UM_RD);
     s.tmem_base = reinterpret_cast<uint32_t*>(s.tsum + UM_RD);
-    s.seen = reinterpret_cast<volatile int*>(s.tmem_base + 1);
+}
+
+// acc_full is indexed by CONSUMER (solver group, matrix slot), not by TMEM buffer: every barrier then
+// has exactly one waiting group that sees its phases strictly in order, so the parity wait is exact
+// (indexing by buffer lets a group that is two uses behind mistake an old phase for the new one).
+template <int K>
+__device__ __forceinline__ void acc_full_slot(uint32_t me, uint32_t& bar_idx, uint32_t& parity) {
+    using C = UmmaCfg<K>;
+    if (K == 128) {
+        bar_idx = me % C::NG;
+        parity = (me / C::NG) & 1;
+    } else {
+        bar_idx = me % (4 * C::NG);           // group (me%12)/4, matrix (me%12)%4
+        parity = (me / (4 * C::NG)) & 1;
+    }
 }
 
 // ---- meta warp: (index, rating) streams of every stage → smem, fully asynchronous ----------
@@ -163,19 +184,19 @@ __device__ __forceinline__ void umma_role_meta(const RowStepParams& p, const Umm
     while (w.next(lane, beg, end, row)) {
         if (beg >= end) continue;
         for (int64_t t0 = beg; t0 < end; t0 += UM_R, ++sg) {
-            const uint32_t slot = sg % C::STAGES, ph = (sg / C::STAGES) & 1;
-            ptx::mbar_wait(&s.empty[slot], ph ^ 1, 1, (int)sg);
-            unsigned char* st = s.stages + (size_t)slot * C::STAGE_STRIDE;
+            const uint32_t ms = sg % C::META, mph = (sg / C::META) & 1;
+            ptx::mbar_wait(&s.meta_empty[ms], mph ^ 1, 1, (int)sg);
+            unsigned char* mt = s.meta + (size_t)ms * C::META_BYTES;
             const int64_t e = t0 + lane;
             const bool live = e < end;
             const int64_t es = live ? e : beg;         // any valid address for the zero-fill form
-            asm volatile("cp.async.ca.shared.global [%0], [%1], 4, %2;" ::"r"(ptx::smem_u32(st + C::OFF_IDX + lane * 4)),
+            asm volatile("cp.async.ca.shared.global [%0], [%1], 4, %2;" ::"r"(ptx::smem_u32(mt + lane * 4)),
                          "l"(p.indices + es), "r"(live ? 4u : 0u)
                          : "memory");
-            asm volatile("cp.async.ca.shared.global [%0], [%1], 4, %2;" ::"r"(ptx::smem_u32(st + C::OFF_VAL + lane * 4)),
+            asm volatile("cp.async.ca.shared.global [%0], [%1], 4, %2;" ::"r"(ptx::smem_u32(mt + 128 + lane * 4)),
                          "l"(p.vals + es), "r"(live ? 4u : 0u)
                          : "memory");
-            ptx::cp_async_mbar_arrive_noinc(&s.meta_full[slot]);
+            ptx::cp_async_mbar_arrive_noinc(&s.meta_full[ms]);
         }
     }
     cp_async_wait<0>();
@@ -198,9 +219,11 @@ __device__ __forceinline__ void umma_role_gather(const RowStepParams& p, const U
         if (beg >= end) continue;
         for (int64_t t0 = beg; t0 < end; t0 += UM_R, ++sg) {
             const uint32_t slot = sg % C::STAGES, ph = (sg / C::STAGES) & 1;
+            const uint32_t ms = sg % C::META, mph = (sg / C::META) & 1;
             unsigned char* st = s.stages + (size_t)slot * C::STAGE_STRIDE;
-            ptx::mbar_wait(&s.meta_full[slot], ph, 2, (int)sg);
-            const int32_t* idx_s = reinterpret_cast<const int32_t*>(st + C::OFF_IDX);
+            ptx::mbar_wait(&s.meta_full[ms], mph, 2, (int)sg);
+            ptx::mbar_wait(&s.empty[slot], ph ^ 1, 11, (int)sg);
+            const int32_t* idx_s = reinterpret_cast<const int32_t*>(s.meta + (size_t)ms * C::META_BYTES);
             const int live_n = (int)((end - t0) < UM_R ? (end - t0) : UM_R);
             const uint32_t st_addr = ptx::smem_u32(st);
 #pragma unroll
@@ -218,7 +241,7 @@ __device__ __forceinline__ void umma_role_gather(const RowStepParams& p, const U
             if (gtid < UM_R) {
                 const bool live = gtid < live_n;
                 const int32_t ix = idx_s[gtid];
-                asm volatile("cp.async.ca.shared.global [%0], [%1], 4, %2;" ::"r"(st_addr + C::OFF_BIAS + gtid * 4),
+                asm volatile("cp.async.ca.shared.global [%0], [%1], 4, %2;" ::"r"(ptx::smem_u32(s.bias + slot * 128 + gtid * 4)),
                              "l"(p.bias_other + ix), "r"(live ? 4u : 0u)
                              : "memory");
             }
@@ -256,12 +279,13 @@ __device__ __forceinline__ void umma_role_mma(const RowStepParams& p, const Umma
         for (int64_t t0 = beg; t0 < end; t0 += UM_R, ++sg) {
             const uint32_t slot = sg % C::STAGES, ph = (sg / C::STAGES) & 1;
             unsigned char* st = s.stages + (size_t)slot * C::STAGE_STRIDE;
-            ptx::mbar_wait(&s.meta_full[slot], ph, 4, (int)sg);
+            const uint32_t ms = sg % C::META, mph = (sg / C::META) & 1;
+            ptx::mbar_wait(&s.meta_full[ms], mph, 4, (int)sg);
             ptx::mbar_wait(&s.full[slot], ph, 5, (int)sg);
             // the [q_hi, q_lo, 1] operand of this stage (no-swizzle MN-major: 8 ratings x 16 B core matrices)
             const bool live = (t0 + lane) < end;
-            const float v = reinterpret_cast<const float*>(st + C::OFF_VAL)[lane];
-            const float bo = reinterpret_cast<const float*>(st + C::OFF_BIAS)[lane];
+            const float v = reinterpret_cast<const float*>(s.meta + (size_t)ms * C::META_BYTES + 128)[lane];
+            const float bo = reinterpret_cast<const float*>(s.bias + slot * 128)[lane];
             const float q = live ? v - (mu + bo) : 0.0f;
             tsum += q;
             const __nv_bfloat16 qh = __float2bfloat16_rn(q);
@@ -272,15 +296,16 @@ __device__ __forceinline__ void umma_role_mma(const RowStepParams& p, const Umma
             c0.x = *reinterpret_cast<const uint32_t*>(&w0);
             c0.y = *reinterpret_cast<const uint32_t*>(&w1);
             c0.z = 0u; c0.w = 0u;
-            unsigned char* b2 = st + C::OFF_B2 + (lane >> 3) * 256 + (lane & 7) * 16;
+            unsigned char* b2 = s.b2 + (size_t)slot * C::B2_BYTES + (lane >> 3) * 256 + (lane & 7) * 16;
             *reinterpret_cast<uint4*>(b2) = c0;                          // columns 0..7
             *reinterpret_cast<uint4*>(b2 + 128) = make_uint4(0u, 0u, 0u, 0u);   // columns 8..15
             ptx::fence_proxy_async();
             __syncwarp();
             ptx::tc_fence_after();
             if (lane == 0) {
+                ptx::mbar_arrive(&s.meta_empty[ms]);                     // idx (gather) and val (this warp) consumed
                 const uint32_t sa = ptx::smem_u32(st);
-                const uint32_t sb2 = sa + C::OFF_B2;
+                const uint32_t sb2 = ptx::smem_u32(s.b2 + (size_t)slot * C::B2_BYTES);
 #pragma unroll
                 for (int ks = 0; ks < UM_R / 16; ++ks) {
                     const uint32_t a_addr = sa + ks * 2 * SBO;
@@ -296,7 +321,11 @@ __device__ __forceinline__ void umma_role_mma(const RowStepParams& p, const Umma
                     }
                 }
                 ptx::umma_commit(&s.empty[slot]);                        // stage reusable once these MMAs finish
-                if (t0 + UM_R >= end) ptx::umma_commit(&s.acc_full[buf]);
+                if (t0 + UM_R >= end) {
+                    uint32_t fb, fp;
+                    acc_full_slot<K>(nrow, fb, fp);
+                    ptx::umma_commit(&s.acc_full[fb]);
+                }
             }
             __syncwarp();
             first = false;
@@ -314,10 +343,6 @@ __device__ __forceinline__ void umma_role_mma(const RowStepParams& p, const Umma
 }
 
 // ---- solver groups ----------------------------------------------------------------------------
-// Scatter one accumulator row chunk into the lower-triangle tiles.
-__device__ __forceinline__ float* tile_elem(float* Gt, int i, int j) {     // i >= j
-    return Gt + tile_off(i >> 2, j >> 2) + (i & 3) * 4 + (j & 3);
-}
 
 // k = 64: accumulator rows 0..63 = P = hi^T hi, rows 64..127 = Q^T = lo^T hi.  A = P + Q^T + Q.
 // Called by the 4 warps of a group (wq = warp in group = TMEM lane quadrant).
@@ -400,34 +425,6 @@ __device__ __forceinline__ void umma_drain128(uint32_t taddr_buf, float* Gt, flo
     }
 }
 
-// acc_full[buf] is consumed by different solver groups in turn, and an mbarrier wait only knows the
-// PARITY of a phase: a group that starts waiting for use j of a buffer while the barrier is still
-// two uses behind would see "complete".  So a group first waits until the previous use of the
-// buffer has been observed by its consumer (seen[buf] == me - ACC_BUFS); from then on the barrier
-// can only be in the phase of row `me`, and the parity wait is exact.
-template <int ACC_BUFS>
-__device__ __forceinline__ void wait_acc_full(const UmmaSmem& s, uint32_t me, int lane, int tag) {
-    const uint32_t buf = me % ACC_BUFS, aph = (me / ACC_BUFS) & 1;
-    if (me >= (uint32_t)ACC_BUFS) {
-        const int want = (int)me - ACC_BUFS;
-#ifdef B200ALS_WATCHDOG
-        const long long t0 = clock64();
-        while (s.seen[buf] < want) {
-            if (clock64() - t0 > 4000000000ll) {
-                if (lane == 0 && blockIdx.x < 2) printf("WATCHDOG blk %d warp %d seen[%u]=%d want %d\n", blockIdx.x, threadIdx.x >> 5, buf, s.seen[buf], want);
-                break;
-            }
-        }
-#else
-        while (s.seen[buf] < want) {
-        }
-#endif
-    }
-    ptx::mbar_wait(&s.acc_full[buf], aph, tag, (int)me);
-    __syncwarp();
-    if (lane == 0) s.seen[buf] = (int)me;     // every warp of the group stores the same value
-}
-
 template <int K>
 __device__ __forceinline__ void umma_role_solver(const RowStepParams& p, const UmmaSmem& s, int warp, int lane) {
     using C = UmmaCfg<K>;
@@ -456,8 +453,12 @@ __device__ __forceinline__ void umma_role_solver(const RowStepParams& p, const U
             if (beg >= end) continue;
             const uint32_t me = nrow++;
             if ((int)(me % C::NG) != g) continue;
-            const uint32_t buf = me % C::ACC_BUFS, aph = (me / C::ACC_BUFS) & 1;
-            wait_acc_full<C::ACC_BUFS>(s, me, lane, 7);
+            const uint32_t buf = me % C::ACC_BUFS;
+            {
+                uint32_t fb, fp;
+                acc_full_slot<K>(me, fb, fp);
+                ptx::mbar_wait(&s.acc_full[fb], fp, 7, (int)me);
+            }
             ptx::tc_fence_after();
             umma_drain128(tmem + buf * C::ACC_STRIDE, S.Gt, c_s, s_s, wq, lane, gbar);
             ptx::tc_fence_before();
@@ -492,8 +493,12 @@ __device__ __forceinline__ void umma_role_solver(const RowStepParams& p, const U
                 if (slot4 / 4 != g) continue;
                 const int j = slot4 & 3;                                 // matrix of warp j of this group
                 float* matj = s.mats + (size_t)(g * 4 + j) * C::MAT_FLOATS;
-                const uint32_t buf = me % C::ACC_BUFS, aph = (me / C::ACC_BUFS) & 1;
-                wait_acc_full<C::ACC_BUFS>(s, me, lane, 9);
+                const uint32_t buf = me % C::ACC_BUFS;
+                {
+                    uint32_t fb, fp;
+                    acc_full_slot<K>(me, fb, fp);
+                    ptx::mbar_wait(&s.acc_full[fb], fp, 9, (int)me);
+                }
                 ptx::tc_fence_after();
                 umma_drain64(tmem + buf * C::ACC_STRIDE, matj, matj + solve_smem_floats(K),
                              matj + solve_smem_floats(K) + K, wq, lane, gbar);
@@ -527,20 +532,20 @@ __global__ void __launch_bounds__(UmmaCfg<K>::THREADS, 1) row_step_umma_kernel(c
     const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
 
     if (threadIdx.x == 0) {
-        for (int i = 0; i < C::STAGES; ++i) {
+        for (int i = 0; i < C::META; ++i) {
             ptx::mbar_init(&s.meta_full[i], 32);
+            ptx::mbar_init(&s.meta_empty[i], 1);
+        }
+        for (int i = 0; i < C::STAGES; ++i) {
             ptx::mbar_init(&s.full[i], UM_GATHER_WARPS * 32);
             ptx::mbar_init(&s.empty[i], 1);
         }
-        for (int i = 0; i < C::ACC_BUFS; ++i) {
-            ptx::mbar_init(&s.acc_full[i], 1);
-            ptx::mbar_init(&s.acc_empty[i], 128);
-        }
+        for (int i = 0; i < C::MATS; ++i) ptx::mbar_init(&s.acc_full[i], 1);
+        for (int i = 0; i < C::ACC_BUFS; ++i) ptx::mbar_init(&s.acc_empty[i], 128);
         for (int i = 0; i < UM_RD; ++i) {
             ptx::mbar_init(&s.rd_full[i], 1);
             ptx::mbar_init(&s.rd_empty[i], 1);
         }
-        for (int i = 0; i < C::ACC_BUFS; ++i) s.seen[i] = -1;
         ptx::fence_barrier_init();
     }
     if (warp == C::WARP_MMA) ptx::tmem_alloc(s.tmem_base, 512);
