@@ -10,7 +10,7 @@ import os
 
 _HERE = os.path.dirname(os.path.abspath(__file__))
 LIB_PATH = os.path.join(_HERE, "libb200als.so")
-ABI_VERSION = 4
+ABI_VERSION = 5
 MAX_K = 160
 MAX_FEATURES = 8
 STATUS_WORDS = 4
@@ -40,7 +40,7 @@ class StepArgs(C.Structure):
         ("X", vp), ("ldx", C.c_int64),
         ("bias_own", vp),
         ("chol_out", vp), ("aux_out", vp),
-        ("status", vp),
+        ("status", vp), ("stats_acc", vp),
         ("workspace", vp), ("workspace_bytes", C.c_size_t),
     ]
 
@@ -69,6 +69,7 @@ _SIGNATURES = {
                                vp, vp, vp, vp],
     "b200als_sumsq": [vp, C.c_int64, C.c_int64, C.c_int64, vp, vp],
     "b200als_finalize_iter": [vp, C.c_int64, vp, vp, vp],
+    "b200als_finalize_iter_fused": [vp, C.c_int64, vp, vp, vp],
     "b200als_item_gram_f64": [C.c_int64, vp, vp, vp, C.c_int32, vp, C.c_int64, vp, vp, vp, vp, vp, vp],
     "b200als_wstep_system": [C.c_int64, C.c_int32, C.c_int32, vp, vp, vp, vp, C.c_int64,
                              C.c_double, vp, vp, vp],

@@ -417,6 +417,7 @@ class FitSession:
             self.wptr = (C.c_void_p * len(names))(*[w.data_ptr() for w in W_d])
             self.dims = (C.c_int32 * len(names))(*[int(x.shape[1]) for x in self.X_d])
         self.launches = 0
+        self.fused_stats = False
 
     # ---- small wrappers ---------------------------------------------------------
     def _stream(self):
@@ -429,7 +430,7 @@ class FitSession:
         self.launches += 1
 
     def _step(self, indptr, indices, vals, n_rows, rows, F, n_f_rows, bias_other, reg, reg_row, lamb, X, bias_own,
-              mode):
+              mode, stats=None):
         a = StepArgs()
         a.struct_bytes = C.sizeof(StepArgs)
         a.k, a.mode, a.path = self.k, mode, self.model.gram_path
@@ -445,6 +446,7 @@ class FitSession:
         a.chol_out = ptr(self.chol_d) if mode == _lib.STEP_FACTOR else None
         a.aux_out = ptr(self.aux_d) if mode == _lib.STEP_FACTOR else None
         a.status = ptr(self.status)
+        a.stats_acc = ptr(stats)
         a.workspace, a.workspace_bytes = ptr(self.ws), self.ws.numel()
         check(self.lib.b200als_row_step(C.byref(a), self._stream()), "row_step")
         self.launches += self.lib.b200als_last_launch_count() + 1      # + the cursor memset
@@ -495,8 +497,14 @@ class FitSession:
                     ptr(self.V_d), ld, ptr(self.b_i_d), stream), "graph_level_solve")
                 self.launches += 1
         else:
+            # A10 fused: with Z == V and no sweep after it, the item step sees every residual of
+            # the iteration's final state, so it accumulates sum d / sum d^2 itself
+            fused = self.fused_stats = not names
+            if fused:
+                self.acc.zero_()
             self._step(rt.cindptr, rt.cindices, rt.cvals, n, self.i_list, self.U_d, m, self.b_u_d, 0.0,
-                       self.reg_item_d, self.lam_bi, self.V_d, self.b_i_d, _lib.STEP_SOLVE)
+                       self.reg_item_d, self.lam_bi, self.V_d, self.b_i_d, _lib.STEP_SOLVE,
+                       stats=self.acc if fused else None)
             if shard.active:
                 shard.all_gather_rows(self.V_d, n)
                 shard.all_gather_rows(self.b_i_d, n)
@@ -525,12 +533,15 @@ class FitSession:
         if names:
             self._compose(self.Z_d)
         acc = self.acc
-        acc.zero_()
+        fused = (not self.use_graph) and self.fused_stats
         ulo, uhi = self.ulo, self.uhi
-        check(lib.b200als_residual_stats(uhi - ulo, rt.indptr.data_ptr() + 8 * ulo, ptr(rt.indices), ptr(rt.vals), k,
-                                         self.U_d.data_ptr() + 4 * ld * ulo, ld, ptr(self.Z_d), ld,
-                                         self.b_u_d.data_ptr() + 4 * ulo, ptr(self.b_i_d), ptr(acc), stream),
-              "residual_stats")
+        if not fused:
+            acc.zero_()
+            check(lib.b200als_residual_stats(uhi - ulo, rt.indptr.data_ptr() + 8 * ulo, ptr(rt.indices), ptr(rt.vals),
+                                             k, self.U_d.data_ptr() + 4 * ld * ulo, ld, ptr(self.Z_d), ld,
+                                             self.b_u_d.data_ptr() + 4 * ulo, ptr(self.b_i_d), ptr(acc), stream),
+                  "residual_stats")
+            self.launches += 1
         if shard.active:
             shard.all_reduce_sum(acc[:2])
         check(lib.b200als_sumsq(ptr(self.U_d), m, k, ld, acc.data_ptr() + 16, stream), "sumsq")
@@ -538,9 +549,9 @@ class FitSession:
         check(lib.b200als_sumsq(ptr(self.b_u_d), 1, m, m, acc.data_ptr() + 32, stream), "sumsq")
         check(lib.b200als_sumsq(ptr(self.b_i_d), 1, n, n, acc.data_ptr() + 40, stream), "sumsq")
         slot = it % self.hist.shape[0]
-        check(lib.b200als_finalize_iter(ptr(acc), rt.nnz, ptr(self.mu_d), self.hist.data_ptr() + 48 * slot, stream),
-              "finalize_iter")
-        self.launches += 6
+        fin = lib.b200als_finalize_iter_fused if fused else lib.b200als_finalize_iter
+        check(fin(ptr(acc), rt.nnz, ptr(self.mu_d), self.hist.data_ptr() + 48 * slot, stream), "finalize_iter")
+        self.launches += 5
         self._mark("end")
 
     # ---- host sync points -----------------------------------------------------------------

@@ -298,6 +298,8 @@ struct RowEpilogueArgs {
     float* bias_own;
     float* chol_out; float* aux_out;
     int32_t* status;
+    float qq;                     // sum q^2 of the row (fused residual statistics)
+    double* stats_d; double* stats_d2;   // thread-0 accumulators, may be null
 };
 
 // Preconditions: the lower-triangle tiles of F^T F are in S.Gt (tile rows 0..kt-1), c_s = F^T q
@@ -348,10 +350,28 @@ __device__ __forceinline__ void row_epilogue_tiles(const SolveSmem& S, const flo
     const float* x = S.x;
     // bias_own = (t - s·x) / (cnt + lam_bias)        (als.py:431-433, 464-466); first warp reduces
     if (tid < 32) {
-        float part = 0.0f;
-        for (int i = tid; i < k; i += 32) part = fmaf(s_s[i], x[i], part);
+        float part = 0.0f, cx = 0.0f, xx = 0.0f;
+        for (int i = tid; i < k; i += 32) {
+            part = fmaf(s_s[i], x[i], part);
+            cx = fmaf(c_s[i], x[i], cx);
+            xx = fmaf(x[i], x[i], xx);
+        }
         part = warp_sum(part);
-        if (tid == 0) a.bias_own[r] = (t_sum - part) / ((float)cnt + a.lam_bias);
+        cx = warp_sum(cx);
+        xx = warp_sum(xx);
+        if (tid == 0) {
+            const float fc = (float)cnt;
+            const float beta = (t_sum - part) / (fc + a.lam_bias);
+            a.bias_own[r] = beta;
+            if (a.stats_d) {
+                // d_e = q_e - beta - f_e.x over the row, from the quantities already at hand:
+                //   sum d^2 = qq - 2 beta t + cnt beta^2 - 2 (c.x - beta s.x) + x^T G x,
+                //   x^T G x = x.(c - beta_old s) - ridge x.x
+                *a.stats_d += (double)(t_sum - fc * beta - part);
+                *a.stats_d2 += (double)(a.qq - 2.0f * beta * t_sum + fc * beta * beta - cx +
+                                        (2.0f * beta - bias_old) * part - a.reg * xx);
+            }
+        }
     }
     float* xo = a.X + (size_t)r * a.ldx;
     for (int i = tid; i < k; i += nthr) xo[i] = x[i];

@@ -129,8 +129,9 @@ int b200als_row_step(const b200als_step_args* a, b200als_stream_t stream) {
         ALS_CHECK_ARG(false, "unknown mode");
     }
     int path = a->path;
-    if (path == B200ALS_PATH_AUTO)
-        path = umma_supported(a->k, a->ldf) ? B200ALS_PATH_UMMA : B200ALS_PATH_FFMA;
+    // FACTOR mode (graph sweep) stores the Cholesky factor from the tile solver: FFMA path only
+    if (path == B200ALS_PATH_AUTO || a->mode == B200ALS_STEP_FACTOR)
+        path = (a->mode == B200ALS_STEP_SOLVE && umma_supported(a->k, a->ldf)) ? B200ALS_PATH_UMMA : B200ALS_PATH_FFMA;
     size_t need = 256;
     if (path == B200ALS_PATH_UMMA) {
         ALS_CHECK_ARG(a->n_f_rows > 0, "n_f_rows must be set for the tcgen05 path");
@@ -149,6 +150,7 @@ int b200als_row_step(const b200als_step_args* a, b200als_stream_t stream) {
     p.reg = a->reg; p.reg_row = a->reg_row; p.lam_bias = a->lam_bias; p.lam_bias_row = a->lam_bias_row;
     p.X = a->X; p.ldx = a->ldx; p.bias_own = a->bias_own;
     p.chol_out = a->chol_out; p.aux_out = a->aux_out; p.status = a->status;
+    p.stats = (a->mode == B200ALS_STEP_SOLVE) ? a->stats_acc : nullptr;
     p.cursor = reinterpret_cast<unsigned long long*>(a->workspace);
     ALS_CUDA(cudaMemsetAsync(a->workspace, 0, 256, s));
 

@@ -34,6 +34,7 @@ struct RowStepParams {
     float* bias_own;
     float* chol_out; float* aux_out;
     int32_t* status;
+    double* stats;                // optional: [0] += sum d, [1] += sum d^2 over the rows solved (A10 fused)
     unsigned long long* cursor;   // zeroed before launch
 };
 
@@ -83,6 +84,7 @@ __global__ void __launch_bounds__(FfmaCfg<KP, T>::THREADS) row_step_ffma_kernel(
         while (ti * (ti + 1) / 2 > tid) --ti;
         tj = tid - ti * (ti + 1) / 2;
     }
+    double stat_d = 0.0, stat_d2 = 0.0;    // fused residual statistics (thread 0)
     // zero the tile ring once: columns [k4, KP) are never written by cp.async
     for (int e = tid; e < FF_STAGES * FF_TR * LDT; e += NTHR) tiles[e] = 0.0f;
 
@@ -105,7 +107,7 @@ __global__ void __launch_bounds__(FfmaCfg<KP, T>::THREADS) row_step_ffma_kernel(
         for (int a = 0; a < T; ++a)
 #pragma unroll
             for (int b = 0; b < T; ++b) acc[a][b] = 0.0f;
-        float c_acc = 0.0f, s_acc = 0.0f, t_acc = 0.0f;
+        float c_acc = 0.0f, s_acc = 0.0f, t_acc = 0.0f, qq_acc = 0.0f;
 
         const int64_t nchunks = (cnt + FF_CHUNK - 1) / FF_CHUNK;
         // stage chunk 0 meta
@@ -194,6 +196,7 @@ __global__ void __launch_bounds__(FfmaCfg<KP, T>::THREADS) row_step_ffma_kernel(
                         c_acc = fmaf(f, q, c_acc);
                         s_acc += f;
                         t_acc += q;
+                        qq_acc = fmaf(q, q, qq_acc);
                     }
                 }
             }
@@ -236,7 +239,7 @@ __global__ void __launch_bounds__(FfmaCfg<KP, T>::THREADS) row_step_ffma_kernel(
                 }
         }
         if (tid < KP) { c_s[tid] = c_acc; s_s[tid] = s_acc; }
-        if (tid == 0) red_s[31] = t_acc;
+        if (tid == 0) { red_s[31] = t_acc; red_s[30] = qq_acc; }
         __syncthreads();
         RowEpilogueArgs ea;
         ea.k = k; ea.mode = p.mode;
@@ -244,8 +247,14 @@ __global__ void __launch_bounds__(FfmaCfg<KP, T>::THREADS) row_step_ffma_kernel(
         ea.lam_bias = p.lam_bias_row ? p.lam_bias_row[r] : p.lam_bias;
         ea.X = p.X; ea.ldx = p.ldx; ea.bias_own = p.bias_own;
         ea.chol_out = p.chol_out; ea.aux_out = p.aux_out; ea.status = p.status;
+        ea.stats_d = &stat_d; ea.stats_d2 = &stat_d2;
         const float t_sum = red_s[31];
+        ea.qq = red_s[30];
         row_epilogue_tiles(S, c_s, s_s, t_sum, cnt, r, ea, tid, NTHR, 1);
+    }
+    if (p.stats && tid == 0) {
+        atomicAdd(&p.stats[0], stat_d);
+        atomicAdd(&p.stats[1], stat_d2);
     }
 }
 

@@ -1,104 +1,92 @@
-// row_step_umma.cuh — tcgen05 / TMEM Gram path for k in {64, 128}.
+// row_step_umma.cuh — tcgen05 / TMEM Gram path for k in {64, 128} (A6/A7, als.py:414-466).
 //
-// One persistent CTA per SM, warp-specialised, rows dealt round-robin from the
-// longest-first schedule.  Gathered operand: the factor matrix pre-split into
-// bf16 (hi | lo) records, H[row] = [hi(k) | lo(k)], 4k bytes — the same bytes per
-// rating as the float32 row.  hi + lo carries ~17 mantissa bits, and
-//     F^T F  ~=  hi^T hi + hi^T lo + (hi^T lo)^T            (lo^T lo ~ 2^-18 dropped)
-// so two bf16 MMAs give a float32-quality Gram at TF32 cost:
-//   k = 64 : one MMA  D[128 x 64]  = [hi;lo]^T hi      (rows 0-63 = P, rows 64-127 = Q^T)
-//   k = 128: one MMA  D[128 x 256] = hi^T [hi | lo]    (cols 0-127 = P, cols 128-255 = Q)
-// plus a 16-column MMA against [q_hi, q_lo, 1] per rating for c = F^T q and s = F^T 1.
-// Ratings are the MMA K dimension, so both operands are MN-major: a gathered record
-// is one 128-byte line per 64 factors, written straight into the 128B-swizzled
-// canonical layout by 16-byte cp.async (no register pass, no transposition).
+// One persistent CTA per SM, warp-specialised; rows are claimed longest-first from a global
+// atomic cursor (guided chunks), so the power-law tail cannot unbalance the SMs.
 //
-// Warp roles:  [solver warps: 4 per group] [meta] [gather x4] [mma]
-//   meta   : streams (index, rating) of each 32-rating stage into smem (cp.async → mbarrier)
+// Gathered operand: the factor matrix pre-split into bf16 records H[row] = [hi(k) | lo(k)],
+// 4k bytes — the same bytes per rating as the float32 row.  hi + lo carries ~17 mantissa bits:
+//     F^T F ~= hi^T hi + hi^T lo + lo^T hi                       (lo^T lo ~ 2^-18 dropped)
+// All three products are accumulated by the tensor core INTO THE SAME k x k accumulator
+// (three tcgen05.mma per 16 ratings, M = N = k), so TMEM lane i ends up holding the whole
+// symmetric row i of the normal matrix and the solver threads read it straight into
+// registers (row_ldl.cuh) — the Gram never touches shared memory.  A 16-column MMA against
+// [q_hi, q_lo, 1] per rating gives c = F^T q and s = F^T 1 next to it.
+// Ratings are the MMA K dimension, so both operands are MN-major: a gathered record is one
+// 128-byte line per 64 factors, written straight into the 128B-swizzled canonical layout by
+// 16-byte cp.async (no register pass, no transposition).
+//
+// k = 64 uses M = 64 MMAs: the accumulator occupies 16 lanes of each TMEM lane quadrant, and
+// consecutive rows alternate between lanes 0-15 and 16-31 ("interleaved" accumulators), so a
+// solver group (4 warps = 4 quadrants) factors two rows' matrices in lock step.
+//
+// Warp roles:  [solver groups: 4 warps each] [meta] [gather x4] [mma]
+//   meta   : claims rows, streams (index, rating) + a stage header of each 32-rating stage
 //   gather : per stage, 128 threads cp.async the 32 records (and the 32 opposite biases)
-//   mma    : builds the [q_hi,q_lo,1] operand, issues tcgen05.mma, commits stage / accumulator
-//   solver : drains the accumulator from TMEM into 4x4 lower-triangle tiles, then runs
-//            the blocked Cholesky epilogue (row_solve.cuh) while the next rows accumulate.
-//            k=64: a group drains 4 rows together, then each warp solves one of them;
-//            k=128: the 4 warps of a group solve one row together.
+//   mma    : builds the [q_hi,q_lo,1] operand, issues tcgen05.mma, commits stage / accumulator,
+//            hands (row, cnt, sum q, sum q^2) to the solver through a descriptor ring
+//   solver : tcgen05.ld the accumulator rows, LDL^T factor + solve in registers, write x, bias,
+//            and the fused residual statistics (A10) of the row.
 #pragma once
+#include "row_ldl.cuh"
 #include "row_step_ffma.cuh"
 #include "umma_ptx.cuh"
 
 namespace b200als {
 
 constexpr int UM_R = 32;          // ratings per stage
-constexpr int UM_RD = 8;          // row-descriptor ring (t_sum hand-off)
+constexpr int UM_RD = 16;         // row-descriptor ring
 constexpr int UM_GATHER_WARPS = 4;
+
+constexpr int HDR_FIRST = 1, HDR_LAST = 2, HDR_END = 4;
+
+struct StageHdr {                 // 16 bytes at the end of a meta slot
+    int32_t live_n;
+    int32_t row;
+    int32_t flags;
+    int32_t cnt;
+};
+struct RowDesc {                  // 16 bytes
+    int32_t row;                  // < 0: no row (odd tail / end of work)
+    int32_t cnt;
+    float tsum;                   // sum q
+    float qq;                     // sum q^2
+};
 
 template <int K>
 struct UmmaCfg {
     static_assert(K == 64 || K == 128, "tcgen05 path covers k = 64 and k = 128");
     static constexpr int REC_BYTES = 4 * K;                 // [hi | lo] bf16
     static constexpr int N_MB = REC_BYTES / 128;            // 128-byte atoms per record
+    static constexpr int HI_ATOMS = N_MB / 2;
     static constexpr int STAGE_DATA = UM_R * REC_BYTES;
     static constexpr int STAGE_STRIDE = STAGE_DATA;         // data ring (1024-byte aligned atoms)
     static constexpr int B2_BYTES = 1024;                   // per stage: [q_hi,q_lo,1] operand, 32 ratings x 32 B
     static constexpr int META = 32;                         // (index, rating) ring: runs far ahead of the data ring
-    static constexpr int META_BYTES = 256;                  // idx[32] int32 + val[32] float
-    static constexpr int NG = 3;                            // solver groups (4 warps each)
-    static constexpr int STAGES = 5;
-    static constexpr int MATS = (K == 64) ? NG * 4 : NG;    // matrices being solved at once
-    static constexpr int ACC_BUFS = (K == 64) ? 4 : 1;
-    static constexpr int ACC_STRIDE = (K == 64) ? 128 : 512;  // TMEM columns per accumulator
-    static constexpr int D2_COL = (K == 64) ? 64 : 256;
-    static constexpr int MAIN_N = (K == 64) ? 64 : 256;
+    static constexpr int META_BYTES = 288;                  // idx[32] int32 | val[32] float | StageHdr | pad
+    static constexpr int STAGES = (K == 64) ? 8 : 5;
+    static constexpr int NG = (K == 64) ? 3 : 2;            // solver groups (4 warps each)
+    static constexpr int RPB = (K == 64) ? 2 : 1;           // rows per TMEM accumulator buffer
+    static constexpr int RPW = (K == 64) ? 16 : 32;         // matrix rows per solver warp
+    static constexpr int NBUF = (K == 64) ? 6 : 3;          // TMEM accumulator buffers
+    static constexpr int ACC_STRIDE = K + 16;               // TMEM columns per buffer: main | [c_hi,c_lo,s,..]
+    static constexpr int D2_COL = K;
     static constexpr int SOLVER_WARPS = NG * 4;
     static constexpr int WARP_META = SOLVER_WARPS;
     static constexpr int WARP_GATHER0 = SOLVER_WARPS + 1;
     static constexpr int WARP_MMA = SOLVER_WARPS + 1 + UM_GATHER_WARPS;
-    static constexpr int THREADS = (WARP_MMA + 1) * 32;
-    static constexpr size_t MAT_FLOATS = solve_smem_floats(K) + 2 * K;
-    static constexpr int NBAR = 2 * STAGES + 2 * META + MATS + ACC_BUFS + 2 * UM_RD;
+    static constexpr int THREADS = (K == 64) ? (WARP_MMA + 1) * 32 : (SOLVER_WARPS + 8) * 32;   // k=128: whole warpgroups
+    static constexpr int MATS = NG * RPB;
+    static constexpr int MAT_FLOATS = ldl_mat_floats<K>();
+    static constexpr int RED_FLOATS = NG * 4 * RPB * 4;     // per group: [warp][matrix][4]
+    static constexpr int NBAR = 2 * META + 2 * STAGES + 2 * NBUF + 2 * UM_RD;
     static constexpr size_t smem_bytes = 1024 /*align slack*/ + (size_t)STAGES * (STAGE_STRIDE + B2_BYTES + 128) +
-                                         (size_t)META * META_BYTES +
-                                         (size_t)MATS * MAT_FLOATS * 4 + (size_t)NBAR * 8 + UM_RD * 4 + 128;
+                                         (size_t)META * META_BYTES + (size_t)MATS * MAT_FLOATS * 4 +
+                                         (size_t)RED_FLOATS * 4 + (size_t)NBAR * 8 + (size_t)UM_RD * 16 + 64 + 128;
     static_assert(smem_bytes <= 232448, "tcgen05 Gram kernel exceeds 227 KB of shared memory");
+    static_assert(NBUF * ACC_STRIDE <= 512, "TMEM columns");
 };
 
-// Warp-level walker over this CTA's rows: row(n) = rows[b + n*G]; bounds prefetched 32 rows at a time.
-struct RowWalker {
-    const int64_t* indptr;
-    const int32_t* rows;
-    int64_t N, n, base;
-    int G, b;
-    int64_t beg_l, end_l;
-    int32_t row_l;
-    __device__ __forceinline__ void init(const RowStepParams& p, int lane) {
-        indptr = p.indptr; rows = p.rows;
-        G = gridDim.x; b = blockIdx.x;
-        N = (p.n_list > b) ? (p.n_list - b + G - 1) / G : 0;
-        n = 0; base = -64;
-        beg_l = end_l = 0; row_l = 0;
-        (void)lane;
-    }
-    __device__ __forceinline__ bool next(int lane, int64_t& beg, int64_t& end, int32_t& row) {
-        if (n >= N) return false;
-        if (n - base >= 32) {
-            base = n;
-            const int64_t seq = n + lane;
-            if (seq < N) {
-                const int64_t slot = (int64_t)b + seq * G;
-                row_l = rows ? rows[slot] : (int32_t)slot;
-                beg_l = indptr[row_l];
-                end_l = indptr[row_l + 1];
-            }
-        }
-        const int src = (int)(n - base);
-        beg = __shfl_sync(0xffffffffu, beg_l, src);
-        end = __shfl_sync(0xffffffffu, end_l, src);
-        row = __shfl_sync(0xffffffffu, row_l, src);
-        ++n;
-        return true;
-    }
-};
-
-// float32 → [hi | lo] bf16 records
+// float32 -> [hi | lo] bf16 records
 __global__ void __launch_bounds__(256) split_bf16_kernel(const float* __restrict__ F, int64_t ldf, int64_t n_rows, int k,
                                                          __nv_bfloat16* __restrict__ H) {
     const int kq = k >> 2;
@@ -128,10 +116,12 @@ struct UmmaSmem {
     unsigned char* stages;   // [STAGES][STAGE_DATA]
     unsigned char* b2;       // [STAGES][1024]
     unsigned char* bias;     // [STAGES][128]
-    unsigned char* meta;     // [META][256]
-    float* mats;
+    unsigned char* meta;     // [META][META_BYTES]
+    float* mats;             // [MATS][MAT_FLOATS]
+    float* red;              // [NG][4][RPB][4]
     uint64_t *meta_full, *meta_empty, *full, *empty, *acc_full, *acc_empty, *rd_full, *rd_empty;
-    float* tsum;
+    RowDesc* rd;             // [UM_RD]
+    int32_t* bad;            // [16] non-SPD flags, one per matrix slot
     uint32_t* tmem_base;
 };
 
@@ -144,59 +134,104 @@ __device__ __forceinline__ void umma_carve(unsigned char* raw, UmmaSmem& s) {
     s.bias = s.b2 + (size_t)C::STAGES * C::B2_BYTES;
     s.meta = s.bias + (size_t)C::STAGES * 128;
     s.mats = reinterpret_cast<float*>(s.meta + (size_t)C::META * C::META_BYTES);
-    uint64_t* bars = reinterpret_cast<uint64_t*>(s.mats + (size_t)C::MATS * C::MAT_FLOATS);
+    s.red = s.mats + (size_t)C::MATS * C::MAT_FLOATS;
+    uint64_t* bars = reinterpret_cast<uint64_t*>(s.red + C::RED_FLOATS);
     s.meta_full = bars;
     s.meta_empty = s.meta_full + C::META;
     s.full = s.meta_empty + C::META;
     s.empty = s.full + C::STAGES;
     s.acc_full = s.empty + C::STAGES;
-    s.acc_empty = s.acc_full + C::MATS;
-    s.rd_full = s.acc_empty + C::ACC_BUFS;
+    s.acc_empty = s.acc_full + C::NBUF;
+    s.rd_full = s.acc_empty + C::NBUF;
     s.rd_empty = s.rd_full + UM_RD;
-    s.tsum = reinterpret_cast<float*>(s.rd_empty + UM_RD);
-    s.tmem_base = reinterpret_cast<uint32_t*>(s.tsum + UM_RD);
+    s.rd = reinterpret_cast<RowDesc*>(s.rd_empty + UM_RD);
+    s.bad = reinterpret_cast<int32_t*>(s.rd + UM_RD);
+    s.tmem_base = reinterpret_cast<uint32_t*>(s.bad + 16);
 }
 
-// acc_full is indexed by CONSUMER (solver group, matrix slot), not by TMEM buffer: every barrier then
-// has exactly one waiting group that sees its phases strictly in order, so the parity wait is exact
-// (indexing by buffer lets a group that is two uses behind mistake an old phase for the new one).
 template <int K>
-__device__ __forceinline__ void acc_full_slot(uint32_t me, uint32_t& bar_idx, uint32_t& parity) {
-    using C = UmmaCfg<K>;
-    if (K == 128) {
-        bar_idx = me % C::NG;
-        parity = (me / C::NG) & 1;
-    } else {
-        bar_idx = me % (4 * C::NG);           // group (me%12)/4, matrix (me%12)%4
-        parity = (me / (4 * C::NG)) & 1;
-    }
+__device__ __forceinline__ const StageHdr* stage_hdr(const UmmaSmem& s, uint32_t ms) {
+    return reinterpret_cast<const StageHdr*>(s.meta + (size_t)ms * UmmaCfg<K>::META_BYTES + 256);
 }
 
-// ---- meta warp: (index, rating) streams of every stage → smem, fully asynchronous ----------
+// ---- meta warp: claims rows, streams (index, rating) + header of every stage --------------
 template <int K>
 __device__ __forceinline__ void umma_role_meta(const RowStepParams& p, const UmmaSmem& s, int lane) {
     using C = UmmaCfg<K>;
-    RowWalker w;
-    w.init(p, lane);
-    int64_t beg, end;
-    int32_t row;
     uint32_t sg = 0;                                   // global stage counter of this CTA
-    while (w.next(lane, beg, end, row)) {
-        if (beg >= end) continue;
-        for (int64_t t0 = beg; t0 < end; t0 += UM_R, ++sg) {
-            const uint32_t ms = sg % C::META, mph = (sg / C::META) & 1;
-            ptx::mbar_wait(&s.meta_empty[ms], mph ^ 1, 1, (int)sg);
-            unsigned char* mt = s.meta + (size_t)ms * C::META_BYTES;
-            const int64_t e = t0 + lane;
-            const bool live = e < end;
-            const int64_t es = live ? e : beg;         // any valid address for the zero-fill form
-            asm volatile("cp.async.ca.shared.global [%0], [%1], 4, %2;" ::"r"(ptx::smem_u32(mt + lane * 4)),
-                         "l"(p.indices + es), "r"(live ? 4u : 0u)
-                         : "memory");
-            asm volatile("cp.async.ca.shared.global [%0], [%1], 4, %2;" ::"r"(ptx::smem_u32(mt + 128 + lane * 4)),
-                         "l"(p.vals + es), "r"(live ? 4u : 0u)
-                         : "memory");
-            ptx::cp_async_mbar_arrive_noinc(&s.meta_full[ms]);
+    const long long n_list = p.n_list;
+    const long long G = gridDim.x;
+    long long seen = 0;
+
+    // one batch of claimed rows lives in registers: lane l holds entry l
+    int nb = 0;
+    int32_t row_l = 0;
+    int64_t beg_l = 0, end_l = 0;
+    auto claim = [&](int& nb_o, int32_t& row_o, int64_t& beg_o, int64_t& end_o) {
+        // guided chunks: single rows while the list is in its long-row head, up to 32 later
+        long long want = (seen < 16 * G) ? 1 : (n_list - seen) / (G * 8);
+        want = want < 1 ? 1 : (want > 32 ? 32 : want);
+        unsigned long long base = 0;
+        if (lane == 0) base = atomicAdd(p.cursor, (unsigned long long)want);
+        base = __shfl_sync(0xffffffffu, base, 0);
+        seen = (long long)base + want;
+        long long avail = n_list - (long long)base;
+        nb_o = (int)(avail < 0 ? 0 : (avail < want ? avail : want));
+        row_o = 0; beg_o = 0; end_o = 0;
+        if (lane < nb_o) {
+            const long long slot = (long long)base + lane;
+            row_o = p.rows ? p.rows[slot] : (int32_t)slot;
+            beg_o = p.indptr[row_o];
+            end_o = p.indptr[row_o + 1];
+        }
+    };
+    claim(nb, row_l, beg_l, end_l);
+    while (nb > 0) {
+        // prefetch the next batch while this one streams
+        int nb_n; int32_t row_n; int64_t beg_n, end_n;
+        claim(nb_n, row_n, beg_n, end_n);
+        for (int e = 0; e < nb; ++e) {
+            const int64_t beg = __shfl_sync(0xffffffffu, beg_l, e);
+            const int64_t end = __shfl_sync(0xffffffffu, end_l, e);
+            const int32_t row = __shfl_sync(0xffffffffu, row_l, e);
+            for (int64_t t0 = beg; t0 < end; t0 += UM_R, ++sg) {
+                const uint32_t ms = sg % C::META, mph = (sg / C::META) & 1;
+                ptx::mbar_wait(&s.meta_empty[ms], mph ^ 1, 1, (int)sg);
+                unsigned char* mt = s.meta + (size_t)ms * C::META_BYTES;
+                const int64_t ee = t0 + lane;
+                const bool live = ee < end;
+                const int64_t es = live ? ee : beg;        // any valid address for the zero-fill form
+                asm volatile("cp.async.ca.shared.global [%0], [%1], 4, %2;" ::"r"(ptx::smem_u32(mt + lane * 4)),
+                             "l"(p.indices + es), "r"(live ? 4u : 0u)
+                             : "memory");
+                asm volatile("cp.async.ca.shared.global [%0], [%1], 4, %2;" ::"r"(ptx::smem_u32(mt + 128 + lane * 4)),
+                             "l"(p.vals + es), "r"(live ? 4u : 0u)
+                             : "memory");
+                ptx::cp_async_mbar_arrive_noinc(&s.meta_full[ms]);
+                if (lane == 0) {
+                    StageHdr h;
+                    h.live_n = (int32_t)((end - t0) < UM_R ? (end - t0) : UM_R);
+                    h.row = row;
+                    h.flags = (t0 == beg ? HDR_FIRST : 0) | (t0 + UM_R >= end ? HDR_LAST : 0);
+                    h.cnt = (int32_t)(end - beg);
+                    *reinterpret_cast<int4*>(mt + 256) = *reinterpret_cast<const int4*>(&h);
+                    ptx::mbar_arrive(&s.meta_full[ms]);    // release: header visible to the waiters
+                }
+            }
+        }
+        nb = nb_n; row_l = row_n; beg_l = beg_n; end_l = end_n;
+    }
+    // end-of-work stage
+    {
+        const uint32_t ms = sg % C::META, mph = (sg / C::META) & 1;
+        ptx::mbar_wait(&s.meta_empty[ms], mph ^ 1, 1, (int)sg);
+        unsigned char* mt = s.meta + (size_t)ms * C::META_BYTES;
+        ptx::cp_async_mbar_arrive_noinc(&s.meta_full[ms]);
+        if (lane == 0) {
+            StageHdr h;
+            h.live_n = 0; h.row = -1; h.flags = HDR_END; h.cnt = 0;
+            *reinterpret_cast<int4*>(mt + 256) = *reinterpret_cast<const int4*>(&h);
+            ptx::mbar_arrive(&s.meta_full[ms]);
         }
     }
     cp_async_wait<0>();
@@ -205,320 +240,261 @@ __device__ __forceinline__ void umma_role_meta(const RowStepParams& p, const Umm
 // ---- gather warps: 32 records (+ opposite biases) per stage into the swizzled MN-major tile ----
 template <int K>
 __device__ __forceinline__ void umma_role_gather(const RowStepParams& p, const UmmaSmem& s, const unsigned char* H,
-                                                 int gtid, int lane) {
+                                                 int gtid) {
     using C = UmmaCfg<K>;
-    RowWalker w;
-    w.init(p, lane);
-    int64_t beg, end;
-    int32_t row;
-    uint32_t sg = 0;
     const int rr = (gtid >> 3) & 7;        // rating inside its group of 8 == swizzle row
     const int ch = gtid & 7;               // 16-byte chunk inside the 128-byte line
     const int half = gtid >> 6;            // 0 / 1
-    while (w.next(lane, beg, end, row)) {
-        if (beg >= end) continue;
-        for (int64_t t0 = beg; t0 < end; t0 += UM_R, ++sg) {
-            const uint32_t slot = sg % C::STAGES, ph = (sg / C::STAGES) & 1;
-            const uint32_t ms = sg % C::META, mph = (sg / C::META) & 1;
-            unsigned char* st = s.stages + (size_t)slot * C::STAGE_STRIDE;
-            ptx::mbar_wait(&s.meta_full[ms], mph, 2, (int)sg);
-            ptx::mbar_wait(&s.empty[slot], ph ^ 1, 11, (int)sg);
-            const int32_t* idx_s = reinterpret_cast<const int32_t*>(s.meta + (size_t)ms * C::META_BYTES);
-            const int live_n = (int)((end - t0) < UM_R ? (end - t0) : UM_R);
-            const uint32_t st_addr = ptx::smem_u32(st);
+    for (uint32_t sg = 0;; ++sg) {
+        const uint32_t slot = sg % C::STAGES, ph = (sg / C::STAGES) & 1;
+        const uint32_t ms = sg % C::META, mph = (sg / C::META) & 1;
+        ptx::mbar_wait(&s.meta_full[ms], mph, 2, (int)sg);
+        const StageHdr* hd = stage_hdr<K>(s, ms);
+        if (hd->flags & HDR_END) break;
+        const int live_n = hd->live_n;
+        unsigned char* st = s.stages + (size_t)slot * C::STAGE_STRIDE;
+        ptx::mbar_wait(&s.empty[slot], ph ^ 1, 11, (int)sg);
+        const int32_t* idx_s = reinterpret_cast<const int32_t*>(s.meta + (size_t)ms * C::META_BYTES);
+        const uint32_t st_addr = ptx::smem_u32(st);
 #pragma unroll
-            for (int j = 0; j < C::N_MB * 2; ++j) {
-                // chunk id c = gtid + 128 j  →  (kb, mb) atom, line rr, chunk ch
-                const int atom = half + 2 * j;             // = c / 64
-                const int kb = atom / C::N_MB, mb = atom % C::N_MB;
-                const int rating = kb * 8 + rr;
-                const bool live = rating < live_n;
-                const int32_t ix = idx_s[rating];
-                const unsigned char* src = H + (size_t)ix * C::REC_BYTES + mb * 128 + ch * 16;
-                const uint32_t dst = st_addr + (uint32_t)((kb * C::N_MB + mb) * 1024 + rr * 128 + ((ch ^ rr) << 4));
-                ptx::cp_async16_zfill(dst, src, live ? 16u : 0u);
-            }
-            if (gtid < UM_R) {
-                const bool live = gtid < live_n;
-                const int32_t ix = idx_s[gtid];
-                asm volatile("cp.async.ca.shared.global [%0], [%1], 4, %2;" ::"r"(ptx::smem_u32(s.bias + slot * 128 + gtid * 4)),
-                             "l"(p.bias_other + ix), "r"(live ? 4u : 0u)
-                             : "memory");
-            }
-            ptx::cp_async_mbar_arrive_noinc(&s.full[slot]);
+        for (int j = 0; j < C::N_MB * 2; ++j) {
+            // chunk id c = gtid + 128 j  ->  (kb, mb) atom, line rr, chunk ch
+            const int atom = half + 2 * j;             // = c / 64
+            const int kb = atom / C::N_MB, mb = atom % C::N_MB;
+            const int rating = kb * 8 + rr;
+            const bool live = rating < live_n;
+            const int32_t ix = idx_s[rating];
+            const unsigned char* src = H + (size_t)ix * C::REC_BYTES + mb * 128 + ch * 16;
+            const uint32_t dst = st_addr + (uint32_t)((kb * C::N_MB + mb) * 1024 + rr * 128 + ((ch ^ rr) << 4));
+            ptx::cp_async16_zfill(dst, src, live ? 16u : 0u);
         }
+        if (gtid < UM_R) {
+            const bool live = gtid < live_n;
+            const int32_t ix = idx_s[gtid];
+            asm volatile("cp.async.ca.shared.global [%0], [%1], 4, %2;" ::"r"(ptx::smem_u32(s.bias + slot * 128 + gtid * 4)),
+                         "l"(p.bias_other + ix), "r"(live ? 4u : 0u)
+                         : "memory");
+        }
+        ptx::cp_async_mbar_arrive_noinc(&s.full[slot]);
     }
     cp_async_wait<0>();
 }
 
 // ---- mma warp ------------------------------------------------------------------------------
 template <int K>
-__device__ __forceinline__ void umma_role_mma(const RowStepParams& p, const UmmaSmem& s, int lane) {
-    using C = UmmaCfg<K>;
-    RowWalker w;
-    w.init(p, lane);
-    int64_t beg, end;
-    int32_t row;
-    uint32_t sg = 0;
-    uint32_t nrow = 0;
-    const float mu = *p.mu;
-    const uint32_t tmem = *s.tmem_base;
-    constexpr uint32_t IDESC_MAIN = ptx::idesc_bf16_mn(128, C::MAIN_N);
-    constexpr uint32_t IDESC_D2 = ptx::idesc_bf16_mn(128, 16);
-    constexpr uint32_t SBO = C::N_MB * 1024;           // K-atom (8 ratings) stride
-    constexpr uint32_t LBO = 1024;                     // MN-atom (64 factors) stride
-    while (w.next(lane, beg, end, row)) {
-        if (beg >= end) continue;
-        const uint32_t buf = nrow % C::ACC_BUFS, aph = (nrow / C::ACC_BUFS) & 1;
-        ptx::mbar_wait(&s.acc_empty[buf], aph ^ 1, 3, (int)nrow);     // accumulator drained by its solver group
-        ptx::tc_fence_after();
-        const uint32_t d_main = tmem + buf * C::ACC_STRIDE;
-        const uint32_t d_two = d_main + C::D2_COL;
-        float tsum = 0.0f;
-        bool first = true;
-        for (int64_t t0 = beg; t0 < end; t0 += UM_R, ++sg) {
-            const uint32_t slot = sg % C::STAGES, ph = (sg / C::STAGES) & 1;
-            unsigned char* st = s.stages + (size_t)slot * C::STAGE_STRIDE;
-            const uint32_t ms = sg % C::META, mph = (sg / C::META) & 1;
-            ptx::mbar_wait(&s.meta_full[ms], mph, 4, (int)sg);
-            ptx::mbar_wait(&s.full[slot], ph, 5, (int)sg);
-            // the [q_hi, q_lo, 1] operand of this stage (no-swizzle MN-major: 8 ratings x 16 B core matrices)
-            const bool live = (t0 + lane) < end;
-            const float v = reinterpret_cast<const float*>(s.meta + (size_t)ms * C::META_BYTES + 128)[lane];
-            const float bo = reinterpret_cast<const float*>(s.bias + slot * 128)[lane];
-            const float q = live ? v - (mu + bo) : 0.0f;
-            tsum += q;
-            const __nv_bfloat16 qh = __float2bfloat16_rn(q);
-            const __nv_bfloat16 ql = __float2bfloat16_rn(q - __bfloat162float(qh));
-            const __nv_bfloat162 w0 = __halves2bfloat162(qh, ql);
-            const __nv_bfloat162 w1 = __halves2bfloat162(__float2bfloat16_rn(live ? 1.0f : 0.0f), __float2bfloat16_rn(0.0f));
-            uint4 c0;
-            c0.x = *reinterpret_cast<const uint32_t*>(&w0);
-            c0.y = *reinterpret_cast<const uint32_t*>(&w1);
-            c0.z = 0u; c0.w = 0u;
-            unsigned char* b2 = s.b2 + (size_t)slot * C::B2_BYTES + (lane >> 3) * 256 + (lane & 7) * 16;
-            *reinterpret_cast<uint4*>(b2) = c0;                          // columns 0..7
-            *reinterpret_cast<uint4*>(b2 + 128) = make_uint4(0u, 0u, 0u, 0u);   // columns 8..15
-            ptx::fence_proxy_async();
-            __syncwarp();
-            ptx::tc_fence_after();
-            if (lane == 0) {
-                ptx::mbar_arrive(&s.meta_empty[ms]);                     // idx (gather) and val (this warp) consumed
-                const uint32_t sa = ptx::smem_u32(st);
-                const uint32_t sb2 = ptx::smem_u32(s.b2 + (size_t)slot * C::B2_BYTES);
-#pragma unroll
-                for (int ks = 0; ks < UM_R / 16; ++ks) {
-                    const uint32_t a_addr = sa + ks * 2 * SBO;
-                    const uint64_t a_desc = ptx::smem_desc(a_addr, LBO, SBO, ptx::SWZ_128B);
-                    const uint64_t b2_desc = ptx::smem_desc(sb2 + ks * 512, 256, 128, ptx::SWZ_NONE);
-                    const uint32_t acc = (first && ks == 0) ? 0u : 1u;
-                    // main Gram MMA: B starts at atom 0 of the same tile (k=64: hi only; k=128: hi|lo)
-                    ptx::umma_bf16(d_main, a_desc, a_desc, IDESC_MAIN, acc);
-                    ptx::umma_bf16(d_two, a_desc, b2_desc, IDESC_D2, acc);
-                    if (K == 128) {
-                        const uint64_t alo_desc = ptx::smem_desc(a_addr + 2 * 1024, LBO, SBO, ptx::SWZ_128B);
-                        ptx::umma_bf16(d_two, alo_desc, b2_desc, IDESC_D2, 1u);
-                    }
-                }
-                ptx::umma_commit(&s.empty[slot]);                        // stage reusable once these MMAs finish
-                if (t0 + UM_R >= end) {
-                    uint32_t fb, fp;
-                    acc_full_slot<K>(nrow, fb, fp);
-                    ptx::umma_commit(&s.acc_full[fb]);
-                }
-            }
-            __syncwarp();
-            first = false;
-        }
-        // t_sum = sum q of the row → solver (explicit release/acquire pair, not the async commit)
-        tsum = warp_sum(tsum);
-        const uint32_t rd = nrow % UM_RD, rph = (nrow / UM_RD) & 1;
-        ptx::mbar_wait(&s.rd_empty[rd], rph ^ 1, 6, (int)nrow);
-        if (lane == 0) {
-            s.tsum[rd] = tsum;
-            ptx::mbar_arrive(&s.rd_full[rd]);
-        }
-        ++nrow;
+__device__ __forceinline__ void umma_publish_desc(const UmmaSmem& s, uint32_t n, int lane, int32_t row, int32_t cnt,
+                                                  float tsum, float qq) {
+    const uint32_t rd = n % UM_RD, rph = (n / UM_RD) & 1;
+    ptx::mbar_wait(&s.rd_empty[rd], rph ^ 1, 6, (int)n);
+    if (lane == 0) {
+        RowDesc d;
+        d.row = row; d.cnt = cnt; d.tsum = tsum; d.qq = qq;
+        *reinterpret_cast<int4*>(&s.rd[rd]) = *reinterpret_cast<const int4*>(&d);
+        ptx::mbar_arrive(&s.rd_full[rd]);                  // release
     }
-}
-
-// ---- solver groups ----------------------------------------------------------------------------
-
-// k = 64: accumulator rows 0..63 = P = hi^T hi, rows 64..127 = Q^T = lo^T hi.  A = P + Q^T + Q.
-// Called by the 4 warps of a group (wq = warp in group = TMEM lane quadrant).
-__device__ __forceinline__ void umma_drain64(uint32_t taddr_buf, float* Gt, float* c_s, float* s_s, int wq, int lane,
-                                             int bar) {
-    const uint32_t trow = taddr_buf + ((uint32_t)(32 * wq) << 16);
-    const int i = (32 * wq + lane) & 63;
-    const bool isQ = wq >= 2;
-    const int imax = ((32 * wq) & 63) + 31;            // warp-uniform bounds for the collective tcgen05.ld
-    const int imin = (32 * wq) & 63;
-    float d2[4];
-    ptx::tmem_ld4(trow + 64, d2);
-    const float cpart = d2[0] + d2[1], spart = d2[2];
-    float v[16];
-    if (!isQ) {
-        c_s[i] = cpart; s_s[i] = spart;
-        for (int jc = 0; jc * 16 <= imax; ++jc) {
-            ptx::tmem_ld16(trow + jc * 16, v);
-#pragma unroll
-            for (int jj = 0; jj < 16; ++jj) {
-                const int j = jc * 16 + jj;
-                if (j <= i) *tile_elem(Gt, i, j) = v[jj];
-            }
-        }
-    }
-    bar_sync(bar, 128);
-    if (isQ) {
-        c_s[i] += cpart; s_s[i] += spart;
-        for (int jc = 0; jc * 16 <= imax; ++jc) {      // row part: A[i][j] += Q^T[i][j], j <= i
-            ptx::tmem_ld16(trow + jc * 16, v);
-#pragma unroll
-            for (int jj = 0; jj < 16; ++jj) {
-                const int j = jc * 16 + jj;
-                if (j <= i) *tile_elem(Gt, i, j) += v[jj];
-            }
-        }
-    }
-    bar_sync(bar, 128);
-    if (isQ) {
-        for (int jc = imin / 16; jc < 4; ++jc) {       // column part: A[j][i] += Q^T[i][j], j >= i
-            ptx::tmem_ld16(trow + jc * 16, v);
-#pragma unroll
-            for (int jj = 0; jj < 16; ++jj) {
-                const int j = jc * 16 + jj;
-                if (j >= i) *tile_elem(Gt, j, i) += v[jj];
-            }
-        }
-    }
-}
-
-// k = 128: accumulator row i = [P[i][0..127] | Q[i][0..127]].  A = P + Q + Q^T.
-__device__ __forceinline__ void umma_drain128(uint32_t taddr_buf, float* Gt, float* c_s, float* s_s, int wq, int lane,
-                                              int bar) {
-    const uint32_t trow = taddr_buf + ((uint32_t)(32 * wq) << 16);
-    const int i = 32 * wq + lane;
-    const int imax = 32 * wq + 31, imin = 32 * wq;
-    float d2[4];
-    ptx::tmem_ld4(trow + 256, d2);
-    c_s[i] = d2[0] + d2[1];
-    s_s[i] = d2[2];
-    float v[16], u[16];
-    for (int jc = 0; jc * 16 <= imax; ++jc) {
-        ptx::tmem_ld16(trow + jc * 16, v);
-        ptx::tmem_ld16(trow + 128 + jc * 16, u);
-#pragma unroll
-        for (int jj = 0; jj < 16; ++jj) {
-            const int j = jc * 16 + jj;
-            if (j < i) *tile_elem(Gt, i, j) = v[jj] + u[jj];
-            else if (j == i) *tile_elem(Gt, i, j) = v[jj] + 2.0f * u[jj];
-        }
-    }
-    bar_sync(bar, 128);
-    for (int jc = imin / 16; jc < 8; ++jc) {
-        ptx::tmem_ld16(trow + 128 + jc * 16, u);
-#pragma unroll
-        for (int jj = 0; jj < 16; ++jj) {
-            const int j = jc * 16 + jj;
-            if (j > i) *tile_elem(Gt, j, i) += u[jj];
-        }
-    }
+    __syncwarp();
 }
 
 template <int K>
+__device__ __forceinline__ void umma_role_mma(const RowStepParams& p, const UmmaSmem& s, int lane) {
+    using C = UmmaCfg<K>;
+    const float mu = *p.mu;
+    const uint32_t tmem = *s.tmem_base;
+    constexpr uint32_t IDESC_MAIN = ptx::idesc_bf16_mn(K, K);
+    constexpr uint32_t IDESC_D2 = ptx::idesc_bf16_mn(K, 16);
+    constexpr uint32_t SBO = C::N_MB * 1024;           // K-atom (8 ratings) stride
+    constexpr uint32_t LBO = 1024;                     // MN-atom (64 factors) stride
+    constexpr uint32_t LO_OFF = C::HI_ATOMS * 1024;    // lo half of the records
+    uint32_t nrow = 0;                                 // rows started so far
+    uint32_t buf = 0, d_main = 0, d_two = 0;
+    float tsum = 0.0f, qq = 0.0f;
+    bool first = true;
+    for (uint32_t sg = 0;; ++sg) {
+        const uint32_t slot = sg % C::STAGES, ph = (sg / C::STAGES) & 1;
+        const uint32_t ms = sg % C::META, mph = (sg / C::META) & 1;
+        ptx::mbar_wait(&s.meta_full[ms], mph, 4, (int)sg);
+        const StageHdr* hd = stage_hdr<K>(s, ms);
+        const int flags = hd->flags, live_n = hd->live_n, hrow = hd->row, hcnt = hd->cnt;
+        if (flags & HDR_END) break;
+        if (flags & HDR_FIRST) {
+            const uint32_t pr = nrow / C::RPB, h = nrow % C::RPB;
+            buf = pr % C::NBUF;
+            if (h == 0) {
+                ptx::mbar_wait(&s.acc_empty[buf], ((pr / C::NBUF) & 1) ^ 1, 3, (int)nrow);   // drained by its solver group
+                ptx::tc_fence_after();
+            }
+            d_main = tmem + buf * C::ACC_STRIDE + ((h * 16u) << 16);
+            d_two = d_main + C::D2_COL;
+            tsum = 0.0f; qq = 0.0f;
+            first = true;
+        }
+        unsigned char* st = s.stages + (size_t)slot * C::STAGE_STRIDE;
+        ptx::mbar_wait(&s.full[slot], ph, 5, (int)sg);
+        // the [q_hi, q_lo, 1] operand of this stage (no-swizzle MN-major: 8 ratings x 16 B core matrices)
+        const bool live = lane < live_n;
+        const float v = reinterpret_cast<const float*>(s.meta + (size_t)ms * C::META_BYTES + 128)[lane];
+        const float bo = reinterpret_cast<const float*>(s.bias + slot * 128)[lane];
+        const float q = live ? v - (mu + bo) : 0.0f;
+        tsum += q;
+        qq = fmaf(q, q, qq);
+        const __nv_bfloat16 qh = __float2bfloat16_rn(q);
+        const __nv_bfloat16 ql = __float2bfloat16_rn(q - __bfloat162float(qh));
+        const __nv_bfloat162 w0 = __halves2bfloat162(qh, ql);
+        const __nv_bfloat162 w1 = __halves2bfloat162(__float2bfloat16_rn(live ? 1.0f : 0.0f), __float2bfloat16_rn(0.0f));
+        uint4 c0;
+        c0.x = *reinterpret_cast<const uint32_t*>(&w0);
+        c0.y = *reinterpret_cast<const uint32_t*>(&w1);
+        c0.z = 0u; c0.w = 0u;
+        unsigned char* b2 = s.b2 + (size_t)slot * C::B2_BYTES + (lane >> 3) * 256 + (lane & 7) * 16;
+        *reinterpret_cast<uint4*>(b2) = c0;                          // columns 0..7
+        *reinterpret_cast<uint4*>(b2 + 128) = make_uint4(0u, 0u, 0u, 0u);   // columns 8..15
+        ptx::fence_proxy_async();
+        __syncwarp();
+        ptx::tc_fence_after();
+        if (lane == 0) {
+            ptx::mbar_arrive(&s.meta_empty[ms]);                     // idx/hdr (gather) and val (this warp) consumed
+            const uint32_t sa = ptx::smem_u32(st);
+            const uint32_t sb2 = ptx::smem_u32(s.b2 + (size_t)slot * C::B2_BYTES);
+#pragma unroll
+            for (int ks = 0; ks < UM_R / 16; ++ks) {
+                const uint32_t a_addr = sa + ks * 2 * SBO;
+                const uint64_t hi_desc = ptx::smem_desc(a_addr, LBO, SBO, ptx::SWZ_128B);
+                const uint64_t lo_desc = ptx::smem_desc(a_addr + LO_OFF, LBO, SBO, ptx::SWZ_128B);
+                const uint64_t b2_desc = ptx::smem_desc(sb2 + ks * 512, 256, 128, ptx::SWZ_NONE);
+                const uint32_t acc = (first && ks == 0) ? 0u : 1u;
+                // A = hi^T hi + hi^T lo + lo^T hi, all into the same accumulator: TMEM lane i = row i of A
+                ptx::umma_bf16(d_main, hi_desc, hi_desc, IDESC_MAIN, acc);
+                ptx::umma_bf16(d_main, hi_desc, lo_desc, IDESC_MAIN, 1u);
+                ptx::umma_bf16(d_main, lo_desc, hi_desc, IDESC_MAIN, 1u);
+                ptx::umma_bf16(d_two, hi_desc, b2_desc, IDESC_D2, acc);
+                ptx::umma_bf16(d_two, lo_desc, b2_desc, IDESC_D2, 1u);
+            }
+            ptx::umma_commit(&s.empty[slot]);                        // stage reusable once these MMAs finish
+            if (flags & HDR_LAST) ptx::umma_commit(&s.acc_full[buf]);
+        }
+        __syncwarp();
+        first = false;
+        if (flags & HDR_LAST) {
+            // (row, cnt, sum q, sum q^2) -> solver (explicit release/acquire pair, not the async commit)
+            tsum = warp_sum(tsum);
+            qq = warp_sum(qq);
+            umma_publish_desc<K>(s, nrow, lane, hrow, hcnt, tsum, qq);
+            ++nrow;
+        }
+    }
+    // odd tail: the second half of the last accumulator pair holds no row
+    if (nrow % C::RPB != 0) {
+        umma_publish_desc<K>(s, nrow, lane, -1, 0, 0.0f, 0.0f);
+        if (lane == 0) ptx::mbar_arrive(&s.acc_full[buf]);
+        ++nrow;
+    }
+    // end-of-work descriptors: one empty pair per solver group
+    for (int i = 0; i < C::NG * C::RPB; ++i, ++nrow) umma_publish_desc<K>(s, nrow, lane, -1, 0, 0.0f, 0.0f);
+}
+
+// ---- solver groups ----------------------------------------------------------------------------
+template <int K>
 __device__ __forceinline__ void umma_role_solver(const RowStepParams& p, const UmmaSmem& s, int warp, int lane) {
     using C = UmmaCfg<K>;
-    const int g = warp >> 2, wq = warp & 3;            // group, warp in group (== TMEM lane quadrant)
-    const int gtid = wq * 32 + lane;
-    const int gbar = 1 + g;                            // named barrier of the group
+    using L = Ldl<K, C::RPW>;
+    const int g = warp >> 2, q = warp & 3;             // group, warp in group (== TMEM lane quadrant)
+    const int h = lane / C::RPW;                       // matrix of the accumulator pair (k=64), else 0
+    const int seg = lane % C::RPW;
+    const int r = C::RPW * q + seg;                    // matrix row owned by this thread
+    const int col_bar = 1 + 2 * g, phase_bar = 2 + 2 * g;
     const uint32_t tmem = *s.tmem_base;
-    RowWalker w;
-    w.init(p, lane);
-    int64_t beg, end;
-    int32_t row;
-    uint32_t nrow = 0;
-    RowEpilogueArgs ea;
-    ea.k = K; ea.mode = p.mode;
-    ea.X = p.X; ea.ldx = p.ldx; ea.bias_own = p.bias_own;
-    ea.chol_out = p.chol_out; ea.aux_out = p.aux_out; ea.status = p.status;
+    float* cb = s.mats + (size_t)(g * C::RPB + h) * C::MAT_FLOATS;
+    float* xb = cb + ldl_cols_floats<K>() + K;
+    float* red = s.red + (size_t)g * 4 * C::RPB * 4;
+    int32_t* bad = s.bad + g * C::RPB + h;
+    double acc_d = 0.0, acc_d2 = 0.0;                  // fused residual statistics (thread r == 0 of each matrix)
 
-    if (K == 128) {
-        // rows nrow with nrow % NG == g; the 4 warps drain and solve together
-        float* mat = s.mats + (size_t)g * C::MAT_FLOATS;
-        SolveSmem S;
-        S.carve<K>(mat);
-        float* c_s = mat + solve_smem_floats(K);
-        float* s_s = c_s + K;
-        while (w.next(lane, beg, end, row)) {
-            if (beg >= end) continue;
-            const uint32_t me = nrow++;
-            if ((int)(me % C::NG) != g) continue;
-            const uint32_t buf = me % C::ACC_BUFS;
-            {
-                uint32_t fb, fp;
-                acc_full_slot<K>(me, fb, fp);
-                ptx::mbar_wait(&s.acc_full[fb], fp, 7, (int)me);
-            }
-            ptx::tc_fence_after();
-            umma_drain128(tmem + buf * C::ACC_STRIDE, S.Gt, c_s, s_s, wq, lane, gbar);
-            ptx::tc_fence_before();
-            ptx::mbar_arrive(&s.acc_empty[buf]);
-            const uint32_t rd = me % UM_RD, rph = (me / UM_RD) & 1;
-            ptx::mbar_wait(&s.rd_full[rd], rph, 8, (int)me);
-            const float t_sum = s.tsum[rd];
-            bar_sync(gbar, 128);
-            if (gtid == 0) ptx::mbar_arrive(&s.rd_empty[rd]);
-            ea.reg = p.reg_row ? p.reg_row[row] : p.reg;
-            ea.lam_bias = p.lam_bias_row ? p.lam_bias_row[row] : p.lam_bias;
-            row_epilogue_tiles(S, c_s, s_s, t_sum, end - beg, row, ea, gtid, 128, gbar);
-            bar_sync(gbar, 128);
+    for (uint32_t pr = g;; pr += C::NG) {
+        // descriptors of the rows in this accumulator buffer
+        const uint32_t n0 = pr * C::RPB;
+#pragma unroll
+        for (int hh = 0; hh < C::RPB; ++hh) {
+            const uint32_t n = n0 + hh;
+            ptx::mbar_wait(&s.rd_full[n % UM_RD], (n / UM_RD) & 1, 8, (int)n);
         }
-    } else {
-        // batches of 4 consecutive rows per group: drained together, then one warp solves each
-        float* mat = s.mats + (size_t)(g * 4 + wq) * C::MAT_FLOATS;     // this warp's own matrix
-        SolveSmem S;
-        S.carve<K>(mat);
-        float* c_s = mat + solve_smem_floats(K);
-        float* s_s = c_s + K;
-        bool more = true;
-        while (more) {
-            int64_t my_beg = 0, my_end = 0;
-            int32_t my_row = -1;
-            uint32_t my_seq = 0;
-            for (int slot4 = 0; slot4 < 4 * C::NG; ++slot4) {
-                // every group walks all rows; a batch is 4*NG consecutive rows, group g owns rows [4g, 4g+4)
-                do { more = w.next(lane, beg, end, row); } while (more && beg >= end);
-                if (!more) break;
-                const uint32_t me = nrow++;
-                if (slot4 / 4 != g) continue;
-                const int j = slot4 & 3;                                 // matrix of warp j of this group
-                float* matj = s.mats + (size_t)(g * 4 + j) * C::MAT_FLOATS;
-                const uint32_t buf = me % C::ACC_BUFS;
-                {
-                    uint32_t fb, fp;
-                    acc_full_slot<K>(me, fb, fp);
-                    ptx::mbar_wait(&s.acc_full[fb], fp, 9, (int)me);
+        const RowDesc d0 = s.rd[n0 % UM_RD];
+        const RowDesc dm = s.rd[(n0 + h) % UM_RD];
+        named_bar_sync(phase_bar, 128);                // everyone holds its descriptor
+        if (q == 0 && seg == 0) ptx::mbar_arrive(&s.rd_empty[(n0 + h) % UM_RD]);
+        if (d0.row < 0) break;                         // end of work (rows fill buffers in order)
+        const bool valid = dm.row >= 0;
+        const int64_t row = valid ? dm.row : d0.row;   // absent half: shadow a valid row, write nothing
+        const float ridge = p.reg_row ? p.reg_row[row] : p.reg;
+        const float lam_bias = p.lam_bias_row ? p.lam_bias_row[row] : p.lam_bias;
+        const float bias_old = p.bias_own[row];
+        if (q == 0 && seg == 0) *bad = 0;
+
+        const uint32_t buf = pr % C::NBUF;
+        ptx::mbar_wait(&s.acc_full[buf], (pr / C::NBUF) & 1, 7, (int)pr);
+        ptx::tc_fence_after();
+        const uint32_t trow = tmem + buf * C::ACC_STRIDE + ((uint32_t)(32 * q) << 16);
+        float a[K];
+#pragma unroll
+        for (int c0 = 0; c0 < K; c0 += 16) {
+            float v[16];
+            ptx::tmem_ld16(trow + c0, v);
+#pragma unroll
+            for (int i = 0; i < 16; ++i) a[c0 + i] = v[i];
+        }
+        float d2[4];
+        ptx::tmem_ld4(trow + C::D2_COL, d2);
+        ptx::tc_fence_before();
+        ptx::mbar_arrive(&s.acc_empty[buf]);           // accumulator buffer free for the next rows
+        const float c_r = d2[0] + d2[1], s_r = d2[2];
+
+        const bool ok = L::factor(a, c_r - bias_old * s_r, ridge, r, q, cb, col_bar);
+        if (!ok && valid) *bad = 1;
+        const float x = L::backsolve(r, q, seg, cb, xb, phase_bar);    // barriers inside publish *bad too
+
+        // s.x, c.x, x.x over the matrix: segment shuffle, then the 4 warps through shared memory
+        float v0 = s_r * x, v1 = c_r * x, v2 = x * x;
+#pragma unroll
+        for (int o = C::RPW / 2; o > 0; o >>= 1) {
+            v0 += __shfl_xor_sync(0xffffffffu, v0, o);
+            v1 += __shfl_xor_sync(0xffffffffu, v1, o);
+            v2 += __shfl_xor_sync(0xffffffffu, v2, o);
+        }
+        if (seg == 0) {
+            float* rr = red + (q * C::RPB + h) * 4;
+            rr[0] = v0; rr[1] = v1; rr[2] = v2;
+        }
+        named_bar_sync(phase_bar, 128);
+        const bool good = valid && (*bad == 0);
+        if (good) p.X[(size_t)row * p.ldx + r] = x;
+        if (q == 0 && seg == 0) {
+            if (good) {
+                float sx = 0.0f, cx = 0.0f, xx = 0.0f;
+#pragma unroll
+                for (int w = 0; w < 4; ++w) {
+                    const float* rr = red + (w * C::RPB + h) * 4;
+                    sx += rr[0]; cx += rr[1]; xx += rr[2];
                 }
-                ptx::tc_fence_after();
-                umma_drain64(tmem + buf * C::ACC_STRIDE, matj, matj + solve_smem_floats(K),
-                             matj + solve_smem_floats(K) + K, wq, lane, gbar);
-                ptx::tc_fence_before();
-                ptx::mbar_arrive(&s.acc_empty[buf]);
-                if (j == wq) { my_beg = beg; my_end = end; my_row = row; my_seq = me; }
+                const float cnt = (float)dm.cnt;
+                const float beta = (dm.tsum - sx) / (cnt + lam_bias);          // als.py:431-433 / 464-466
+                p.bias_own[row] = beta;
+                // residuals of the row with the fresh x, beta:  d_e = q_e - beta - f_e.x
+                //   sum d   = t - cnt beta - s.x
+                //   sum d^2 = qq - 2 beta t + cnt beta^2 - 2 (c.x - beta s.x) + x^T G x,
+                //   x^T G x = x.(c - beta_old s) - ridge x.x      (x solves (G + ridge I) x = c - beta_old s)
+                const float sd = dm.tsum - cnt * beta - sx;
+                const float sd2 = dm.qq - 2.0f * beta * dm.tsum + cnt * beta * beta - cx +
+                                  (2.0f * beta - bias_old) * sx - ridge * xx;
+                acc_d += (double)sd;
+                acc_d2 += (double)sd2;
+            } else if (valid && p.status) {
+                if (atomicAdd(&p.status[0], 1) == 0) p.status[1] = (int32_t)row;
             }
-            bar_sync(gbar, 128);                                         // all drains of the batch visible
-            if (my_row >= 0) {
-                const uint32_t rd = my_seq % UM_RD, rph = (my_seq / UM_RD) & 1;
-                ptx::mbar_wait(&s.rd_full[rd], rph, 10, (int)my_seq);
-                const float t_sum = s.tsum[rd];
-                __syncwarp();
-                if (lane == 0) ptx::mbar_arrive(&s.rd_empty[rd]);
-                ea.reg = p.reg_row ? p.reg_row[my_row] : p.reg;
-                ea.lam_bias = p.lam_bias_row ? p.lam_bias_row[my_row] : p.lam_bias;
-                row_epilogue_tiles(S, c_s, s_s, t_sum, my_end - my_beg, my_row, ea, lane, 32, 0);
-            }
-            bar_sync(gbar, 128);                                         // matrices free for the next batch
         }
+        named_bar_sync(phase_bar, 128);                // red / xb / columns free for the next pair
+    }
+    if (p.stats && q == 0 && seg == 0) {
+        atomicAdd(&p.stats[0], acc_d);
+        atomicAdd(&p.stats[1], acc_d2);
     }
 }
 
@@ -533,15 +509,17 @@ __global__ void __launch_bounds__(UmmaCfg<K>::THREADS, 1) row_step_umma_kernel(c
 
     if (threadIdx.x == 0) {
         for (int i = 0; i < C::META; ++i) {
-            ptx::mbar_init(&s.meta_full[i], 32);
+            ptx::mbar_init(&s.meta_full[i], 33);
             ptx::mbar_init(&s.meta_empty[i], 1);
         }
         for (int i = 0; i < C::STAGES; ++i) {
             ptx::mbar_init(&s.full[i], UM_GATHER_WARPS * 32);
             ptx::mbar_init(&s.empty[i], 1);
         }
-        for (int i = 0; i < C::MATS; ++i) ptx::mbar_init(&s.acc_full[i], 1);
-        for (int i = 0; i < C::ACC_BUFS; ++i) ptx::mbar_init(&s.acc_empty[i], 128);
+        for (int i = 0; i < C::NBUF; ++i) {
+            ptx::mbar_init(&s.acc_full[i], C::RPB);
+            ptx::mbar_init(&s.acc_empty[i], 128);
+        }
         for (int i = 0; i < UM_RD; ++i) {
             ptx::mbar_init(&s.rd_full[i], 1);
             ptx::mbar_init(&s.rd_empty[i], 1);
@@ -554,13 +532,17 @@ __global__ void __launch_bounds__(UmmaCfg<K>::THREADS, 1) row_step_umma_kernel(c
     ptx::tc_fence_after();
 
     if (warp < C::SOLVER_WARPS) {
+        if (K == 128) asm volatile("setmaxnreg.inc.sync.aligned.u32 200;");
         umma_role_solver<K>(p, s, warp, lane);
-    } else if (warp == C::WARP_META) {
-        umma_role_meta<K>(p, s, lane);
-    } else if (warp < C::WARP_MMA) {
-        umma_role_gather<K>(p, s, H, (warp - C::WARP_GATHER0) * 32 + lane, lane);
     } else {
-        umma_role_mma<K>(p, s, lane);
+        if (K == 128) asm volatile("setmaxnreg.dec.sync.aligned.u32 56;");
+        if (warp == C::WARP_META) {
+            umma_role_meta<K>(p, s, lane);
+        } else if (warp < C::WARP_MMA) {
+            umma_role_gather<K>(p, s, H, (warp - C::WARP_GATHER0) * 32 + lane);
+        } else if (warp == C::WARP_MMA) {
+            umma_role_mma<K>(p, s, lane);
+        }
     }
 
     ptx::tc_fence_before();

@@ -143,6 +143,24 @@ __global__ void finalize_iter_kernel(const double* __restrict__ acc, int64_t nnz
     }
 }
 
+// acc[0..1] are sums of d' = d - mu_old (the item step ran with mu_old, als.py:447): shift back
+__global__ void finalize_iter_fused_kernel(const double* __restrict__ acc, int64_t nnz, float* mu_f32, double* hist) {
+    if (threadIdx.x == 0 && blockIdx.x == 0) {
+        const double N = (double)nnz;
+        const double delta = acc[0] / N;
+        const double mu = (double)*mu_f32 + delta;          // als.py:507
+        double sse = acc[1] - acc[0] * delta;               // sum (d' - delta)^2
+        if (sse < 0.0) sse = 0.0;
+        hist[0] = sqrt(sse / N);                            // als.py:512
+        hist[1] = sqrt(acc[2]);
+        hist[2] = sqrt(acc[3]);
+        hist[3] = sqrt(acc[4]);
+        hist[4] = sqrt(acc[5]);
+        hist[5] = mu;
+        *mu_f32 = (float)mu;
+    }
+}
+
 __global__ void f64_to_f32_kernel(const double* __restrict__ src, float* __restrict__ dst, int64_t count) {
     const int64_t stride = (int64_t)gridDim.x * blockDim.x;
     for (int64_t e = (int64_t)blockIdx.x * blockDim.x + threadIdx.x; e < count; e += stride) dst[e] = (float)src[e];
@@ -294,6 +312,14 @@ int b200als_finalize_iter(const double* acc6, int64_t nnz_total, float* mu_f32, 
                           b200als_stream_t stream) {
     ALS_CHECK_ARG(acc6 && mu_f32 && hist6 && nnz_total > 0, "bad args");
     finalize_iter_kernel<<<1, 32, 0, as_stream(stream)>>>(acc6, nnz_total, mu_f32, hist6);
+    ALS_LAUNCH_CHECK();
+    return B200ALS_OK;
+}
+
+int b200als_finalize_iter_fused(const double* acc6, int64_t nnz_total, float* mu_f32, double* hist6,
+                                b200als_stream_t stream) {
+    ALS_CHECK_ARG(acc6 && mu_f32 && hist6 && nnz_total > 0, "bad args");
+    finalize_iter_fused_kernel<<<1, 32, 0, as_stream(stream)>>>(acc6, nnz_total, mu_f32, hist6);
     ALS_LAUNCH_CHECK();
     return B200ALS_OK;
 }

@@ -31,7 +31,7 @@
 extern "C" {
 #endif
 
-#define B200ALS_ABI_VERSION 4
+#define B200ALS_ABI_VERSION 5
 
 #define B200ALS_OK            0
 #define B200ALS_E_INVALID    -1   /* bad argument */
@@ -123,7 +123,7 @@ int b200als_compose_z(const float* V, int64_t ldv, int64_t n, int32_t k,
  * b_u, X = V.  Rows with no ratings are left untouched.
  *
  * mode B200ALS_STEP_SOLVE   : as above.
- * mode B200ALS_STEP_FACTOR  : (graph sweep, A8) do not solve; store the lower
+ * mode B200ALS_STEP_FACTOR  : (graph sweep, A8; always runs on the FFMA path) do not solve; store the lower
  *     Cholesky factor of A in chol_out[r] (k*k floats, row-major, ld = k) and
  *     c_r = F^T q  (k), s_r = F^T 1 (k), t_r = sum q, in aux_out[r] (2k+2
  *     floats: c, s, t, cnt) for b200als_graph_level_solve.
@@ -157,6 +157,9 @@ typedef struct b200als_step_args {
     float* chol_out;             /* FACTOR mode: n_rows * k * k */
     float* aux_out;              /* FACTOR mode: n_rows * (2k+2) */
     int32_t* status;             /* B200ALS_STATUS_WORDS ints, may be NULL */
+    double*  stats_acc;          /* optional, SOLVE mode: A10 fused into the step (als.py:503-511 when Z == F-side
+                                    factors are final): [0] += sum_e d_e, [1] += sum_e d_e^2 over the rows solved,
+                                    d_e = R_e - (mu + bias_other + bias_own_new + F[idx_e].x_new).  Caller zeroes. */
     void*  workspace; size_t workspace_bytes;   /* see b200als_step_workspace_bytes */
 } b200als_step_args;
 
@@ -197,6 +200,11 @@ int b200als_sumsq(const float* x, int64_t rows, int64_t cols, int64_t ld,
                   double* acc, b200als_stream_t stream);
 int b200als_finalize_iter(const double* acc6, int64_t nnz_total,
                           float* mu_f32, double* hist6, b200als_stream_t stream);
+/* Same, when acc6[0..1] came from b200als_step_args.stats_acc of the item step, i.e. are sums of
+ * d'_e = d_e - mu_old (the step subtracts the mu it ran with):  mu = mu_old + acc[0]/nnz,
+ * rmse^2 = acc[1]/nnz - (acc[0]/nnz)^2.  *mu_f32 is read (mu_old) and overwritten. */
+int b200als_finalize_iter_fused(const double* acc6, int64_t nnz_total,
+                                float* mu_f32, double* hist6, b200als_stream_t stream);
 
 /* ------------------------------------------------------------------------
  * A9 — W_f update (als.py:468-501) in Kronecker form, float64:
