@@ -19,11 +19,12 @@
 // consecutive rows alternate between lanes 0-15 and 16-31 ("interleaved" accumulators), so a
 // solver group (4 warps = 4 quadrants) factors two rows' matrices in lock step.
 //
-// Warp roles:  [solver groups: 4 warps each] [meta] [gather x4] [mma]
+// Warp roles:  [solver groups: 4 warps each] [meta] [gather x4] [prep] [mma]
 //   meta   : claims rows, streams (index, rating) + a stage header of each 32-rating stage
 //   gather : per stage, 128 threads cp.async the 32 records (and the 32 opposite biases)
-//   mma    : builds the [q_hi,q_lo,1] operand, issues tcgen05.mma, commits stage / accumulator,
-//            hands (row, cnt, sum q, sum q^2) to the solver through a descriptor ring
+//   prep   : q = rating - mu - bias, writes the [q_hi,q_lo,1] atom of the stage, hands (row, cnt,
+//            sum q, sum q^2) to the solver through a descriptor ring
+//   mma    : issues tcgen05.mma (3 per 16 ratings), commits stage / accumulator
 //   solver : tcgen05.ld the accumulator rows, LDL^T factor + solve in registers, write x, bias,
 //            and the fused residual statistics (A10) of the row.
 #pragma once
@@ -58,9 +59,9 @@ struct UmmaCfg {
     static constexpr int REC_BYTES = 4 * K;                 // [hi | lo] bf16
     static constexpr int N_MB = REC_BYTES / 128;            // 128-byte atoms per record
     static constexpr int HI_ATOMS = N_MB / 2;
-    static constexpr int STAGE_DATA = UM_R * REC_BYTES;
+    static constexpr int NA = N_MB + 1;                     // atoms per 8-rating K-atom: hi.. | q | lo..
+    static constexpr int STAGE_DATA = (UM_R / 8) * NA * 1024;
     static constexpr int STAGE_STRIDE = STAGE_DATA;         // data ring (1024-byte aligned atoms)
-    static constexpr int B2_BYTES = 1024;                   // per stage: [q_hi,q_lo,1] operand, 32 ratings x 32 B
     static constexpr int META = 32;                         // (index, rating) ring: runs far ahead of the data ring
     static constexpr int META_BYTES = 288;                  // idx[32] int32 | val[32] float | StageHdr | pad
     static constexpr int STAGES = (K == 64) ? 8 : 5;
@@ -73,13 +74,14 @@ struct UmmaCfg {
     static constexpr int SOLVER_WARPS = NG * 4;
     static constexpr int WARP_META = SOLVER_WARPS;
     static constexpr int WARP_GATHER0 = SOLVER_WARPS + 1;
-    static constexpr int WARP_MMA = SOLVER_WARPS + 1 + UM_GATHER_WARPS;
+    static constexpr int WARP_PREP = SOLVER_WARPS + 1 + UM_GATHER_WARPS;
+    static constexpr int WARP_MMA = WARP_PREP + 1;
     static constexpr int THREADS = (K == 64) ? (WARP_MMA + 1) * 32 : (SOLVER_WARPS + 8) * 32;   // k=128: whole warpgroups
     static constexpr int MATS = NG * RPB;
     static constexpr int MAT_FLOATS = ldl_mat_floats<K>();
     static constexpr int RED_FLOATS = NG * 4 * RPB * 4;     // per group: [warp][matrix][4]
-    static constexpr int NBAR = 2 * META + 2 * STAGES + 2 * NBUF + 2 * UM_RD;
-    static constexpr size_t smem_bytes = 1024 /*align slack*/ + (size_t)STAGES * (STAGE_STRIDE + B2_BYTES + 128) +
+    static constexpr int NBAR = (2 * META + 3 * STAGES + 2 * NBUF + 2 * UM_RD + 1) & ~1;   // even: RowDesc ring stays 16-byte aligned
+    static constexpr size_t smem_bytes = 1024 /*align slack*/ + (size_t)STAGES * (STAGE_STRIDE + 128 + 16) +
                                          (size_t)META * META_BYTES + (size_t)MATS * MAT_FLOATS * 4 +
                                          (size_t)RED_FLOATS * 4 + (size_t)NBAR * 8 + (size_t)UM_RD * 16 + 64 + 128;
     static_assert(smem_bytes <= 232448, "tcgen05 Gram kernel exceeds 227 KB of shared memory");
@@ -114,12 +116,12 @@ __global__ void __launch_bounds__(256) split_bf16_kernel(const float* __restrict
 
 struct UmmaSmem {
     unsigned char* stages;   // [STAGES][STAGE_DATA]
-    unsigned char* b2;       // [STAGES][1024]
     unsigned char* bias;     // [STAGES][128]
+    int32_t* sflags;         // [STAGES] stage flags, prep -> mma
     unsigned char* meta;     // [META][META_BYTES]
     float* mats;             // [MATS][MAT_FLOATS]
     float* red;              // [NG][4][RPB][4]
-    uint64_t *meta_full, *meta_empty, *full, *empty, *acc_full, *acc_empty, *rd_full, *rd_empty;
+    uint64_t *meta_full, *meta_empty, *full, *prep_full, *empty, *acc_full, *acc_empty, *rd_full, *rd_empty;
     RowDesc* rd;             // [UM_RD]
     int32_t* bad;            // [16] non-SPD flags, one per matrix slot
     uint32_t* tmem_base;
@@ -130,21 +132,22 @@ __device__ __forceinline__ void umma_carve(unsigned char* raw, UmmaSmem& s) {
     using C = UmmaCfg<K>;
     unsigned char* base = reinterpret_cast<unsigned char*>((reinterpret_cast<uintptr_t>(raw) + 1023) & ~(uintptr_t)1023);
     s.stages = base;
-    s.b2 = s.stages + (size_t)C::STAGES * C::STAGE_STRIDE;
-    s.bias = s.b2 + (size_t)C::STAGES * C::B2_BYTES;
-    s.meta = s.bias + (size_t)C::STAGES * 128;
+    s.bias = s.stages + (size_t)C::STAGES * C::STAGE_STRIDE;
+    s.sflags = reinterpret_cast<int32_t*>(s.bias + (size_t)C::STAGES * 128);
+    s.meta = s.bias + (size_t)C::STAGES * (128 + 16);
     s.mats = reinterpret_cast<float*>(s.meta + (size_t)C::META * C::META_BYTES);
     s.red = s.mats + (size_t)C::MATS * C::MAT_FLOATS;
     uint64_t* bars = reinterpret_cast<uint64_t*>(s.red + C::RED_FLOATS);
     s.meta_full = bars;
     s.meta_empty = s.meta_full + C::META;
     s.full = s.meta_empty + C::META;
-    s.empty = s.full + C::STAGES;
+    s.prep_full = s.full + C::STAGES;
+    s.empty = s.prep_full + C::STAGES;
     s.acc_full = s.empty + C::STAGES;
     s.acc_empty = s.acc_full + C::NBUF;
     s.rd_full = s.acc_empty + C::NBUF;
     s.rd_empty = s.rd_full + UM_RD;
-    s.rd = reinterpret_cast<RowDesc*>(s.rd_empty + UM_RD);
+    s.rd = reinterpret_cast<RowDesc*>(bars + C::NBAR);
     s.bad = reinterpret_cast<int32_t*>(s.rd + UM_RD);
     s.tmem_base = reinterpret_cast<uint32_t*>(s.bad + 16);
 }
@@ -265,7 +268,8 @@ __device__ __forceinline__ void umma_role_gather(const RowStepParams& p, const U
             const bool live = rating < live_n;
             const int32_t ix = idx_s[rating];
             const unsigned char* src = H + (size_t)ix * C::REC_BYTES + mb * 128 + ch * 16;
-            const uint32_t dst = st_addr + (uint32_t)((kb * C::N_MB + mb) * 1024 + rr * 128 + ((ch ^ rr) << 4));
+            const int at = mb < C::HI_ATOMS ? mb : mb + 1;         // the q atom sits between the hi and lo atoms
+            const uint32_t dst = st_addr + (uint32_t)((kb * C::NA + at) * 1024 + rr * 128 + ((ch ^ rr) << 4));
             ptx::cp_async16_zfill(dst, src, live ? 16u : 0u);
         }
         if (gtid < UM_R) {
@@ -280,7 +284,7 @@ __device__ __forceinline__ void umma_role_gather(const RowStepParams& p, const U
     cp_async_wait<0>();
 }
 
-// ---- mma warp ------------------------------------------------------------------------------
+// ---- prep warp: q = rating - mu - bias, the [q_hi, q_lo, 1] atom of the stage, row descriptors ----
 template <int K>
 __device__ __forceinline__ void umma_publish_desc(const UmmaSmem& s, uint32_t n, int lane, int32_t row, int32_t cnt,
                                                   float tsum, float qq) {
@@ -296,41 +300,30 @@ __device__ __forceinline__ void umma_publish_desc(const UmmaSmem& s, uint32_t n,
 }
 
 template <int K>
-__device__ __forceinline__ void umma_role_mma(const RowStepParams& p, const UmmaSmem& s, int lane) {
+__device__ __forceinline__ void umma_role_prep(const RowStepParams& p, const UmmaSmem& s, int lane) {
     using C = UmmaCfg<K>;
     const float mu = *p.mu;
-    const uint32_t tmem = *s.tmem_base;
-    constexpr uint32_t IDESC_MAIN = ptx::idesc_bf16_mn(K, K);
-    constexpr uint32_t IDESC_D2 = ptx::idesc_bf16_mn(K, 16);
-    constexpr uint32_t SBO = C::N_MB * 1024;           // K-atom (8 ratings) stride
-    constexpr uint32_t LBO = 1024;                     // MN-atom (64 factors) stride
-    constexpr uint32_t LO_OFF = C::HI_ATOMS * 1024;    // lo half of the records
-    uint32_t nrow = 0;                                 // rows started so far
-    uint32_t buf = 0, d_main = 0, d_two = 0;
+    uint32_t nrow = 0;                                 // rows finished so far
     float tsum = 0.0f, qq = 0.0f;
-    bool first = true;
+    // this lane's rating line inside the stage's q atoms (128B-swizzled MN-major, like the records)
+    const uint32_t kb = (uint32_t)lane >> 3, rr = (uint32_t)lane & 7;
+    const uint32_t q_off = (kb * C::NA + C::HI_ATOMS) * 1024 + rr * 128;
     for (uint32_t sg = 0;; ++sg) {
         const uint32_t slot = sg % C::STAGES, ph = (sg / C::STAGES) & 1;
         const uint32_t ms = sg % C::META, mph = (sg / C::META) & 1;
         ptx::mbar_wait(&s.meta_full[ms], mph, 4, (int)sg);
         const StageHdr* hd = stage_hdr<K>(s, ms);
         const int flags = hd->flags, live_n = hd->live_n, hrow = hd->row, hcnt = hd->cnt;
-        if (flags & HDR_END) break;
-        if (flags & HDR_FIRST) {
-            const uint32_t pr = nrow / C::RPB, h = nrow % C::RPB;
-            buf = pr % C::NBUF;
-            if (h == 0) {
-                ptx::mbar_wait(&s.acc_empty[buf], ((pr / C::NBUF) & 1) ^ 1, 3, (int)nrow);   // drained by its solver group
-                ptx::tc_fence_after();
+        if (flags & HDR_END) {
+            ptx::mbar_wait(&s.empty[slot], ph ^ 1, 12, (int)sg);      // the slot's previous MMAs (and flag read) are done
+            if (lane == 0) {
+                s.sflags[slot] = HDR_END;
+                ptx::mbar_arrive(&s.prep_full[slot]);
             }
-            d_main = tmem + buf * C::ACC_STRIDE + ((h * 16u) << 16);
-            d_two = d_main + C::D2_COL;
-            tsum = 0.0f; qq = 0.0f;
-            first = true;
+            break;
         }
-        unsigned char* st = s.stages + (size_t)slot * C::STAGE_STRIDE;
+        if (flags & HDR_FIRST) { tsum = 0.0f; qq = 0.0f; }
         ptx::mbar_wait(&s.full[slot], ph, 5, (int)sg);
-        // the [q_hi, q_lo, 1] operand of this stage (no-swizzle MN-major: 8 ratings x 16 B core matrices)
         const bool live = lane < live_n;
         const float v = reinterpret_cast<const float*>(s.meta + (size_t)ms * C::META_BYTES + 128)[lane];
         const float bo = reinterpret_cast<const float*>(s.bias + slot * 128)[lane];
@@ -345,51 +338,92 @@ __device__ __forceinline__ void umma_role_mma(const RowStepParams& p, const Umma
         c0.x = *reinterpret_cast<const uint32_t*>(&w0);
         c0.y = *reinterpret_cast<const uint32_t*>(&w1);
         c0.z = 0u; c0.w = 0u;
-        unsigned char* b2 = s.b2 + (size_t)slot * C::B2_BYTES + (lane >> 3) * 256 + (lane & 7) * 16;
-        *reinterpret_cast<uint4*>(b2) = c0;                          // columns 0..7
-        *reinterpret_cast<uint4*>(b2 + 128) = make_uint4(0u, 0u, 0u, 0u);   // columns 8..15
+        unsigned char* qa = s.stages + (size_t)slot * C::STAGE_STRIDE + q_off;
+        *reinterpret_cast<uint4*>(qa + (rr << 4)) = c0;                              // columns 0..7  (chunk 0 ^ rr)
+        *reinterpret_cast<uint4*>(qa + ((rr ^ 1) << 4)) = make_uint4(0u, 0u, 0u, 0u);   // columns 8..15 (chunk 1 ^ rr)
         ptx::fence_proxy_async();
         __syncwarp();
-        ptx::tc_fence_after();
         if (lane == 0) {
+            s.sflags[slot] = flags;
+            ptx::mbar_arrive(&s.prep_full[slot]);                    // release: atom + flags visible to the mma warp
             ptx::mbar_arrive(&s.meta_empty[ms]);                     // idx/hdr (gather) and val (this warp) consumed
-            const uint32_t sa = ptx::smem_u32(st);
-            const uint32_t sb2 = ptx::smem_u32(s.b2 + (size_t)slot * C::B2_BYTES);
-#pragma unroll
-            for (int ks = 0; ks < UM_R / 16; ++ks) {
-                const uint32_t a_addr = sa + ks * 2 * SBO;
-                const uint64_t hi_desc = ptx::smem_desc(a_addr, LBO, SBO, ptx::SWZ_128B);
-                const uint64_t lo_desc = ptx::smem_desc(a_addr + LO_OFF, LBO, SBO, ptx::SWZ_128B);
-                const uint64_t b2_desc = ptx::smem_desc(sb2 + ks * 512, 256, 128, ptx::SWZ_NONE);
-                const uint32_t acc = (first && ks == 0) ? 0u : 1u;
-                // A = hi^T hi + hi^T lo + lo^T hi, all into the same accumulator: TMEM lane i = row i of A
-                ptx::umma_bf16(d_main, hi_desc, hi_desc, IDESC_MAIN, acc);
-                ptx::umma_bf16(d_main, hi_desc, lo_desc, IDESC_MAIN, 1u);
-                ptx::umma_bf16(d_main, lo_desc, hi_desc, IDESC_MAIN, 1u);
-                ptx::umma_bf16(d_two, hi_desc, b2_desc, IDESC_D2, acc);
-                ptx::umma_bf16(d_two, lo_desc, b2_desc, IDESC_D2, 1u);
-            }
-            ptx::umma_commit(&s.empty[slot]);                        // stage reusable once these MMAs finish
-            if (flags & HDR_LAST) ptx::umma_commit(&s.acc_full[buf]);
         }
-        __syncwarp();
-        first = false;
         if (flags & HDR_LAST) {
-            // (row, cnt, sum q, sum q^2) -> solver (explicit release/acquire pair, not the async commit)
-            tsum = warp_sum(tsum);
-            qq = warp_sum(qq);
-            umma_publish_desc<K>(s, nrow, lane, hrow, hcnt, tsum, qq);
+            // (row, cnt, sum q, sum q^2) -> solver
+            const float ts = warp_sum(tsum), qs = warp_sum(qq);
+            umma_publish_desc<K>(s, nrow, lane, hrow, hcnt, ts, qs);
             ++nrow;
         }
     }
     // odd tail: the second half of the last accumulator pair holds no row
     if (nrow % C::RPB != 0) {
         umma_publish_desc<K>(s, nrow, lane, -1, 0, 0.0f, 0.0f);
-        if (lane == 0) ptx::mbar_arrive(&s.acc_full[buf]);
         ++nrow;
     }
     // end-of-work descriptors: one empty pair per solver group
     for (int i = 0; i < C::NG * C::RPB; ++i, ++nrow) umma_publish_desc<K>(s, nrow, lane, -1, 0, 0.0f, 0.0f);
+}
+
+// ---- mma warp: nothing but tcgen05 issue ------------------------------------------------------
+__device__ __forceinline__ uint64_t desc_from_words(uint32_t lo, uint32_t hi) {
+    uint64_t d;
+    asm("mov.b64 %0, {%1, %2};" : "=l"(d) : "r"(lo), "r"(hi));
+    return d;
+}
+
+template <int K>
+__device__ __forceinline__ void umma_role_mma(const RowStepParams& p, const UmmaSmem& s, int lane) {
+    using C = UmmaCfg<K>;
+    (void)p;
+    const uint32_t tmem = *s.tmem_base;
+    constexpr uint32_t IDESC_HQ = ptx::idesc_bf16_mn(K, K + 16);   // B = [hi | q atom's 16 columns]
+    constexpr uint32_t IDESC_LO = ptx::idesc_bf16_mn(K, K);        // B = lo
+    constexpr uint32_t SBO = C::NA * 1024;             // K-atom (8 ratings) stride
+    constexpr uint32_t LBO = 1024;                     // MN-atom (64 factors) stride
+    constexpr uint32_t LO_OFF = (C::HI_ATOMS + 1) * 1024;
+    // descriptor template: everything but the 14-bit start address
+    const uint64_t tmpl = ptx::smem_desc(0u, LBO, SBO, ptx::SWZ_128B);
+    const uint32_t d_hiword = (uint32_t)(tmpl >> 32);
+    const uint32_t d_loword = (uint32_t)tmpl;
+    const uint32_t stage0 = ptx::smem_u32(s.stages) >> 4;
+    uint32_t nrow = 0;                                 // rows started so far
+    uint32_t buf = 0, d_main = 0;
+    bool first = true;
+    for (uint32_t sg = 0;; ++sg) {
+        const uint32_t slot = sg % C::STAGES, ph = (sg / C::STAGES) & 1;
+        ptx::mbar_wait(&s.prep_full[slot], ph, 13, (int)sg);
+        const int flags = s.sflags[slot];
+        if (flags & HDR_END) break;
+        if (flags & HDR_FIRST) {
+            const uint32_t pr = nrow / C::RPB, h = nrow % C::RPB;
+            buf = pr % C::NBUF;
+            if (h == 0) ptx::mbar_wait(&s.acc_empty[buf], ((pr / C::NBUF) & 1) ^ 1, 3, (int)nrow);   // drained by its solver group
+            d_main = tmem + buf * C::ACC_STRIDE + ((h * 16u) << 16);
+            first = true;
+        }
+        ptx::tc_fence_after();
+        if (lane == 0) {
+            const uint32_t w0 = d_loword + stage0 + slot * (uint32_t)(C::STAGE_STRIDE >> 4);
+#pragma unroll
+            for (int ks = 0; ks < UM_R / 16; ++ks) {
+                const uint64_t hi_desc = desc_from_words(w0 + ks * (2 * SBO >> 4), d_hiword);
+                const uint64_t lo_desc = desc_from_words(w0 + ks * (2 * SBO >> 4) + (LO_OFF >> 4), d_hiword);
+                // [A | c s] += hi^T [hi | q] + lo^T [hi | q] + hi^T lo : TMEM lane i = row i of A, then (F^T q, F^T 1)
+                ptx::umma_bf16(d_main, hi_desc, hi_desc, IDESC_HQ, (first && ks == 0) ? 0u : 1u);
+                ptx::umma_bf16(d_main, lo_desc, hi_desc, IDESC_HQ, 1u);
+                ptx::umma_bf16(d_main, hi_desc, lo_desc, IDESC_LO, 1u);
+            }
+            ptx::umma_commit(&s.empty[slot]);                        // stage reusable once these MMAs finish
+            if (flags & HDR_LAST) ptx::umma_commit(&s.acc_full[buf]);
+        }
+        __syncwarp();
+        first = false;
+        if (flags & HDR_LAST) ++nrow;
+    }
+    // odd tail: the second half of the last accumulator pair holds no row
+    if (nrow % C::RPB != 0) {
+        if (lane == 0) ptx::mbar_arrive(&s.acc_full[buf]);
+    }
 }
 
 // ---- solver groups ----------------------------------------------------------------------------
@@ -403,8 +437,7 @@ __device__ __forceinline__ void umma_role_solver(const RowStepParams& p, const U
     const int r = C::RPW * q + seg;                    // matrix row owned by this thread
     const int col_bar = 1 + 2 * g, phase_bar = 2 + 2 * g;
     const uint32_t tmem = *s.tmem_base;
-    float* cb = s.mats + (size_t)(g * C::RPB + h) * C::MAT_FLOATS;
-    float* xb = cb + ldl_cols_floats<K>() + K;
+    const uint32_t cbs = ptx::smem_u32(s.mats + (size_t)(g * C::RPB + h) * C::MAT_FLOATS);
     float* red = s.red + (size_t)g * 4 * C::RPB * 4;
     int32_t* bad = s.bad + g * C::RPB + h;
     double acc_d = 0.0, acc_d2 = 0.0;                  // fused residual statistics (thread r == 0 of each matrix)
@@ -447,9 +480,9 @@ __device__ __forceinline__ void umma_role_solver(const RowStepParams& p, const U
         ptx::mbar_arrive(&s.acc_empty[buf]);           // accumulator buffer free for the next rows
         const float c_r = d2[0] + d2[1], s_r = d2[2];
 
-        const bool ok = L::factor(a, c_r - bias_old * s_r, ridge, r, q, cb, col_bar);
+        const bool ok = L::factor(a, c_r - bias_old * s_r, ridge, r, q, cbs, col_bar);
         if (!ok && valid) *bad = 1;
-        const float x = L::backsolve(r, q, seg, cb, xb, phase_bar);    // barriers inside publish *bad too
+        const float x = L::backsolve(r, q, seg, cbs, phase_bar);       // barriers inside publish *bad too
 
         // s.x, c.x, x.x over the matrix: segment shuffle, then the 4 warps through shared memory
         float v0 = s_r * x, v1 = c_r * x, v2 = x * x;
@@ -514,6 +547,7 @@ __global__ void __launch_bounds__(UmmaCfg<K>::THREADS, 1) row_step_umma_kernel(c
         }
         for (int i = 0; i < C::STAGES; ++i) {
             ptx::mbar_init(&s.full[i], UM_GATHER_WARPS * 32);
+            ptx::mbar_init(&s.prep_full[i], 1);
             ptx::mbar_init(&s.empty[i], 1);
         }
         for (int i = 0; i < C::NBUF; ++i) {
@@ -538,8 +572,10 @@ __global__ void __launch_bounds__(UmmaCfg<K>::THREADS, 1) row_step_umma_kernel(c
         if (K == 128) asm volatile("setmaxnreg.dec.sync.aligned.u32 56;");
         if (warp == C::WARP_META) {
             umma_role_meta<K>(p, s, lane);
-        } else if (warp < C::WARP_MMA) {
+        } else if (warp < C::WARP_PREP) {
             umma_role_gather<K>(p, s, H, (warp - C::WARP_GATHER0) * 32 + lane);
+        } else if (warp == C::WARP_PREP) {
+            umma_role_prep<K>(p, s, lane);
         } else if (warp == C::WARP_MMA) {
             umma_role_mma<K>(p, s, lane);
         }
