@@ -383,8 +383,6 @@ __device__ __forceinline__ void umma_role_mma(const RowStepParams& p, const Umma
     constexpr uint32_t LO_OFF = (C::HI_ATOMS + 1) * 1024;
     // descriptor template: everything but the 14-bit start address
     const uint64_t tmpl = ptx::smem_desc(0u, LBO, SBO, ptx::SWZ_128B);
-    const uint32_t d_hiword = (uint32_t)(tmpl >> 32);
-    const uint32_t d_loword = (uint32_t)tmpl;
     const uint32_t stage0 = ptx::smem_u32(s.stages) >> 4;
     uint32_t nrow = 0;                                 // rows started so far
     uint32_t buf = 0, d_main = 0;
@@ -402,12 +400,12 @@ __device__ __forceinline__ void umma_role_mma(const RowStepParams& p, const Umma
             first = true;
         }
         ptx::tc_fence_after();
-        if (lane == 0) {
-            const uint32_t w0 = d_loword + stage0 + slot * (uint32_t)(C::STAGE_STRIDE >> 4);
+        if (ptx::elect_one()) {
+            const uint64_t d0 = tmpl + (uint64_t)(stage0 + slot * (uint32_t)(C::STAGE_STRIDE >> 4));
 #pragma unroll
             for (int ks = 0; ks < UM_R / 16; ++ks) {
-                const uint64_t hi_desc = desc_from_words(w0 + ks * (2 * SBO >> 4), d_hiword);
-                const uint64_t lo_desc = desc_from_words(w0 + ks * (2 * SBO >> 4) + (LO_OFF >> 4), d_hiword);
+                const uint64_t hi_desc = d0 + (uint64_t)(ks * (2 * SBO >> 4));
+                const uint64_t lo_desc = hi_desc + (uint64_t)(LO_OFF >> 4);
                 // [A | c s] += hi^T [hi | q] + lo^T [hi | q] + hi^T lo : TMEM lane i = row i of A, then (F^T q, F^T 1)
                 ptx::umma_bf16(d_main, hi_desc, hi_desc, IDESC_HQ, (first && ks == 0) ? 0u : 1u);
                 ptx::umma_bf16(d_main, lo_desc, hi_desc, IDESC_HQ, 1u);

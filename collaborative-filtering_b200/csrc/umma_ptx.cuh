@@ -69,6 +69,21 @@ __device__ __forceinline__ void cp_async16_zfill(uint32_t smem_dst, const void* 
 }
 __device__ __forceinline__ void fence_proxy_async() { asm volatile("fence.proxy.async.shared::cta;" ::: "memory"); }
 
+// one lane of the (converged) warp; ptxas recognises elect.sync and keeps the tcgen05 operands of the
+// elected region in uniform registers instead of emitting a per-active-lane issue loop
+__device__ __forceinline__ bool elect_one() {
+    uint32_t pred = 0;
+    asm volatile(
+        "{\n"
+        ".reg .b32 rx;\n"
+        ".reg .pred px;\n"
+        "elect.sync rx|px, 0xffffffff;\n"
+        "@px mov.s32 %0, 1;\n"
+        "}\n"
+        : "+r"(pred));
+    return pred != 0;
+}
+
 // ---- tcgen05 ---------------------------------------------------------------------
 __device__ __forceinline__ void tmem_alloc(uint32_t* smem_dst, uint32_t ncols) {   // whole warp
     asm volatile("tcgen05.alloc.cta_group::1.sync.aligned.shared::cta.b32 [%0], %1;" ::"r"(smem_u32(smem_dst)),
