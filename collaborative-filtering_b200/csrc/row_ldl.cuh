@@ -47,7 +47,7 @@ __host__ __device__ constexpr int ldl_cols_floats() { return K * K / 2 + 2 * K; 
 // interleaved matrices of a k=64 group sit 16 banks apart
 template <int K>
 __host__ __device__ constexpr int ldl_mat_floats() {
-    const int raw = ldl_cols_floats<K>() + 2 * K;
+    const int raw = ldl_cols_floats<K>() + 2 * K + 2 * (4 * K + 4);   // columns | z | x | raw-row scratch (2 buffers)
     return ((raw + 31) / 32) * 32 + 16;
 }
 
@@ -57,89 +57,133 @@ __device__ __forceinline__ float fast_rcp(float d) {
     return r * fmaf(-d, r, 2.0f);             // one Newton step: < 1 ulp
 }
 
+__device__ __forceinline__ float rcp_approx(float d) {
+    float r;
+    asm("rcp.approx.ftz.f32 %0, %1;" : "=f"(r) : "f"(d));
+    return r;
+}
+
 __device__ __forceinline__ void named_bar_sync(int id, int nthr) {
     asm volatile("bar.sync %0, %1;" ::"r"(id), "r"(nthr) : "memory");
 }
 __device__ __forceinline__ void named_bar_arrive(int id, int nthr) {
     asm volatile("bar.arrive %0, %1;" ::"r"(id), "r"(nthr) : "memory");
 }
-__device__ __forceinline__ float lds_f32(uint32_t a) {
-    float v;
-    asm volatile("ld.shared.f32 %0, [%1];" : "=f"(v) : "r"(a) : "memory");
-    return v;
+// Shared-memory accessors on 32-bit .shared addresses.  The pointer is rebuilt with
+// cvta.shared->generic, which NVVM's address-space inference folds back into LDS/STS, so
+// the compiler can batch the loads ahead of the FFMAs (volatile asm loads would pin each
+// LDS right in front of its consumers and expose its latency sixteen times per column).
+__device__ __forceinline__ const float* smem_ptr(uint32_t a) {
+    return reinterpret_cast<const float*>(__cvta_shared_to_generic((size_t)a));
 }
-__device__ __forceinline__ float4 lds_f32x4(uint32_t a) {
-    float4 v;
-    asm volatile("ld.shared.v4.f32 {%0,%1,%2,%3}, [%4];" : "=f"(v.x), "=f"(v.y), "=f"(v.z), "=f"(v.w) : "r"(a) : "memory");
-    return v;
-}
-__device__ __forceinline__ void sts_f32(uint32_t a, float v) {
-    asm volatile("st.shared.f32 [%0], %1;" ::"r"(a), "f"(v) : "memory");
+__device__ __forceinline__ float lds_f32(uint32_t a) { return *smem_ptr(a); }
+__device__ __forceinline__ float4 lds_f32x4(uint32_t a) { return *reinterpret_cast<const float4*>(smem_ptr(a)); }
+__device__ __forceinline__ void sts_f32(uint32_t a, float v) { *const_cast<float*>(smem_ptr(a)) = v; }
+
+// predicated store: one STS under a predicate, never a branch (lanes of a warp differ in `on`)
+__device__ __forceinline__ void sts_f32_if(uint32_t a, float v, bool on) {
+    asm volatile(
+        "{\n"
+        ".reg .pred p;\n"
+        "setp.ne.b32 p, %2, 0;\n"
+        "@p st.shared.f32 [%0], %1;\n"
+        "}\n" ::"r"(a), "f"(v), "r"((int)on)
+        : "memory");
 }
 
 template <int K, int RPW>
 struct Ldl {
     static constexpr int NW = K / RPW;       // warps per group (4)
+    static constexpr int RAWSZ = 4 * K + 4;  // floats of one raw-row scratch buffer: rho[4][K] | rhs[4]
     static_assert(NW == 4, "a solver group is the four TMEM lane quadrants");
 
-    // Four column steps J = j0 .. j0+3 (j0 % 4 == 0) on a row window of W registers:
-    // a[c] holds the row's entry for column j0 + c.  The last step writes its update four
-    // registers down, so after the call a[c] holds column j0 + 4 + c: the code of a step
-    // never depends on J, every register index is static, and the loop stays rolled — the
-    // whole factorisation is a few KB of instructions that live in the instruction cache
-    // (a fully unrolled column loop is >100 KB of straight-line code and ran
-    // instruction-fetch bound).  nthr = threads of the warps that still own a row >= j0.
-    // `last` (warp-uniform): j0 + 3 is this warp's last row — publish, arrive, no update.
+    // Four columns J = j0 .. j0+3 (j0 % 4 == 0) in ONE barrier ("block pivot") on a row window of W
+    // registers: a[c] holds the row's entry for column j0 + c.
+    //   every row r >= j0 publishes its four raw entries rho_r = a[0..3] (and the four pivot rows
+    //   their rhs); barrier; every thread reads the 4 x 4 pivot block P (+ its rhs), factors it
+    //   redundantly in registers (P = L4 D4 L4^T), forward-substitutes its own four entries
+    //   (u_k = l_rk d_k go to the column store, t_k = l_rk), and applies the rank-4 update in terms
+    //   of the RAW published rows:  a[c] -= (t L4^-1) . rho_c  — the same four FFMAs per element as
+    //   four single-column steps, fed by the same broadcast LDS.128s, with a quarter of the barriers
+    //   and of the latency chain.  The update writes four registers down, so the window slides, every
+    //   register index is static and the loop over blocks stays rolled (instruction-cache resident).
+    // nthr = threads of the warps that still own a row >= j0.  `last` (warp-uniform): j0 + 3 is this
+    // warp's last row — its pivot rows are all in this warp, nothing below them is ours to update.
     template <int W>
     static __device__ __forceinline__ void body4(float (&a)[K], float& rhs, bool& ok, const float ridge,
                                                  const int r, const uint32_t cbs, const int j0, const int bar_id,
                                                  const int nthr, const bool last) {
         const int g = j0 >> 2;
         const uint32_t zb = cbs + 4u * ldl_cols_floats<K>();
+        const uint32_t raw = zb + 8u * K + (uint32_t)(g & 1) * (4u * RAWSZ);                // raw[parity][4][K] | zraw[4]
         const uint32_t S4 = 4u * (uint32_t)(K - 4 * g);                                  // column stride (bytes)
         const uint32_t col0 = cbs + 4u * (uint32_t)(4 * g * K - 8 * g * (g - 1) - 4 * g);   // element (i, j0) at col0 + 4 i
+        const int dr = r - j0;                                                           // row position relative to the block
 #pragma unroll
-        for (int s = 0; s < 4; ++s) {
-            const int J = j0 + s;
-            const uint32_t cj = col0 + (uint32_t)s * S4;
-            {
-                const float d = a[s] + ridge;
-                if (r >= J) sts_f32(cj + 4u * r, r == J ? d : a[s]);
-                if (r == J) {
-                    sts_f32(zb + 4u * J, rhs);
-                    ok = d > 0.0f;
-                }
-            }
-            if (s == 3 && last) {
-                if (nthr > 32) named_bar_arrive(bar_id, nthr);
-                return;
-            }
+        for (int s = 0; s < 4; ++s) a[s] += (dr == s) ? ridge : 0.0f;
+#pragma unroll
+        for (int s = 0; s < 4; ++s) sts_f32_if(raw + 4u * (uint32_t)(s * K + r), a[s], dr >= 0);
+        sts_f32_if(raw + 4u * (uint32_t)(4 * K + dr), rhs, (unsigned)dr < 4u);
+        if (last) {
+            if (nthr > 32) named_bar_arrive(bar_id, nthr);
+            __syncwarp();
+        } else {
             named_bar_sync(bar_id, nthr);
-            const float inv = fast_rcp(lds_f32(cj + 4u * J));
-            const float t = a[s] * inv;
-            rhs = fmaf(-t, lds_f32(zb + 4u * J), rhs);
-            const uint32_t cw = cj + 4u * j0;                  // window start: element (j0 + c, J) at cw + 4 c
-            if (s < 3) {
+        }
+        const float4 p0 = lds_f32x4(raw + 4u * (uint32_t)(0 * K + j0));     // P[0..3][0]
+        const float4 p1 = lds_f32x4(raw + 4u * (uint32_t)(1 * K + j0));     // P[0..3][1]
+        const float4 p2 = lds_f32x4(raw + 4u * (uint32_t)(2 * K + j0));
+        const float4 p3 = lds_f32x4(raw + 4u * (uint32_t)(3 * K + j0));
+        const float4 zr = lds_f32x4(raw + 4u * (uint32_t)(4 * K));
+        // 4 x 4 LDL^T of the pivot block (lower part of P; MUFU.RCP is good to 1 ulp)
+        const float d0 = p0.x, i0 = rcp_approx(d0);
+        const float l10 = p0.y * i0, l20 = p0.z * i0, l30 = p0.w * i0;
+        const float d1 = fmaf(-l10, p0.y, p1.y), i1 = rcp_approx(d1);
+        const float u21 = fmaf(-l20, p0.y, p1.z), u31 = fmaf(-l30, p0.y, p1.w);
+        const float l21 = u21 * i1, l31 = u31 * i1;
+        const float d2 = fmaf(-l21, u21, fmaf(-l20, p0.z, p2.z)), i2 = rcp_approx(d2);
+        const float u32 = fmaf(-l31, u21, fmaf(-l30, p0.z, p2.w));
+        const float l32 = u32 * i2;
+        const float d3 = fmaf(-l32, u32, fmaf(-l31, u31, fmaf(-l30, p0.w, p3.w))), i3 = rcp_approx(d3);
+        // own row: unscaled entries u_k = l_rk d_k and multipliers t_k = l_rk
+        const float u0 = a[0], t0 = u0 * i0;
+        const float u1 = fmaf(-t0, p0.y, a[1]), t1 = u1 * i1;
+        const float u2 = fmaf(-t1, u21, fmaf(-t0, p0.z, a[2])), t2 = u2 * i2;
+        const float u3 = fmaf(-t2, u32, fmaf(-t1, u31, fmaf(-t0, p0.w, a[3]))), t3 = u3 * i3;
+        sts_f32_if(col0 + 4u * r, u0, dr >= 0);
+        sts_f32_if(col0 + S4 + 4u * r, u1, dr >= 1);
+        sts_f32_if(col0 + 2u * S4 + 4u * r, u2, dr >= 2);
+        sts_f32_if(col0 + 3u * S4 + 4u * r, u3, dr >= 3);
+        // rhs of the block rows, forward-substituted; the pivot rows keep theirs in the z array
+        const float z0 = zr.x;
+        const float z1 = fmaf(-l10, z0, zr.y);
+        const float z2 = fmaf(-l21, z1, fmaf(-l20, z0, zr.z));
+        const float z3 = fmaf(-l32, z2, fmaf(-l31, z1, fmaf(-l30, z0, zr.w)));
+        {
+            const bool piv = (unsigned)dr < 4u;
+            const float zsel = dr == 0 ? z0 : (dr == 1 ? z1 : (dr == 2 ? z2 : z3));
+            const float dsel = dr == 0 ? d0 : (dr == 1 ? d1 : (dr == 2 ? d2 : d3));
+            sts_f32_if(zb + 4u * r, zsel, piv);
+            ok = piv ? (dsel > 0.0f) : ok;
+        }
+        if (last) return;
+        rhs = fmaf(-t3, z3, fmaf(-t2, z2, fmaf(-t1, z1, fmaf(-t0, z0, rhs))));
+        // tau = t L4^-1, so that l_r D4 l_c^T = tau . rho_c
+        const float w3 = t3;
+        const float w2 = fmaf(-w3, l32, t2);
+        const float w1 = fmaf(-w3, l31, fmaf(-w2, l21, t1));
+        const float w0 = fmaf(-w3, l30, fmaf(-w2, l20, fmaf(-w1, l10, t0)));
+        const uint32_t rw = raw + 4u * (uint32_t)j0;           // rho_{j0+c}[s] at rw + 4 (s K + c)
 #pragma unroll
-                for (int c = s + 1; c < 4; ++c) a[c] = fmaf(-t, lds_f32(cw + 4u * c), a[c]);
-#pragma unroll
-                for (int c4 = 4; c4 < W; c4 += 4) {
-                    const float4 v = lds_f32x4(cw + 4u * c4);
-                    a[c4 + 0] = fmaf(-t, v.x, a[c4 + 0]);
-                    a[c4 + 1] = fmaf(-t, v.y, a[c4 + 1]);
-                    a[c4 + 2] = fmaf(-t, v.z, a[c4 + 2]);
-                    a[c4 + 3] = fmaf(-t, v.w, a[c4 + 3]);
-                }
-            } else {
-#pragma unroll
-                for (int c4 = 4; c4 < W; c4 += 4) {
-                    const float4 v = lds_f32x4(cw + 4u * c4);
-                    a[c4 - 4] = fmaf(-t, v.x, a[c4 + 0]);
-                    a[c4 - 3] = fmaf(-t, v.y, a[c4 + 1]);
-                    a[c4 - 2] = fmaf(-t, v.z, a[c4 + 2]);
-                    a[c4 - 1] = fmaf(-t, v.w, a[c4 + 3]);
-                }
-            }
+        for (int c4 = 4; c4 < W; c4 += 4) {
+            const float4 v0 = lds_f32x4(rw + 4u * (uint32_t)(0 * K + c4));
+            const float4 v1 = lds_f32x4(rw + 4u * (uint32_t)(1 * K + c4));
+            const float4 v2 = lds_f32x4(rw + 4u * (uint32_t)(2 * K + c4));
+            const float4 v3 = lds_f32x4(rw + 4u * (uint32_t)(3 * K + c4));
+            a[c4 - 4] = fmaf(-w3, v3.x, fmaf(-w2, v2.x, fmaf(-w1, v1.x, fmaf(-w0, v0.x, a[c4 + 0]))));
+            a[c4 - 3] = fmaf(-w3, v3.y, fmaf(-w2, v2.y, fmaf(-w1, v1.y, fmaf(-w0, v0.y, a[c4 + 1]))));
+            a[c4 - 2] = fmaf(-w3, v3.z, fmaf(-w2, v2.z, fmaf(-w1, v1.z, fmaf(-w0, v0.z, a[c4 + 2]))));
+            a[c4 - 1] = fmaf(-w3, v3.w, fmaf(-w2, v2.w, fmaf(-w1, v1.w, fmaf(-w0, v0.w, a[c4 + 3]))));
         }
     }
 

@@ -165,6 +165,12 @@ int b200als_row_step(const b200als_step_args* a, b200als_stream_t stream) {
     return dispatch_ffma(p, s);
 }
 
+#ifdef B200ALS_TIMING
+int b200als_debug_timing(unsigned long long* out16_host) {
+    return cudaMemcpyFromSymbol(out16_host, b200als::g_timing, 16 * sizeof(unsigned long long)) == cudaSuccess ? 0 : -2;
+}
+#endif
+
 int b200als_graph_level_solve(int32_t k, const int32_t* level_rows, int64_t n_level, const float* chol,
                               const float* aux, const int64_t* sptr, const int32_t* sidx, const float* sval,
                               float alpha, float lam_bias, const float* lam_bias_row, float* V, int64_t ldv,

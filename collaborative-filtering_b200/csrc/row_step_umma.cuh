@@ -76,7 +76,10 @@ struct UmmaCfg {
     static constexpr int WARP_GATHER0 = SOLVER_WARPS + 1;
     static constexpr int WARP_PREP = SOLVER_WARPS + 1 + UM_GATHER_WARPS;
     static constexpr int WARP_MMA = WARP_PREP + 1;
-    static constexpr int THREADS = (K == 64) ? (WARP_MMA + 1) * 32 : (SOLVER_WARPS + 8) * 32;   // k=128: whole warpgroups
+    static constexpr int THREADS = (SOLVER_WARPS + 8) * 32;  // whole warpgroups: solvers | 7 producer warps + 1 idle
+    // setmaxnreg split of the CTA's register allocation (launch: 65536 / THREADS rounded down to 8)
+    static constexpr int REG_SOLVER = (K == 64) ? 128 : 200;
+    static constexpr int REG_PRODUCER = (K == 64) ? 48 : 56;
     static constexpr int MATS = NG * RPB;
     static constexpr int MAT_FLOATS = ldl_mat_floats<K>();
     static constexpr int RED_FLOATS = NG * 4 * RPB * 4;     // per group: [warp][matrix][4]
@@ -425,6 +428,12 @@ __device__ __forceinline__ void umma_role_mma(const RowStepParams& p, const Umma
 }
 
 // ---- solver groups ----------------------------------------------------------------------------
+#ifdef B200ALS_TIMING
+__device__ unsigned long long g_timing[16];
+#define TICK(i) do { if (blockIdx.x == 0 && threadIdx.x == 96) { const long long t__ = clock64(); tacc[i] += t__ - tlast; tlast = t__; } } while (0)
+#else
+#define TICK(i) do { } while (0)
+#endif
 template <int K>
 __device__ __forceinline__ void umma_role_solver(const RowStepParams& p, const UmmaSmem& s, int warp, int lane) {
     using C = UmmaCfg<K>;
@@ -439,6 +448,10 @@ __device__ __forceinline__ void umma_role_solver(const RowStepParams& p, const U
     float* red = s.red + (size_t)g * 4 * C::RPB * 4;
     int32_t* bad = s.bad + g * C::RPB + h;
     double acc_d = 0.0, acc_d2 = 0.0;                  // fused residual statistics (thread r == 0 of each matrix)
+#ifdef B200ALS_TIMING
+    long long tacc[8] = {0, 0, 0, 0, 0, 0, 0, 0};
+    long long tlast = clock64();
+#endif
 
     for (uint32_t pr = g;; pr += C::NG) {
         // descriptors of the rows in this accumulator buffer
@@ -448,6 +461,7 @@ __device__ __forceinline__ void umma_role_solver(const RowStepParams& p, const U
             const uint32_t n = n0 + hh;
             ptx::mbar_wait(&s.rd_full[n % UM_RD], (n / UM_RD) & 1, 8, (int)n);
         }
+        TICK(0);
         const RowDesc d0 = s.rd[n0 % UM_RD];
         const RowDesc dm = s.rd[(n0 + h) % UM_RD];
         named_bar_sync(phase_bar, 128);                // everyone holds its descriptor
@@ -463,6 +477,7 @@ __device__ __forceinline__ void umma_role_solver(const RowStepParams& p, const U
         const uint32_t buf = pr % C::NBUF;
         ptx::mbar_wait(&s.acc_full[buf], (pr / C::NBUF) & 1, 7, (int)pr);
         ptx::tc_fence_after();
+        TICK(1);
         const uint32_t trow = tmem + buf * C::ACC_STRIDE + ((uint32_t)(32 * q) << 16);
         float a[K];
 #pragma unroll
@@ -477,11 +492,14 @@ __device__ __forceinline__ void umma_role_solver(const RowStepParams& p, const U
         ptx::tc_fence_before();
         ptx::mbar_arrive(&s.acc_empty[buf]);           // accumulator buffer free for the next rows
         const float c_r = d2[0] + d2[1], s_r = d2[2];
+        TICK(2);
 
         const bool ok = L::factor(a, c_r - bias_old * s_r, ridge, r, q, cbs, col_bar);
         if (!ok && valid) *bad = 1;
+        TICK(3);
         const float x = L::backsolve(r, q, seg, cbs, phase_bar);       // barriers inside publish *bad too
 
+        TICK(4);
         // s.x, c.x, x.x over the matrix: segment shuffle, then the 4 warps through shared memory
         float v0 = s_r * x, v1 = c_r * x, v2 = x * x;
 #pragma unroll
@@ -522,7 +540,15 @@ __device__ __forceinline__ void umma_role_solver(const RowStepParams& p, const U
             }
         }
         named_bar_sync(phase_bar, 128);                // red / xb / columns free for the next pair
+        TICK(5);
+#ifdef B200ALS_TIMING
+        if (blockIdx.x == 0 && threadIdx.x == 96) tacc[6] += 1;
+#endif
     }
+#ifdef B200ALS_TIMING
+    if (blockIdx.x == 0 && threadIdx.x == 96)
+        for (int i = 0; i < 8; ++i) g_timing[i] = (unsigned long long)tacc[i];
+#endif
     if (p.stats && q == 0 && seg == 0) {
         atomicAdd(&p.stats[0], acc_d);
         atomicAdd(&p.stats[1], acc_d2);
@@ -564,10 +590,10 @@ __global__ void __launch_bounds__(UmmaCfg<K>::THREADS, 1) row_step_umma_kernel(c
     ptx::tc_fence_after();
 
     if (warp < C::SOLVER_WARPS) {
-        if (K == 128) asm volatile("setmaxnreg.inc.sync.aligned.u32 200;");
+        asm volatile("setmaxnreg.inc.sync.aligned.u32 %0;" ::"n"(C::REG_SOLVER));
         umma_role_solver<K>(p, s, warp, lane);
     } else {
-        if (K == 128) asm volatile("setmaxnreg.dec.sync.aligned.u32 56;");
+        asm volatile("setmaxnreg.dec.sync.aligned.u32 %0;" ::"n"(C::REG_PRODUCER));
         if (warp == C::WARP_META) {
             umma_role_meta<K>(p, s, lane);
         } else if (warp < C::WARP_PREP) {
