@@ -216,8 +216,9 @@ struct Ldl {
 
     // Back substitution.  Needs a group barrier (phase_bar) between blocks; ends with x_r
     // returned to thread r and stored in xb[r].  `seg` = lane % RPW.
-    static __device__ __forceinline__ float backsolve(const int r, const int q, const int seg, const uint32_t cbs,
-                                                      const int phase_bar) {
+    // lane_xor: 0, or RPW-1 when the lanes of a segment hold their rows in reverse order.
+    static __device__ __forceinline__ float backsolve(const int r, const int q, const int seg, const int lane_xor,
+                                                      const uint32_t cbs, const int phase_bar) {
         const uint32_t zb = cbs + 4u * ldl_cols_floats<K>();
         const uint32_t xb = zb + 4u * K;
         const int g = r >> 2, jj = r & 3;
@@ -237,7 +238,7 @@ struct Ldl {
 #pragma unroll
                 for (int ii = RPW - 1; ii >= 0; --ii) {
                     const float mine = acc * dinv;
-                    const float xi = __shfl_sync(0xffffffffu, mine, ii, RPW);
+                    const float xi = __shfl_sync(0xffffffffu, mine, ii ^ lane_xor, RPW);
                     if (seg < ii) acc = fmaf(-lt[ii], xi, acc);
                     if (seg == ii) x = mine;
                 }

@@ -442,6 +442,13 @@ __device__ __forceinline__ void umma_role_solver(const RowStepParams& p, const U
     const int h = lane / C::RPW;                       // matrix of the accumulator pair (k=64), else 0
     const int seg = lane % C::RPW;
     const int r = C::RPW * q + seg;                    // matrix row owned by this thread
+    // Odd groups eliminate in reverse order (the permuted system P A P^T, P = index reversal): the
+    // thread-per-row factorisation loads the LAST rows most, so alternating the direction spreads
+    // the heavy warps over quadrants 0 and 3 instead of piling them on one SM sub-partition.
+    const bool rev = (g & 1) != 0;
+    const int qe = rev ? 3 - q : q;                    // elimination-order block / row / lane segment
+    const int re = rev ? K - 1 - r : r;
+    const int sege = rev ? C::RPW - 1 - seg : seg;
     const int col_bar = 1 + 2 * g, phase_bar = 2 + 2 * g;
     const uint32_t tmem = *s.tmem_base;
     const uint32_t cbs = ptx::smem_u32(s.mats + (size_t)(g * C::RPB + h) * C::MAT_FLOATS);
@@ -480,12 +487,22 @@ __device__ __forceinline__ void umma_role_solver(const RowStepParams& p, const U
         TICK(1);
         const uint32_t trow = tmem + buf * C::ACC_STRIDE + ((uint32_t)(32 * q) << 16);
         float a[K];
+        if (!rev) {
 #pragma unroll
-        for (int c0 = 0; c0 < K; c0 += 16) {
-            float v[16];
-            ptx::tmem_ld16(trow + c0, v);
+            for (int c0 = 0; c0 < K; c0 += 16) {
+                float v[16];
+                ptx::tmem_ld16(trow + c0, v);
 #pragma unroll
-            for (int i = 0; i < 16; ++i) a[c0 + i] = v[i];
+                for (int i = 0; i < 16; ++i) a[c0 + i] = v[i];
+            }
+        } else {
+#pragma unroll
+            for (int c0 = 0; c0 < K; c0 += 16) {
+                float v[16];
+                ptx::tmem_ld16(trow + c0, v);
+#pragma unroll
+                for (int i = 0; i < 16; ++i) a[K - 1 - c0 - i] = v[i];
+            }
         }
         float d2[4];
         ptx::tmem_ld4(trow + C::D2_COL, d2);
@@ -494,10 +511,10 @@ __device__ __forceinline__ void umma_role_solver(const RowStepParams& p, const U
         const float c_r = d2[0] + d2[1], s_r = d2[2];
         TICK(2);
 
-        const bool ok = L::factor(a, c_r - bias_old * s_r, ridge, r, q, cbs, col_bar);
+        const bool ok = L::factor(a, c_r - bias_old * s_r, ridge, re, qe, cbs, col_bar);
         if (!ok && valid) *bad = 1;
         TICK(3);
-        const float x = L::backsolve(r, q, seg, cbs, phase_bar);       // barriers inside publish *bad too
+        const float x = L::backsolve(re, qe, sege, rev ? C::RPW - 1 : 0, cbs, phase_bar);   // barriers inside publish *bad too
 
         TICK(4);
         // s.x, c.x, x.x over the matrix: segment shuffle, then the 4 warps through shared memory
