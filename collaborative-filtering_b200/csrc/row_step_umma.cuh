@@ -155,9 +155,34 @@ __device__ __forceinline__ void umma_carve(unsigned char* raw, UmmaSmem& s) {
     s.tmem_base = reinterpret_cast<uint32_t*>(s.bad + 16);
 }
 
+// shared-space loads (explicit .shared addressing: generic LD on the carved buffer takes the long-scoreboard path)
+__device__ __forceinline__ int4 lds_s32x4(uint32_t a) {
+    int4 v;
+    asm volatile("ld.shared.v4.s32 {%0,%1,%2,%3}, [%4];" : "=r"(v.x), "=r"(v.y), "=r"(v.z), "=r"(v.w) : "r"(a) : "memory");
+    return v;
+}
+__device__ __forceinline__ int32_t lds_s32(uint32_t a) {
+    int32_t v;
+    asm volatile("ld.shared.s32 %0, [%1];" : "=r"(v) : "r"(a) : "memory");
+    return v;
+}
+__device__ __forceinline__ float lds_f32v(uint32_t a) {
+    float v;
+    asm volatile("ld.shared.f32 %0, [%1];" : "=f"(v) : "r"(a) : "memory");
+    return v;
+}
+__device__ __forceinline__ void sts_s32(uint32_t a, int32_t v) {
+    asm volatile("st.shared.s32 [%0], %1;" ::"r"(a), "r"(v) : "memory");
+}
+__device__ __forceinline__ void sts_s32x4(uint32_t a, int4 v) {
+    asm volatile("st.shared.v4.s32 [%0], {%1,%2,%3,%4};" ::"r"(a), "r"(v.x), "r"(v.y), "r"(v.z), "r"(v.w) : "memory");
+}
 template <int K>
-__device__ __forceinline__ const StageHdr* stage_hdr(const UmmaSmem& s, uint32_t ms) {
-    return reinterpret_cast<const StageHdr*>(s.meta + (size_t)ms * UmmaCfg<K>::META_BYTES + 256);
+__device__ __forceinline__ StageHdr stage_hdr(const UmmaSmem& s, uint32_t ms) {
+    const int4 v = lds_s32x4(ptx::smem_u32(s.meta + (size_t)ms * UmmaCfg<K>::META_BYTES + 256));
+    StageHdr h;
+    h.live_n = v.x; h.row = v.y; h.flags = v.z; h.cnt = v.w;
+    return h;
 }
 
 // ---- meta warp: claims rows, streams (index, rating) + header of every stage --------------
@@ -220,7 +245,7 @@ __device__ __forceinline__ void umma_role_meta(const RowStepParams& p, const Umm
                     h.row = row;
                     h.flags = (t0 == beg ? HDR_FIRST : 0) | (t0 + UM_R >= end ? HDR_LAST : 0);
                     h.cnt = (int32_t)(end - beg);
-                    *reinterpret_cast<int4*>(mt + 256) = *reinterpret_cast<const int4*>(&h);
+                    sts_s32x4(ptx::smem_u32(mt + 256), make_int4(h.live_n, h.row, h.flags, h.cnt));
                     ptx::mbar_arrive(&s.meta_full[ms]);    // release: header visible to the waiters
                 }
             }
@@ -236,7 +261,7 @@ __device__ __forceinline__ void umma_role_meta(const RowStepParams& p, const Umm
         if (lane == 0) {
             StageHdr h;
             h.live_n = 0; h.row = -1; h.flags = HDR_END; h.cnt = 0;
-            *reinterpret_cast<int4*>(mt + 256) = *reinterpret_cast<const int4*>(&h);
+            sts_s32x4(ptx::smem_u32(mt + 256), make_int4(h.live_n, h.row, h.flags, h.cnt));
             ptx::mbar_arrive(&s.meta_full[ms]);
         }
     }
@@ -255,12 +280,12 @@ __device__ __forceinline__ void umma_role_gather(const RowStepParams& p, const U
         const uint32_t slot = sg % C::STAGES, ph = (sg / C::STAGES) & 1;
         const uint32_t ms = sg % C::META, mph = (sg / C::META) & 1;
         ptx::mbar_wait(&s.meta_full[ms], mph, 2, (int)sg);
-        const StageHdr* hd = stage_hdr<K>(s, ms);
-        if (hd->flags & HDR_END) break;
-        const int live_n = hd->live_n;
+        const StageHdr hd = stage_hdr<K>(s, ms);
+        if (hd.flags & HDR_END) break;
+        const int live_n = hd.live_n;
         unsigned char* st = s.stages + (size_t)slot * C::STAGE_STRIDE;
         ptx::mbar_wait(&s.empty[slot], ph ^ 1, 11, (int)sg);
-        const int32_t* idx_s = reinterpret_cast<const int32_t*>(s.meta + (size_t)ms * C::META_BYTES);
+        const uint32_t idx_a = ptx::smem_u32(s.meta + (size_t)ms * C::META_BYTES);
         const uint32_t st_addr = ptx::smem_u32(st);
 #pragma unroll
         for (int j = 0; j < C::N_MB * 2; ++j) {
@@ -269,7 +294,7 @@ __device__ __forceinline__ void umma_role_gather(const RowStepParams& p, const U
             const int kb = atom / C::N_MB, mb = atom % C::N_MB;
             const int rating = kb * 8 + rr;
             const bool live = rating < live_n;
-            const int32_t ix = idx_s[rating];
+            const int32_t ix = lds_s32(idx_a + 4u * (uint32_t)rating);
             const unsigned char* src = H + (size_t)ix * C::REC_BYTES + mb * 128 + ch * 16;
             const int at = mb < C::HI_ATOMS ? mb : mb + 1;         // the q atom sits between the hi and lo atoms
             const uint32_t dst = st_addr + (uint32_t)((kb * C::NA + at) * 1024 + rr * 128 + ((ch ^ rr) << 4));
@@ -277,7 +302,7 @@ __device__ __forceinline__ void umma_role_gather(const RowStepParams& p, const U
         }
         if (gtid < UM_R) {
             const bool live = gtid < live_n;
-            const int32_t ix = idx_s[gtid];
+            const int32_t ix = lds_s32(idx_a + 4u * (uint32_t)gtid);
             asm volatile("cp.async.ca.shared.global [%0], [%1], 4, %2;" ::"r"(ptx::smem_u32(s.bias + slot * 128 + gtid * 4)),
                          "l"(p.bias_other + ix), "r"(live ? 4u : 0u)
                          : "memory");
@@ -296,7 +321,7 @@ __device__ __forceinline__ void umma_publish_desc(const UmmaSmem& s, uint32_t n,
     if (lane == 0) {
         RowDesc d;
         d.row = row; d.cnt = cnt; d.tsum = tsum; d.qq = qq;
-        *reinterpret_cast<int4*>(&s.rd[rd]) = *reinterpret_cast<const int4*>(&d);
+        sts_s32x4(ptx::smem_u32(&s.rd[rd]), make_int4(d.row, d.cnt, __float_as_int(d.tsum), __float_as_int(d.qq)));
         ptx::mbar_arrive(&s.rd_full[rd]);                  // release
     }
     __syncwarp();
@@ -315,12 +340,12 @@ __device__ __forceinline__ void umma_role_prep(const RowStepParams& p, const Umm
         const uint32_t slot = sg % C::STAGES, ph = (sg / C::STAGES) & 1;
         const uint32_t ms = sg % C::META, mph = (sg / C::META) & 1;
         ptx::mbar_wait(&s.meta_full[ms], mph, 4, (int)sg);
-        const StageHdr* hd = stage_hdr<K>(s, ms);
-        const int flags = hd->flags, live_n = hd->live_n, hrow = hd->row, hcnt = hd->cnt;
+        const StageHdr hd = stage_hdr<K>(s, ms);
+        const int flags = hd.flags, live_n = hd.live_n, hrow = hd.row, hcnt = hd.cnt;
         if (flags & HDR_END) {
             ptx::mbar_wait(&s.empty[slot], ph ^ 1, 12, (int)sg);      // the slot's previous MMAs (and flag read) are done
             if (lane == 0) {
-                s.sflags[slot] = HDR_END;
+                sts_s32(ptx::smem_u32(s.sflags + slot), HDR_END);
                 ptx::mbar_arrive(&s.prep_full[slot]);
             }
             break;
@@ -328,8 +353,8 @@ __device__ __forceinline__ void umma_role_prep(const RowStepParams& p, const Umm
         if (flags & HDR_FIRST) { tsum = 0.0f; qq = 0.0f; }
         ptx::mbar_wait(&s.full[slot], ph, 5, (int)sg);
         const bool live = lane < live_n;
-        const float v = reinterpret_cast<const float*>(s.meta + (size_t)ms * C::META_BYTES + 128)[lane];
-        const float bo = reinterpret_cast<const float*>(s.bias + slot * 128)[lane];
+        const float v = lds_f32v(ptx::smem_u32(s.meta + (size_t)ms * C::META_BYTES + 128) + 4u * (uint32_t)lane);
+        const float bo = lds_f32v(ptx::smem_u32(s.bias + slot * 128) + 4u * (uint32_t)lane);
         const float q = live ? v - (mu + bo) : 0.0f;
         tsum += q;
         qq = fmaf(q, q, qq);
@@ -342,12 +367,12 @@ __device__ __forceinline__ void umma_role_prep(const RowStepParams& p, const Umm
         c0.y = *reinterpret_cast<const uint32_t*>(&w1);
         c0.z = 0u; c0.w = 0u;
         unsigned char* qa = s.stages + (size_t)slot * C::STAGE_STRIDE + q_off;
-        *reinterpret_cast<uint4*>(qa + (rr << 4)) = c0;                              // columns 0..7  (chunk 0 ^ rr)
-        *reinterpret_cast<uint4*>(qa + ((rr ^ 1) << 4)) = make_uint4(0u, 0u, 0u, 0u);   // columns 8..15 (chunk 1 ^ rr)
+        sts_s32x4(ptx::smem_u32(qa + (rr << 4)), make_int4((int)c0.x, (int)c0.y, 0, 0));    // columns 0..7  (chunk 0 ^ rr)
+        sts_s32x4(ptx::smem_u32(qa + ((rr ^ 1) << 4)), make_int4(0, 0, 0, 0));              // columns 8..15 (chunk 1 ^ rr)
         ptx::fence_proxy_async();
         __syncwarp();
         if (lane == 0) {
-            s.sflags[slot] = flags;
+            sts_s32(ptx::smem_u32(s.sflags + slot), flags);
             ptx::mbar_arrive(&s.prep_full[slot]);                    // release: atom + flags visible to the mma warp
             ptx::mbar_arrive(&s.meta_empty[ms]);                     // idx/hdr (gather) and val (this warp) consumed
         }
@@ -393,7 +418,7 @@ __device__ __forceinline__ void umma_role_mma(const RowStepParams& p, const Umma
     for (uint32_t sg = 0;; ++sg) {
         const uint32_t slot = sg % C::STAGES, ph = (sg / C::STAGES) & 1;
         ptx::mbar_wait(&s.prep_full[slot], ph, 13, (int)sg);
-        const int flags = s.sflags[slot];
+        const int flags = lds_s32(ptx::smem_u32(s.sflags + slot));
         if (flags & HDR_END) break;
         if (flags & HDR_FIRST) {
             const uint32_t pr = nrow / C::RPB, h = nrow % C::RPB;
@@ -469,8 +494,11 @@ __device__ __forceinline__ void umma_role_solver(const RowStepParams& p, const U
             ptx::mbar_wait(&s.rd_full[n % UM_RD], (n / UM_RD) & 1, 8, (int)n);
         }
         TICK(0);
-        const RowDesc d0 = s.rd[n0 % UM_RD];
-        const RowDesc dm = s.rd[(n0 + h) % UM_RD];
+        const int4 d0v = lds_s32x4(ptx::smem_u32(&s.rd[n0 % UM_RD]));
+        const int4 dmv = lds_s32x4(ptx::smem_u32(&s.rd[(n0 + h) % UM_RD]));
+        RowDesc d0, dm;
+        d0.row = d0v.x; d0.cnt = d0v.y; d0.tsum = __int_as_float(d0v.z); d0.qq = __int_as_float(d0v.w);
+        dm.row = dmv.x; dm.cnt = dmv.y; dm.tsum = __int_as_float(dmv.z); dm.qq = __int_as_float(dmv.w);
         named_bar_sync(phase_bar, 128);                // everyone holds its descriptor
         if (q == 0 && seg == 0) ptx::mbar_arrive(&s.rd_empty[(n0 + h) % UM_RD]);
         if (d0.row < 0) break;                         // end of work (rows fill buffers in order)
