@@ -1,26 +1,24 @@
-// row_ldl.cuh — register-resident, thread-per-row LDL^T solve fed straight from TMEM
+// row_ldl.cuh — thread-per-row LDL^T solve fed straight from TMEM
 // (A6/A7/A11: the per-row normal equations, als.py:426-428 / 455-461, helpers.py:19-20).
 //
-// The tcgen05 Gram kernel leaves row i of the k x k normal matrix in TMEM lane i, so a
-// tcgen05.ld hands every solver thread one full matrix row in registers.  The
-// factorisation never copies the matrix to shared memory:
+// The tcgen05 Gram kernel leaves row i of the k x k normal matrix in TMEM lane i.  The matrix
+// STAYS in TMEM while it is factored: warp q owns rows [RPW q, RPW (q+1)) and runs phases
+// p = 0..q; in phase p a thread pulls only the RPW columns [RPW p, RPW (p+1)) of its row out of
+// TMEM (tcgen05.ld), so the register footprint is one RPW-wide window, not a k-wide row.
 //
-//   for column j (fully unrolled, register indices static):
-//     every thread r >= j publishes its entry a_r[j] (still unscaled: l_rj * d_j) into
-//     the packed column store; thread j also publishes z_j (forward-substituted rhs);
-//     ONE named barrier among the warps that still own a row >= j;
-//     t = a_r[j] / d_j;  rhs_r -= t * z_j;  a_r[c] -= t * col_j[c]  for c in (j, warp max row]
-//     (col_j read as broadcast LDS.128: one shared-memory wavefront per four FFMAs).
+//   phase p, per thread (row r >= RPW p):
+//     left-looking: window -= sum over finished columns j < RPW p of l_rj d_j l_cj, four
+//       columns per step: own entries u_rj (LDS.32), 1/d_j (broadcast LDS.128), column
+//       entries u_cj for the window rows c (broadcast LDS.128) — no barrier, pure FFMA stream;
+//     in-block: RPW/4 "block pivot" steps of four columns (body4): publish the raw entries,
+//       ONE named barrier among the warps that still own a row >= j, redundant 4 x 4 LDL^T,
+//       rank-4 update of the rest of the window written four registers down (the window slides,
+//       every register index is static, the loop stays rolled and instruction-cache resident).
 //
-// The column loop is ROLLED: four columns per iteration, the fourth writing its update four
-// registers down so that the window slides and every register index stays static.  Warp q
-// owns rows [RPW q, RPW (q+1)): it runs phases p = 0..q of RPW columns on a window of
-// RPW (q+1-p) registers, then leaves the column barrier to the warps above it.
-//
-// The column store doubles as L^T for the back substitution (thread j owns column j:
-// x_j = (z_j - sum_{i>j} col_j[i] x_i) / d_j), done block by block: the owning warp
-// resolves its RPW rows with shuffles, the warps below fold the block in with per-thread
-// LDS.128.  Shared memory per matrix: k^2/2 + 2k floats of columns + z + x.
+// The packed column store (unscaled u_rj = l_rj d_j) doubles as L^T for the back substitution
+// (thread j owns column j: x_j = (z_j - sum_{i>j} col_j[i] x_i) / d_j), done block by block: the
+// owning warp resolves its RPW rows with shuffles, the warps below fold the block in with
+// per-thread LDS.128.  Shared memory per matrix: k^2/2 + 2k floats of columns + z + x + 1/d.
 //
 // A solver group is 4 warps = the 4 TMEM lane quadrants.  k = 128: one matrix per group,
 // RPW = 32 rows per warp.  k = 64: the Gram MMAs run with M = 64, whose accumulator uses
@@ -43,11 +41,11 @@ __host__ __device__ constexpr int ldl_col_base(int j) {
 }
 template <int K>
 __host__ __device__ constexpr int ldl_cols_floats() { return K * K / 2 + 2 * K; }
-// per-matrix buffer: columns | z[K] | x[K] | pad — size = 16 (mod 32) floats so that the two
-// interleaved matrices of a k=64 group sit 16 banks apart
+// per-matrix buffer: columns | z[K] | x[K] | 1/d[K] | raw scratch | pad — size = 16 (mod 32) floats
+// so that the two interleaved matrices of a k=64 group sit 16 banks apart
 template <int K>
 __host__ __device__ constexpr int ldl_mat_floats() {
-    const int raw = ldl_cols_floats<K>() + 2 * K + 2 * (4 * K + 4);   // columns | z | x | raw-row scratch (2 buffers)
+    const int raw = ldl_cols_floats<K>() + 3 * K + 2 * (4 * K + 4);   // columns | z | x | 1/d | raw-row scratch (2 buffers)
     return ((raw + 31) / 32) * 32 + 16;
 }
 
@@ -97,27 +95,62 @@ struct Ldl {
     static constexpr int RAWSZ = 4 * K + 4;  // floats of one raw-row scratch buffer: rho[4][K] | rhs[4]
     static_assert(NW == 4, "a solver group is the four TMEM lane quadrants");
 
-    // Four columns J = j0 .. j0+3 (j0 % 4 == 0) in ONE barrier ("block pivot") on a row window of W
-    // registers: a[c] holds the row's entry for column j0 + c.
+    // byte offsets inside a matrix buffer
+    static constexpr uint32_t Z_OFF = 4u * ldl_cols_floats<K>();
+    static constexpr uint32_t X_OFF = Z_OFF + 4u * K;
+    static constexpr uint32_t INV_OFF = X_OFF + 4u * K;
+    static constexpr uint32_t RAW_OFF = INV_OFF + 4u * K;
+
+    // element (i, 4 g) of the column store at col_block(g) + 4 i; the block's columns are S4(g) bytes apart
+    static __device__ __forceinline__ uint32_t col_block(const uint32_t cbs, const int g) {
+        return cbs + 4u * (uint32_t)(4 * g * K - 8 * g * (g - 1) - 4 * g);
+    }
+
+    // Left-looking step: fold the finished columns 4 jb .. 4 jb + 3 into the window
+    // a[c] = A[r][c0 + c], c0 % 4 == 0, c0 > 4 jb + 3:  a[c] -= sum_k (u_rk / d_k) u_(c0+c)k.
+    static __device__ __forceinline__ void left4(float (&a)[RPW], const int r, const uint32_t cbs, const int jb,
+                                                 const int c0) {
+        const uint32_t S4 = 4u * (uint32_t)(K - 4 * jb);
+        const uint32_t col0 = col_block(cbs, jb);
+        const float4 inv = lds_f32x4(cbs + INV_OFF + 16u * (uint32_t)jb);
+        const float t0 = lds_f32(col0 + 4u * r) * inv.x;
+        const float t1 = lds_f32(col0 + S4 + 4u * r) * inv.y;
+        const float t2 = lds_f32(col0 + 2u * S4 + 4u * r) * inv.z;
+        const float t3 = lds_f32(col0 + 3u * S4 + 4u * r) * inv.w;
+        const uint32_t cw = col0 + 4u * (uint32_t)c0;
+#pragma unroll
+        for (int c4 = 0; c4 < RPW; c4 += 4) {
+            const float4 v0 = lds_f32x4(cw + 4u * c4);
+            const float4 v1 = lds_f32x4(cw + S4 + 4u * c4);
+            const float4 v2 = lds_f32x4(cw + 2u * S4 + 4u * c4);
+            const float4 v3 = lds_f32x4(cw + 3u * S4 + 4u * c4);
+            a[c4 + 0] = fmaf(-t3, v3.x, fmaf(-t2, v2.x, fmaf(-t1, v1.x, fmaf(-t0, v0.x, a[c4 + 0]))));
+            a[c4 + 1] = fmaf(-t3, v3.y, fmaf(-t2, v2.y, fmaf(-t1, v1.y, fmaf(-t0, v0.y, a[c4 + 1]))));
+            a[c4 + 2] = fmaf(-t3, v3.z, fmaf(-t2, v2.z, fmaf(-t1, v1.z, fmaf(-t0, v0.z, a[c4 + 2]))));
+            a[c4 + 3] = fmaf(-t3, v3.w, fmaf(-t2, v2.w, fmaf(-t1, v1.w, fmaf(-t0, v0.w, a[c4 + 3]))));
+        }
+    }
+
+    // Four columns J = j0 .. j0+3 (j0 % 4 == 0) in ONE barrier ("block pivot") on the row window:
+    // a[c] holds the row's entry for column j0 + c (c < the columns left in this phase).
     //   every row r >= j0 publishes its four raw entries rho_r = a[0..3] (and the four pivot rows
     //   their rhs); barrier; every thread reads the 4 x 4 pivot block P (+ its rhs), factors it
     //   redundantly in registers (P = L4 D4 L4^T), forward-substitutes its own four entries
     //   (u_k = l_rk d_k go to the column store, t_k = l_rk), and applies the rank-4 update in terms
     //   of the RAW published rows:  a[c] -= (t L4^-1) . rho_c  — the same four FFMAs per element as
     //   four single-column steps, fed by the same broadcast LDS.128s, with a quarter of the barriers
-    //   and of the latency chain.  The update writes four registers down, so the window slides, every
-    //   register index is static and the loop over blocks stays rolled (instruction-cache resident).
+    //   and of the latency chain.  The update writes four registers down, so the window slides.
     // nthr = threads of the warps that still own a row >= j0.  `last` (warp-uniform): j0 + 3 is this
-    // warp's last row — its pivot rows are all in this warp, nothing below them is ours to update.
-    template <int W>
-    static __device__ __forceinline__ void body4(float (&a)[K], float& rhs, bool& ok, const float ridge,
+    // warp's last row — its pivot rows are all in this warp, nothing below them is ours to update;
+    // the warp then signs off on start_bar, which the warps below wait on before their next phase.
+    static __device__ __forceinline__ void body4(float (&a)[RPW], float& rhs, bool& ok, const float ridge,
                                                  const int r, const uint32_t cbs, const int j0, const int bar_id,
-                                                 const int nthr, const bool last) {
+                                                 const int start_bar, const int nthr, const bool last) {
         const int g = j0 >> 2;
-        const uint32_t zb = cbs + 4u * ldl_cols_floats<K>();
-        const uint32_t raw = zb + 8u * K + (uint32_t)(g & 1) * (4u * RAWSZ);                // raw[parity][4][K] | zraw[4]
+        const uint32_t zb = cbs + Z_OFF;
+        const uint32_t raw = cbs + RAW_OFF + (uint32_t)(g & 1) * (4u * RAWSZ);           // raw[parity][4][K] | zraw[4]
         const uint32_t S4 = 4u * (uint32_t)(K - 4 * g);                                  // column stride (bytes)
-        const uint32_t col0 = cbs + 4u * (uint32_t)(4 * g * K - 8 * g * (g - 1) - 4 * g);   // element (i, j0) at col0 + 4 i
+        const uint32_t col0 = col_block(cbs, g);                                         // element (i, j0) at col0 + 4 i
         const int dr = r - j0;                                                           // row position relative to the block
 #pragma unroll
         for (int s = 0; s < 4; ++s) a[s] += (dr == s) ? ridge : 0.0f;
@@ -163,10 +196,15 @@ struct Ldl {
             const bool piv = (unsigned)dr < 4u;
             const float zsel = dr == 0 ? z0 : (dr == 1 ? z1 : (dr == 2 ? z2 : z3));
             const float dsel = dr == 0 ? d0 : (dr == 1 ? d1 : (dr == 2 ? d2 : d3));
+            const float isel = dr == 0 ? i0 : (dr == 1 ? i1 : (dr == 2 ? i2 : i3));
             sts_f32_if(zb + 4u * r, zsel, piv);
+            sts_f32_if(cbs + INV_OFF + 4u * r, isel, piv);
             ok = piv ? (dsel > 0.0f) : ok;
         }
-        if (last) return;
+        if (last) {
+            if (nthr > 32) named_bar_arrive(start_bar, nthr);
+            return;
+        }
         rhs = fmaf(-t3, z3, fmaf(-t2, z2, fmaf(-t1, z1, fmaf(-t0, z0, rhs))));
         // tau = t L4^-1, so that l_r D4 l_c^T = tau . rho_c
         const float w3 = t3;
@@ -175,7 +213,7 @@ struct Ldl {
         const float w0 = fmaf(-w3, l30, fmaf(-w2, l20, fmaf(-w1, l10, t0)));
         const uint32_t rw = raw + 4u * (uint32_t)j0;           // rho_{j0+c}[s] at rw + 4 (s K + c)
 #pragma unroll
-        for (int c4 = 4; c4 < W; c4 += 4) {
+        for (int c4 = 4; c4 < RPW; c4 += 4) {
             const float4 v0 = lds_f32x4(rw + 4u * (uint32_t)(0 * K + c4));
             const float4 v1 = lds_f32x4(rw + 4u * (uint32_t)(1 * K + c4));
             const float4 v2 = lds_f32x4(rw + 4u * (uint32_t)(2 * K + c4));
@@ -187,29 +225,29 @@ struct Ldl {
         }
     }
 
-    // phase p = columns [RPW p, RPW (p+1)) on a window of W = RPW (q + 1 - p) registers
-    template <int W>
-    static __device__ __forceinline__ void phase(float (&a)[K], float& rhs, bool& ok, const float ridge, const int r,
-                                                 const uint32_t cbs, const int p, const int bar_id) {
-        const int nthr = 32 * (NW - p);
-#pragma unroll 1
-        for (int it = 0; it < RPW / 4; ++it)
-            body4<W>(a, rhs, ok, ridge, r, cbs, p * RPW + 4 * it, bar_id, nthr, W == RPW && it == RPW / 4 - 1);
-    }
-
-    // Factor + forward substitution.  a[] = this thread's matrix row (row position r in
-    // warp quadrant q), rhs = its right-hand-side entry, ridge is added on the pivot.
+    // Factor + forward substitution.  load_window(p, a, is_last) fills a[c] = A[r][RPW p + c] from
+    // TMEM (and releases the accumulator after this thread's last load); rhs = this row's
+    // right-hand-side entry, ridge is added on the pivot.  r / q = row and warp in ELIMINATION order.
     // Returns true if thread r's pivot was positive.
-    static __device__ __forceinline__ bool factor(float (&a)[K], float rhs, const float ridge, const int r,
-                                                  const int q, const uint32_t cbs, const int bar_id) {
+    template <class LoadWindow>
+    static __device__ __forceinline__ bool factor(float rhs, const float ridge, const int r, const int q,
+                                                  const uint32_t cbs, const int bar_id, const int start_bar,
+                                                  LoadWindow&& load_window) {
         bool ok = true;
+        float a[RPW];
 #pragma unroll 1
         for (int p = 0; p <= q; ++p) {
-            const int w = q + 1 - p;
-            if (w == 4) phase<4 * RPW>(a, rhs, ok, ridge, r, cbs, p, bar_id);
-            else if (w == 3) phase<3 * RPW>(a, rhs, ok, ridge, r, cbs, p, bar_id);
-            else if (w == 2) phase<2 * RPW>(a, rhs, ok, ridge, r, cbs, p, bar_id);
-            else phase<RPW>(a, rhs, ok, ridge, r, cbs, p, bar_id);
+            load_window(p, a, p == q);
+            const int nthr = 32 * (NW - p);
+            if (p > 0) {
+                named_bar_sync(start_bar, nthr + 32);          // phase p-1 fully in the column store
+#pragma unroll 1
+                for (int jb = 0; jb < p * (RPW / 4); ++jb) left4(a, r, cbs, jb, p * RPW);
+            }
+#pragma unroll 1
+            for (int it = 0; it < RPW / 4; ++it)
+                body4(a, rhs, ok, ridge, r, cbs, p * RPW + 4 * it, bar_id, start_bar, nthr,
+                      p == q && it == RPW / 4 - 1);
         }
         return ok;
     }
@@ -219,8 +257,8 @@ struct Ldl {
     // lane_xor: 0, or RPW-1 when the lanes of a segment hold their rows in reverse order.
     static __device__ __forceinline__ float backsolve(const int r, const int q, const int seg, const int lane_xor,
                                                       const uint32_t cbs, const int phase_bar) {
-        const uint32_t zb = cbs + 4u * ldl_cols_floats<K>();
-        const uint32_t xb = zb + 4u * K;
+        const uint32_t zb = cbs + Z_OFF;
+        const uint32_t xb = cbs + X_OFF;
         const int g = r >> 2, jj = r & 3;
         const uint32_t mycol = cbs + 4u * (uint32_t)(4 * g * K - 8 * g * (g - 1) + jj * (K - 4 * g) - 4 * g);
         const float dinv = fast_rcp(lds_f32(mycol + 4u * r));

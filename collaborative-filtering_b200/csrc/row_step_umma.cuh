@@ -64,8 +64,11 @@ struct UmmaCfg {
     static constexpr int STAGE_STRIDE = STAGE_DATA;         // data ring (1024-byte aligned atoms)
     static constexpr int META = 32;                         // (index, rating) ring: runs far ahead of the data ring
     static constexpr int META_BYTES = 288;                  // idx[32] int32 | val[32] float | StageHdr | pad
-    static constexpr int STAGES = (K == 64) ? 8 : 5;
-    static constexpr int NG = (K == 64) ? 3 : 2;            // solver groups (4 warps each)
+    static constexpr int STAGES = (K == 64) ? 6 : 4;
+#ifndef B200ALS_NG64
+#define B200ALS_NG64 4
+#endif
+    static constexpr int NG = (K == 64) ? B200ALS_NG64 : 3; // solver groups (4 warps each); 3 named barriers per group
     static constexpr int RPB = (K == 64) ? 2 : 1;           // rows per TMEM accumulator buffer
     static constexpr int RPW = (K == 64) ? 16 : 32;         // matrix rows per solver warp
     static constexpr int NBUF = (K == 64) ? 6 : 3;          // TMEM accumulator buffers
@@ -78,8 +81,11 @@ struct UmmaCfg {
     static constexpr int WARP_MMA = WARP_PREP + 1;
     static constexpr int THREADS = (SOLVER_WARPS + 8) * 32;  // whole warpgroups: solvers | 7 producer warps + 1 idle
     // setmaxnreg split of the CTA's register allocation (launch: 65536 / THREADS rounded down to 8)
-    static constexpr int REG_SOLVER = (K == 64) ? 128 : 200;
-    static constexpr int REG_PRODUCER = (K == 64) ? 48 : 56;
+    static constexpr int REG_PRODUCER = 48;
+    static constexpr int REG_LAUNCH = (65536 / THREADS) & ~7;
+    static constexpr int REG_SOLVER_RAW = ((REG_LAUNCH * THREADS - 256 * REG_PRODUCER) / (SOLVER_WARPS * 32)) & ~7;
+    static constexpr int REG_SOLVER = REG_SOLVER_RAW > 232 ? 232 : REG_SOLVER_RAW;
+    static_assert(3 * NG + 1 <= 16, "named barriers");
     static constexpr int MATS = NG * RPB;
     static constexpr int MAT_FLOATS = ldl_mat_floats<K>();
     static constexpr int RED_FLOATS = NG * 4 * RPB * 4;     // per group: [warp][matrix][4]
@@ -252,16 +258,15 @@ __device__ __forceinline__ void umma_role_meta(const RowStepParams& p, const Umm
         }
         nb = nb_n; row_l = row_n; beg_l = beg_n; end_l = end_n;
     }
-    // end-of-work stage
-    {
+    // end-of-work stages: one per gather warp (each walks its own stride of the stage sequence);
+    // the prep and mma warps stop at the first
+    for (int e = 0; e < UM_GATHER_WARPS; ++e, ++sg) {
         const uint32_t ms = sg % C::META, mph = (sg / C::META) & 1;
         ptx::mbar_wait(&s.meta_empty[ms], mph ^ 1, 1, (int)sg);
         unsigned char* mt = s.meta + (size_t)ms * C::META_BYTES;
         ptx::cp_async_mbar_arrive_noinc(&s.meta_full[ms]);
         if (lane == 0) {
-            StageHdr h;
-            h.live_n = 0; h.row = -1; h.flags = HDR_END; h.cnt = 0;
-            sts_s32x4(ptx::smem_u32(mt + 256), make_int4(h.live_n, h.row, h.flags, h.cnt));
+            sts_s32x4(ptx::smem_u32(mt + 256), make_int4(0, -1, HDR_END, 0));
             ptx::mbar_arrive(&s.meta_full[ms]);
         }
     }
@@ -269,42 +274,43 @@ __device__ __forceinline__ void umma_role_meta(const RowStepParams& p, const Umm
 }
 
 // ---- gather warps: 32 records (+ opposite biases) per stage into the swizzled MN-major tile ----
+// Warp w takes stages w, w + 4, ... whole: the per-stage fixed cost (two barrier waits, header) is a
+// latency chain, and four warps walking it in lock step on the same stage would bound the pipeline.
 template <int K>
 __device__ __forceinline__ void umma_role_gather(const RowStepParams& p, const UmmaSmem& s, const unsigned char* H,
-                                                 int gtid) {
+                                                 int w, int lane) {
     using C = UmmaCfg<K>;
-    const int rr = (gtid >> 3) & 7;        // rating inside its group of 8 == swizzle row
-    const int ch = gtid & 7;               // 16-byte chunk inside the 128-byte line
-    const int half = gtid >> 6;            // 0 / 1
-    for (uint32_t sg = 0;; ++sg) {
+    const int ch = lane & 7;               // 16-byte chunk inside the 128-byte line
+    const int r4 = lane >> 3;              // rating inside its group of 4
+    for (uint32_t sg = (uint32_t)w;; sg += UM_GATHER_WARPS) {
         const uint32_t slot = sg % C::STAGES, ph = (sg / C::STAGES) & 1;
         const uint32_t ms = sg % C::META, mph = (sg / C::META) & 1;
         ptx::mbar_wait(&s.meta_full[ms], mph, 2, (int)sg);
         const StageHdr hd = stage_hdr<K>(s, ms);
         if (hd.flags & HDR_END) break;
         const int live_n = hd.live_n;
-        unsigned char* st = s.stages + (size_t)slot * C::STAGE_STRIDE;
         ptx::mbar_wait(&s.empty[slot], ph ^ 1, 11, (int)sg);
         const uint32_t idx_a = ptx::smem_u32(s.meta + (size_t)ms * C::META_BYTES);
-        const uint32_t st_addr = ptx::smem_u32(st);
+        const uint32_t st_addr = ptx::smem_u32(s.stages + (size_t)slot * C::STAGE_STRIDE);
+        const int32_t ixb = lds_s32(idx_a + 4u * (uint32_t)lane);
 #pragma unroll
-        for (int j = 0; j < C::N_MB * 2; ++j) {
-            // chunk id c = gtid + 128 j  ->  (kb, mb) atom, line rr, chunk ch
-            const int atom = half + 2 * j;             // = c / 64
-            const int kb = atom / C::N_MB, mb = atom % C::N_MB;
-            const int rating = kb * 8 + rr;
+        for (int t = 0; t < UM_R / 4; ++t) {
+            const int rating = 4 * t + r4;             // = 8 kb + rr
+            const int kb = t >> 1, rr = (t & 1) * 4 + r4;
             const bool live = rating < live_n;
-            const int32_t ix = lds_s32(idx_a + 4u * (uint32_t)rating);
-            const unsigned char* src = H + (size_t)ix * C::REC_BYTES + mb * 128 + ch * 16;
-            const int at = mb < C::HI_ATOMS ? mb : mb + 1;         // the q atom sits between the hi and lo atoms
-            const uint32_t dst = st_addr + (uint32_t)((kb * C::NA + at) * 1024 + rr * 128 + ((ch ^ rr) << 4));
-            ptx::cp_async16_zfill(dst, src, live ? 16u : 0u);
+            const int32_t ix = __shfl_sync(0xffffffffu, ixb, rating);
+            const unsigned char* src = H + (size_t)ix * C::REC_BYTES + ch * 16;
+            const uint32_t dst = st_addr + (uint32_t)(kb * C::NA * 1024 + rr * 128 + ((ch ^ rr) << 4));
+#pragma unroll
+            for (int mb = 0; mb < C::N_MB; ++mb) {
+                const int at = mb < C::HI_ATOMS ? mb : mb + 1;     // the q atom sits between the hi and lo atoms
+                ptx::cp_async16_zfill(dst + at * 1024, src + mb * 128, live ? 16u : 0u);
+            }
         }
-        if (gtid < UM_R) {
-            const bool live = gtid < live_n;
-            const int32_t ix = lds_s32(idx_a + 4u * (uint32_t)gtid);
-            asm volatile("cp.async.ca.shared.global [%0], [%1], 4, %2;" ::"r"(ptx::smem_u32(s.bias + slot * 128 + gtid * 4)),
-                         "l"(p.bias_other + ix), "r"(live ? 4u : 0u)
+        {
+            const bool live = lane < live_n;
+            asm volatile("cp.async.ca.shared.global [%0], [%1], 4, %2;" ::"r"(ptx::smem_u32(s.bias + slot * 128 + lane * 4)),
+                         "l"(p.bias_other + ixb), "r"(live ? 4u : 0u)
                          : "memory");
         }
         ptx::cp_async_mbar_arrive_noinc(&s.full[slot]);
@@ -474,7 +480,7 @@ __device__ __forceinline__ void umma_role_solver(const RowStepParams& p, const U
     const int qe = rev ? 3 - q : q;                    // elimination-order block / row / lane segment
     const int re = rev ? K - 1 - r : r;
     const int sege = rev ? C::RPW - 1 - seg : seg;
-    const int col_bar = 1 + 2 * g, phase_bar = 2 + 2 * g;
+    const int col_bar = 1 + 3 * g, phase_bar = 2 + 3 * g, start_bar = 3 + 3 * g;
     const uint32_t tmem = *s.tmem_base;
     const uint32_t cbs = ptx::smem_u32(s.mats + (size_t)(g * C::RPB + h) * C::MAT_FLOATS);
     float* red = s.red + (size_t)g * 4 * C::RPB * 4;
@@ -514,32 +520,32 @@ __device__ __forceinline__ void umma_role_solver(const RowStepParams& p, const U
         ptx::tc_fence_after();
         TICK(1);
         const uint32_t trow = tmem + buf * C::ACC_STRIDE + ((uint32_t)(32 * q) << 16);
-        float a[K];
-        if (!rev) {
-#pragma unroll
-            for (int c0 = 0; c0 < K; c0 += 16) {
-                float v[16];
-                ptx::tmem_ld16(trow + c0, v);
-#pragma unroll
-                for (int i = 0; i < 16; ++i) a[c0 + i] = v[i];
-            }
-        } else {
-#pragma unroll
-            for (int c0 = 0; c0 < K; c0 += 16) {
-                float v[16];
-                ptx::tmem_ld16(trow + c0, v);
-#pragma unroll
-                for (int i = 0; i < 16; ++i) a[K - 1 - c0 - i] = v[i];
-            }
-        }
         float d2[4];
         ptx::tmem_ld4(trow + C::D2_COL, d2);
-        ptx::tc_fence_before();
-        ptx::mbar_arrive(&s.acc_empty[buf]);           // accumulator buffer free for the next rows
         const float c_r = d2[0] + d2[1], s_r = d2[2];
         TICK(2);
 
-        const bool ok = L::factor(a, c_r - bias_old * s_r, ridge, re, qe, cbs, col_bar);
+        // the matrix stays in TMEM; every phase pulls one RPW-column window of this thread's row
+        auto load_window = [&](const int ph, float (&w)[C::RPW], const bool is_last) {
+            const uint32_t c0 = (uint32_t)(rev ? K - C::RPW * (ph + 1) : C::RPW * ph);
+#pragma unroll
+            for (int cc = 0; cc < C::RPW; cc += 16) {
+                float v[16];
+                ptx::tmem_ld16(trow + c0 + cc, v);
+                if (!rev) {
+#pragma unroll
+                    for (int i = 0; i < 16; ++i) w[cc + i] = v[i];
+                } else {
+#pragma unroll
+                    for (int i = 0; i < 16; ++i) w[C::RPW - 1 - cc - i] = v[i];
+                }
+            }
+            if (is_last) {
+                ptx::tc_fence_before();
+                ptx::mbar_arrive(&s.acc_empty[buf]);   // this thread is done with the accumulator
+            }
+        };
+        const bool ok = L::factor(c_r - bias_old * s_r, ridge, re, qe, cbs, col_bar, start_bar, load_window);
         if (!ok && valid) *bad = 1;
         TICK(3);
         const float x = L::backsolve(re, qe, sege, rev ? C::RPW - 1 : 0, cbs, phase_bar);   // barriers inside publish *bad too
@@ -615,7 +621,7 @@ __global__ void __launch_bounds__(UmmaCfg<K>::THREADS, 1) row_step_umma_kernel(c
             ptx::mbar_init(&s.meta_empty[i], 1);
         }
         for (int i = 0; i < C::STAGES; ++i) {
-            ptx::mbar_init(&s.full[i], UM_GATHER_WARPS * 32);
+            ptx::mbar_init(&s.full[i], 32);
             ptx::mbar_init(&s.prep_full[i], 1);
             ptx::mbar_init(&s.empty[i], 1);
         }
@@ -642,7 +648,7 @@ __global__ void __launch_bounds__(UmmaCfg<K>::THREADS, 1) row_step_umma_kernel(c
         if (warp == C::WARP_META) {
             umma_role_meta<K>(p, s, lane);
         } else if (warp < C::WARP_PREP) {
-            umma_role_gather<K>(p, s, H, (warp - C::WARP_GATHER0) * 32 + lane);
+            umma_role_gather<K>(p, s, H, warp - C::WARP_GATHER0, lane);
         } else if (warp == C::WARP_PREP) {
             umma_role_prep<K>(p, s, lane);
         } else if (warp == C::WARP_MMA) {
