@@ -42,6 +42,9 @@ WORKLOADS = {
     "c4k64": (480_189, 17_770, 100_000_000, 64),
     "tiny": (3000, 2000, 200_000, 64),
 }
+# DRAM bytes (read + write) of one row_step launch, from `ncu --set full` on a single GPU; None = not captured.
+# Source: profiles/r01_ncu_c3_umma_k64_v5.txt (the algorithmic bytes are mostly served by the 126 MB L2).
+NCU_DRAM_BYTES = {("c3", "user"): 198.4e6, ("c3", "item"): 209.2e6}
 WORKLOAD_NAMES = {"c1": "c1_bundled_shape_uv_biases", "c3": "c3_movielens20m_shape",
                   "c4": "c4_netflix_shape", "c4k64": "c4_netflix_shape_k64", "tiny": "tiny_debug"}
 HYPER = dict(lambda_u=5.0, lambda_v=5.0, lambda_bu=3.0, lambda_bi=3.0)
@@ -311,6 +314,8 @@ def b200_arm(args):
     dom = max(("user", "item"), key=lambda p: phases[p])
     ach = cand[dom] / (phases[dom] * 1e-3) / 1e9 if phases[dom] > 0 else 0.0
     b_iter = cand["user"] + cand["item"]
+    # dram__bytes_read.sum + dram__bytes_write.sum of that launch from one `ncu --set full` capture (profiles/)
+    traffic = NCU_DRAM_BYTES.get((wl, dom)) if world == 1 and args.path == "auto" else None
     out = {
         "metric": "ALS ratings/sec/iter (= nnz x ALS iterations/sec)", "value": value, "unit": "ratings/s",
         "iterations_per_sec": 1e3 / ms_per_step,
@@ -327,7 +332,7 @@ def b200_arm(args):
                         "K iterations, D2H of U,V,b_u,b_i"},
         "gpu_launches": int(launches),
         "roofline": {"bound": "hbm", "kernel": f"row_step ({dom} half-step)", "achieved": ach, "peak": peak,
-                     "unit": "GB/s", "frac": ach / peak, "traffic": None, "peak_source": peak_kind,
+                     "unit": "GB/s", "frac": ach / peak, "traffic": traffic, "peak_source": peak_kind,
                      "algorithmic_bytes_per_launch": cand[dom],
                      "iteration_frac": b_iter / (ms_per_step * 1e-3) / 1e9 / peak},
         "phase_ms": phases,

@@ -32,6 +32,13 @@
 
 namespace b200als {
 
+#ifdef B200ALS_TIMING
+__device__ unsigned long long g_timing[16];
+#define LDL_TICK(i) do { if (blockIdx.x == 0 && threadIdx.x == 96) { const long long t__ = clock64(); g_timing[i] += (unsigned long long)(t__ - tl__); tl__ = t__; } } while (0)
+#else
+#define LDL_TICK(i) do { } while (0)
+#endif
+
 // element (i, j), i >= j, of the packed column store sits at ldl_col_base(j) + i
 // (column j is allocated from row 4*(j/4), so every column keeps i % 4 alignment for LDS.128)
 template <int K>
@@ -236,18 +243,25 @@ struct Ldl {
         bool ok = true;
         float a[RPW];
 #pragma unroll 1
+#ifdef B200ALS_TIMING
+        long long tl__ = clock64();
+#endif
         for (int p = 0; p <= q; ++p) {
             load_window(p, a, p == q);
+            LDL_TICK(8);
             const int nthr = 32 * (NW - p);
             if (p > 0) {
                 named_bar_sync(start_bar, nthr + 32);          // phase p-1 fully in the column store
+                LDL_TICK(9);
 #pragma unroll 1
                 for (int jb = 0; jb < p * (RPW / 4); ++jb) left4(a, r, cbs, jb, p * RPW);
+                LDL_TICK(10);
             }
 #pragma unroll 1
             for (int it = 0; it < RPW / 4; ++it)
                 body4(a, rhs, ok, ridge, r, cbs, p * RPW + 4 * it, bar_id, start_bar, nthr,
                       p == q && it == RPW / 4 - 1);
+            LDL_TICK(11);
         }
         return ok;
     }

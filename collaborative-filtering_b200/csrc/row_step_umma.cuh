@@ -460,7 +460,6 @@ __device__ __forceinline__ void umma_role_mma(const RowStepParams& p, const Umma
 
 // ---- solver groups ----------------------------------------------------------------------------
 #ifdef B200ALS_TIMING
-__device__ unsigned long long g_timing[16];
 #define TICK(i) do { if (blockIdx.x == 0 && threadIdx.x == 96) { const long long t__ = clock64(); tacc[i] += t__ - tlast; tlast = t__; } } while (0)
 #else
 #define TICK(i) do { } while (0)
@@ -489,6 +488,8 @@ __device__ __forceinline__ void umma_role_solver(const RowStepParams& p, const U
 #ifdef B200ALS_TIMING
     long long tacc[8] = {0, 0, 0, 0, 0, 0, 0, 0};
     long long tlast = clock64();
+    if (blockIdx.x == 0 && threadIdx.x == 96)
+        for (int i = 8; i < 12; ++i) g_timing[i] = 0;
 #endif
 
     for (uint32_t pr = g;; pr += C::NG) {
@@ -599,6 +600,7 @@ __device__ __forceinline__ void umma_role_solver(const RowStepParams& p, const U
 #ifdef B200ALS_TIMING
     if (blockIdx.x == 0 && threadIdx.x == 96)
         for (int i = 0; i < 8; ++i) g_timing[i] = (unsigned long long)tacc[i];
+    // g_timing[8..11] (window load / start barrier / left-looking / in-block) accumulate inside Ldl::factor
 #endif
     if (p.stats && q == 0 && seg == 0) {
         atomicAdd(&p.stats[0], acc_d);

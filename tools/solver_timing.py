@@ -23,7 +23,9 @@ for it in range(2):
     out = (C.c_ulonglong * 16)()
     fn(out)
     v = [out[i] for i in range(7)]
+    sub = [out[i] for i in range(8, 12)]
     pairs = max(v[6], 1)
-    print("iter", it, "(item step timing, last launch)", {nm: round(v[i] / pairs) for i, nm in enumerate(names[:6])}, "pairs", v[6])
+    print("iter", it, "(item step timing, last launch)", {nm: round(v[i] / pairs) for i, nm in enumerate(names[:6])}, "pairs", v[6],
+          "factor split", dict(zip(["win_ld", "start_bar", "left", "inblock"], [round(x / pairs) for x in sub])))
 ses.collect_phase_times()
 print({p_: np.mean(t) for p_, t in ses.phase_ms.items() if t})
