@@ -371,18 +371,17 @@ class FitSession:
         self.lam_bu = float(np.float32(model.lambda_bu + EPS))
         self.lam_bi = float(np.float32(float(model.lambda_bi) + EPS))
 
-        # ---- schedules: longest rows first; each rank keeps its contiguous slab ----
+        # ---- schedules: longest rows first, dealt round-robin over the ranks (dist.py) ----
         u_order, u_nonempty = row_schedule(rt.indptr)
         i_order, i_nonempty = row_schedule(rt.cindptr)
+        self.ulo, self.uhi = shard.my_range(m)          # contiguous split, residual reduction only
+        self.ilo, self.ihi = shard.my_range(n)
         if shard.active:
-            self.ulo, self.uhi = shard.my_range(m)
-            self.ilo, self.ihi = shard.my_range(n)
-            uo = u_order[:u_nonempty]
-            self.u_list = uo[(uo >= self.ulo) & (uo < self.uhi)].contiguous()
-            io = i_order[:i_nonempty]
-            self.i_list = io[(io >= self.ilo) & (io < self.ihi)].contiguous()
+            uo, io = u_order[:u_nonempty], i_order[:i_nonempty]
+            self.u_list, self.i_list = shard.deal(uo), shard.deal(io)
+            self.u_plan = shard.plan_exchange(uo, m)    # row m / n of the replicas is the dummy row
+            self.i_plan = shard.plan_exchange(io, n)
         else:
-            self.ulo, self.uhi, self.ilo, self.ihi = 0, m, 0, n
             self.u_list, self.i_list = u_order[:u_nonempty], i_order[:i_nonempty]
         if use_graph:
             self.i_list = i_order[:i_nonempty]      # the Gauss–Seidel sweep is not sharded (§8e)
@@ -481,8 +480,8 @@ class FitSession:
         self._step(rt.indptr, rt.indices, rt.vals, m, self.u_list, self.Z_d, n, self.b_i_d, self.reg_user, None,
                    self.lam_bu, self.U_d, self.b_u_d, _lib.STEP_SOLVE)
         if shard.active:
-            shard.all_gather_rows(self.U_d, m)
-            shard.all_gather_rows(self.b_u_d, m)
+            shard.exchange_rows(self.U_d, self.u_plan)
+            shard.exchange_rows(self.b_u_d, self.u_plan)
         # (2) items (als.py:436-466); the item step ignores the feature term
         self._mark("item")
         if self.use_graph:
@@ -506,8 +505,8 @@ class FitSession:
                        self.reg_item_d, self.lam_bi, self.V_d, self.b_i_d, _lib.STEP_SOLVE,
                        stats=self.acc if fused else None)
             if shard.active:
-                shard.all_gather_rows(self.V_d, n)
-                shard.all_gather_rows(self.b_i_d, n)
+                shard.exchange_rows(self.V_d, self.i_plan)
+                shard.exchange_rows(self.b_i_d, self.i_plan)
         # (3) W_f (als.py:468-501)
         self._mark("wstep")
         if names and ((it % model.update_w_every == 0) or (it == self.n_iters - 1)):

@@ -1,13 +1,21 @@
 """Row sharding of the two ALS half-steps across the GPUs of one box (§8e).
 
 One process per GPU (torchrun).  Each half-step's rows are independent
-(als.py:414-433; 436-466 without the graph), so rank r solves a contiguous
-slab of users, then of items; the freshly solved slab of factors and biases is
-exchanged with one NCCL all-gather over NVLink, in place inside the replica
-every rank keeps (gathers touch arbitrary rows, so U/V/b_u/b_i are replicated).
-Slabs have equal row counts (the replica is padded to a multiple of the world
-size) so a single `all_gather_into_tensor` moves them.  Residual sums are
-combined with one float64 all-reduce per iteration.
+(als.py:414-433; 436-466 without the graph), so the rows are dealt out to the
+ranks and the freshly solved factors and biases are exchanged with one NCCL
+all-gather over NVLink per array, in place inside the replica every rank keeps
+(gathers touch arbitrary rows, so U/V/b_u/b_i are replicated).
+
+Partition: the non-empty rows sorted longest first (the kernel's own schedule)
+are dealt round-robin, rank r taking entries r, r + world, ...  Every rank
+therefore holds the same length distribution — the same number of rows (solver
+work) and, to within one row per round, the same number of ratings (gather /
+Gram work) — which contiguous equal-row slabs do not give on popularity-skewed
+data.  The solved rows travel packed: index_select -> all_gather_into_tensor ->
+index_copy_ through a precomputed permutation; the padding slots of the last
+round point at one dummy row appended to each replica.
+
+Residual sums are combined with one float64 all-reduce per iteration.
 
 `torch.distributed` is plumbing only; with a `gloo` group on CPU tensors the
 same code paths run in the CPU test-suite.
@@ -18,6 +26,14 @@ from dataclasses import dataclass
 
 import torch
 import torch.distributed as td
+
+
+@dataclass
+class ExchangePlan:
+    """perm[r * cnt + j] = row solved by rank r in its slot j (or the dummy row)."""
+    perm: torch.Tensor     # int64 [world * cnt]
+    mine: torch.Tensor     # int64 [cnt]  == perm[rank * cnt : (rank + 1) * cnt]
+    cnt: int
 
 
 @dataclass
@@ -37,35 +53,48 @@ class Shard:
         return Shard()
 
     # ---- partition ---------------------------------------------------------
-    def slab_rows(self, n_rows: int) -> int:
-        """Rows per rank (replicas are padded to world * slab_rows)."""
-        return (n_rows + self.world - 1) // self.world
-
     def padded_rows(self, n_rows: int) -> int:
-        return self.slab_rows(n_rows) * self.world
+        """Rows of a replica: one dummy row behind the real ones when sharded."""
+        return n_rows + 1 if self.active else n_rows
 
     def my_range(self, n_rows: int):
-        """[lo, hi) of real rows owned by this rank (hi clipped to n_rows)."""
-        s = self.slab_rows(n_rows)
+        """[lo, hi): contiguous equal split of the rows (used for the residual reduction)."""
+        s = (n_rows + self.world - 1) // self.world
         lo = min(self.rank * s, n_rows)
         return lo, min(lo + s, n_rows)
 
+    def deal(self, order: torch.Tensor, rank: int | None = None) -> torch.Tensor:
+        """This rank's share of a schedule: entries rank, rank + world, ..."""
+        r = self.rank if rank is None else rank
+        return order[r::self.world].contiguous()
+
+    def plan_exchange(self, order: torch.Tensor, dummy_row: int) -> ExchangePlan:
+        n, w = int(order.numel()), self.world
+        cnt = max((n + w - 1) // w, 1)
+        slot = torch.arange(w * cnt, device=order.device, dtype=torch.int64)
+        src = (slot // cnt) + (slot % cnt) * w             # position in `order`
+        valid = src < n
+        if n > 0:
+            rows = order.to(torch.int64)[src.clamp(max=n - 1)]
+        else:
+            rows = torch.zeros_like(src)
+        perm = torch.where(valid, rows, torch.full_like(rows, dummy_row))
+        return ExchangePlan(perm, perm[self.rank * cnt:(self.rank + 1) * cnt].contiguous(), cnt)
+
     # ---- collectives -------------------------------------------------------
-    def all_gather_rows(self, full: torch.Tensor, n_rows: int) -> None:
-        """In-place all-gather of each rank's slab of `full` (rows padded)."""
+    def exchange_rows(self, full: torch.Tensor, plan: ExchangePlan) -> None:
+        """Every rank's solved rows of `full` ([rows(+1 dummy), ...]) land in every replica."""
         if not self.active:
             return
-        s = self.slab_rows(n_rows)
-        assert full.shape[0] == s * self.world, "replica must be padded to world * slab_rows"
-        mine = full[self.rank * s:(self.rank + 1) * s]
+        send = full.index_select(0, plan.mine)
+        recv = torch.empty((self.world * plan.cnt,) + tuple(full.shape[1:]), dtype=full.dtype, device=full.device)
         if full.is_cuda:
-            td.all_gather_into_tensor(full, mine, group=self.group)
+            td.all_gather_into_tensor(recv, send, group=self.group)
         else:  # gloo: list form
-            parts = [full[r * s:(r + 1) * s] for r in range(self.world)]
-            gathered = [torch.empty_like(mine) for _ in range(self.world)]
-            td.all_gather(gathered, mine.contiguous(), group=self.group)
-            for dst, src in zip(parts, gathered):
-                dst.copy_(src)
+            parts = [torch.empty_like(send) for _ in range(self.world)]
+            td.all_gather(parts, send, group=self.group)
+            recv = torch.cat(parts, 0)
+        full.index_copy_(0, plan.perm, recv)
 
     def all_reduce_sum(self, t: torch.Tensor) -> None:
         if self.active:

@@ -152,6 +152,7 @@ def test_synth_is_deterministic_and_well_formed():
 
 
 def test_shard_partition_covers_rows():
+    import torch
     from b200als import Shard
     for n_rows in (1, 7, 8, 9, 1000):
         for world in (1, 2, 3, 8):
@@ -160,8 +161,22 @@ def test_shard_partition_covers_rows():
                 s = Shard(r, world)
                 lo, hi = s.my_range(n_rows)
                 seen += list(range(lo, hi))
-                assert s.padded_rows(n_rows) % world == 0 and s.padded_rows(n_rows) >= n_rows
+                assert s.padded_rows(n_rows) == n_rows + (1 if world > 1 else 0)
             assert seen == list(range(n_rows))
+            # the dealt schedule: every entry exactly once, counts differ by at most one,
+            # and the exchange permutation lists rank r's rows in its slots (padding -> dummy row)
+            order = torch.randperm(n_rows)
+            dealt = [Shard(r, world).deal(order) for r in range(world)]
+            assert sorted(torch.cat(dealt).tolist()) == list(range(n_rows))
+            assert max(d.numel() for d in dealt) - min(d.numel() for d in dealt) <= 1
+            for r in range(world):
+                plan = Shard(r, world).plan_exchange(order, n_rows)
+                assert plan.perm.numel() == world * plan.cnt
+                for q in range(world):
+                    slots = plan.perm[q * plan.cnt:(q + 1) * plan.cnt]
+                    assert slots[:dealt[q].numel()].tolist() == dealt[q].tolist()
+                    assert (slots[dealt[q].numel():] == n_rows).all()
+                assert torch.equal(plan.mine, plan.perm[r * plan.cnt:(r + 1) * plan.cnt])
 
 
 _GLOO_WORKER = r'''
@@ -173,15 +188,21 @@ td.init_process_group("gloo", init_method="tcp://127.0.0.1:" + os.environ["PORT"
                       rank=int(os.environ["RANK"]), world_size=2)
 s = b200als.Shard.from_env()
 m, ld = 7, 4
-full = torch.zeros(s.padded_rows(m), ld)
-lo, hi = s.my_range(m)
-full[lo:hi] = torch.arange(lo, hi, dtype=torch.float32)[:, None] + 0.25 * s.rank
-s.all_gather_rows(full, m)
-want = torch.zeros_like(full)
-for r in range(2):
-    rl, rh = b200als.Shard(r, 2).my_range(m)
-    want[rl:rh] = torch.arange(rl, rh, dtype=torch.float32)[:, None] + 0.25 * r
-assert torch.equal(full, want), (full, want)
+order = torch.tensor([5, 0, 3, 6, 1])                  # rows 2 and 4 are empty: nobody solves them
+for shape in ((s.padded_rows(m), ld), (s.padded_rows(m),)):
+    full = torch.full(shape, -1.0)
+    full[m] = 0.0
+    mine = s.deal(order)
+    val = mine.to(torch.float32) + 0.25 * s.rank
+    full[mine] = val[:, None] if len(shape) == 2 else val
+    s.exchange_rows(full, s.plan_exchange(order, m))
+    want = torch.full(shape, -1.0)
+    want[m] = 0.0
+    for r in range(2):
+        rows = b200als.Shard(r, 2).deal(order)
+        v = rows.to(torch.float32) + 0.25 * r
+        want[rows] = v[:, None] if len(shape) == 2 else v
+    assert torch.equal(full, want), (full, want)
 acc = torch.tensor([1.0 + s.rank, 10.0], dtype=torch.float64)
 s.all_reduce_sum(acc)
 assert acc.tolist() == [3.0, 20.0]

@@ -1,0 +1,32 @@
+"""torchrun --nproc-per-node N tools/dist_check.py: the sharded fit must reproduce the single-GPU fit."""
+import os, sys
+sys.path.insert(0, os.path.dirname(os.path.dirname(os.path.abspath(__file__))))
+import numpy as np, torch, torch.distributed as td
+import b200als
+from b200als.synth import synth_ratings
+
+rank = int(os.environ.get("LOCAL_RANK", "0"))
+torch.cuda.set_device(rank)
+td.init_process_group("nccl")
+worst = 0.0
+for k, (m, n, nnz) in ((64, (3000, 500, 120000)), (128, (700, 900, 60000)), (32, (400, 300, 9000))):
+    flat, vals = synth_ratings(m, n, nnz, seed=7)
+    cfg = b200als.ALSConfig(core=b200als.CoreConfig(n_factors=k, n_iters=3, lambda_u=4.0, lambda_v=3.0),
+                            biases=b200als.BiasesConfig(lambda_bu=2.0, lambda_bi=2.5))
+    one = b200als.ALS(cfg)
+    one.fit_coo(flat, vals, (m, n))
+    many = b200als.ALS(cfg)
+    many.shard = b200als.Shard.from_env()
+    many.fit_coo(flat, vals, (m, n))
+    for nm in ("U", "V", "b_u", "b_i"):
+        a, b = np.asarray(getattr(one, nm)), np.asarray(getattr(many, nm))
+        err = float(np.abs(a - b).max() / max(np.abs(a).max(), 1e-30))
+        worst = max(worst, err)
+        assert err < 1e-5, (k, nm, err)
+    r1, r2 = one.history["train_rmse"][-1], many.history["train_rmse"][-1]
+    assert abs(r1 - r2) < 1e-6, (r1, r2)
+    if td.get_rank() == 0:
+        print(f"k={k} world={td.get_world_size()} ok: rmse {r1:.6f} vs {r2:.6f}")
+if td.get_rank() == 0:
+    print("dist_check ok, worst rel diff", worst)
+td.destroy_process_group()
