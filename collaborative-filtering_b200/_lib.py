@@ -10,7 +10,7 @@ import os
 
 _HERE = os.path.dirname(os.path.abspath(__file__))
 LIB_PATH = os.path.join(_HERE, "libb200als.so")
-ABI_VERSION = 5
+ABI_VERSION = 6
 MAX_K = 160
 MAX_FEATURES = 8
 STATUS_WORDS = 4
@@ -24,6 +24,15 @@ vp = C.c_void_p
 
 class B200ALSError(RuntimeError):
     pass
+
+
+class SplitPlan(C.Structure):
+    """mirror of struct b200als_split_plan (include/b200als.h)"""
+    _fields_ = [
+        ("items", vp), ("hdr", vp), ("slot_np", vp), ("slot_ctr", vp), ("slot_acc", vp),
+        ("n_list", C.c_int64),
+        ("slot_floats", C.c_int32), ("thresh", C.c_int32), ("piece", C.c_int32), ("reserved", C.c_int32),
+    ]
 
 
 class StepArgs(C.Structure):
@@ -41,6 +50,7 @@ class StepArgs(C.Structure):
         ("bias_own", vp),
         ("chol_out", vp), ("aux_out", vp),
         ("status", vp), ("stats_acc", vp),
+        ("split", vp),
         ("workspace", vp), ("workspace_bytes", C.c_size_t),
     ]
 
@@ -62,6 +72,9 @@ _SIGNATURES = {
                           C.POINTER(vp), C.POINTER(C.c_int32), C.POINTER(vp),
                           C.c_int64, C.c_int32, vp, C.c_int64, vp],
     "b200als_step_workspace_bytes": [C.c_int32, C.c_int32, C.c_int64, C.POINTER(C.c_size_t)],
+    "b200als_split_plan_bytes": [C.c_int32, C.c_int64, C.c_int64, C.c_int32, C.c_int32, C.POINTER(C.c_size_t)],
+    "b200als_split_plan_build": [vp, vp, C.c_int64, C.c_int64, C.c_int32, C.c_int32, C.c_int32, vp, C.c_size_t,
+                                 C.POINTER(SplitPlan), vp],
     "b200als_row_step": [C.POINTER(StepArgs), vp],
     "b200als_graph_level_solve": [C.c_int32, vp, C.c_int64, vp, vp, vp, vp, vp,
                                   C.c_float, C.c_float, vp, vp, C.c_int64, vp, vp],

@@ -76,6 +76,8 @@ class ALS:
         # build-side knobs (not part of the reference surface)
         self.device = None                 # torch device; default: current CUDA device
         self.gram_path = _lib.PATH_AUTO    # PATH_FFMA / PATH_UMMA force one Gram path
+        self.split_rows = 0                # tcgen05 path: cut rows longer than this into pieces (0: default, <0: never)
+        self.split_piece = 0               # ratings per piece (0: split_rows / 2)
         self.shard: Shard | None = None    # row sharding across ranks (dist.Shard)
         self.timings: dict[str, float] = {}
         self.launches_per_iter: int = 0
@@ -386,6 +388,9 @@ class FitSession:
         if use_graph:
             self.i_list = i_order[:i_nonempty]      # the Gauss–Seidel sweep is not sharded (§8e)
 
+        self.u_split = self._split_plan(rt.indptr, self.u_list)
+        self.i_split = None if use_graph else self._split_plan(rt.cindptr, self.i_list)
+
         need = C.c_size_t(0)
         check(lib.b200als_step_workspace_bytes(k, model.gram_path, max(m, n), C.byref(need)), "step_workspace_bytes")
         self.ws = torch.empty(need.value, dtype=torch.uint8, device=dev)
@@ -428,8 +433,29 @@ class FitSession:
               "compose_z")
         self.launches += 1
 
+    def _split_plan(self, indptr, rows):
+        """Long rows of a schedule cut into pieces for the tcgen05 path (b200als_split_plan_build); None if
+        the path is not in use or no row can exceed the threshold."""
+        model, lib = self.model, self.lib
+        if model.gram_path == _lib.PATH_FFMA or self.k not in (64, 128) or model.split_rows < 0 or rows.numel() == 0:
+            return None
+        r64 = rows.to(torch.int64)
+        nnz_list = int((indptr[r64 + 1] - indptr[r64]).sum().item())
+        need = C.c_size_t(0)
+        check(lib.b200als_split_plan_bytes(self.k, rows.numel(), nnz_list, model.split_rows, model.split_piece,
+                                           C.byref(need)), "split_plan_bytes")
+        mem = torch.empty(max(need.value, 256), dtype=torch.uint8, device=self.dev)
+        plan = _lib.SplitPlan()
+        check(lib.b200als_split_plan_build(ptr(indptr), ptr(rows), rows.numel(), nnz_list, self.k, model.split_rows,
+                                           model.split_piece, ptr(mem), mem.numel(), C.byref(plan), self._stream()),
+              "split_plan_build")
+        if not plan.items:
+            return None
+        plan._mem = mem                     # keeps the device memory alive
+        return plan
+
     def _step(self, indptr, indices, vals, n_rows, rows, F, n_f_rows, bias_other, reg, reg_row, lamb, X, bias_own,
-              mode, stats=None):
+              mode, stats=None, split=None):
         a = StepArgs()
         a.struct_bytes = C.sizeof(StepArgs)
         a.k, a.mode, a.path = self.k, mode, self.model.gram_path
@@ -446,6 +472,7 @@ class FitSession:
         a.aux_out = ptr(self.aux_d) if mode == _lib.STEP_FACTOR else None
         a.status = ptr(self.status)
         a.stats_acc = ptr(stats)
+        a.split = C.addressof(split) if split is not None else None
         a.workspace, a.workspace_bytes = ptr(self.ws), self.ws.numel()
         check(self.lib.b200als_row_step(C.byref(a), self._stream()), "row_step")
         self.launches += self.lib.b200als_last_launch_count() + 1      # + the cursor memset
@@ -478,7 +505,7 @@ class FitSession:
         # (1) users (als.py:414-433)
         self._mark("user")
         self._step(rt.indptr, rt.indices, rt.vals, m, self.u_list, self.Z_d, n, self.b_i_d, self.reg_user, None,
-                   self.lam_bu, self.U_d, self.b_u_d, _lib.STEP_SOLVE)
+                   self.lam_bu, self.U_d, self.b_u_d, _lib.STEP_SOLVE, split=self.u_split)
         if shard.active:
             shard.exchange_rows(self.U_d, self.u_plan)
             shard.exchange_rows(self.b_u_d, self.u_plan)
@@ -503,7 +530,7 @@ class FitSession:
                 self.acc.zero_()
             self._step(rt.cindptr, rt.cindices, rt.cvals, n, self.i_list, self.U_d, m, self.b_u_d, 0.0,
                        self.reg_item_d, self.lam_bi, self.V_d, self.b_i_d, _lib.STEP_SOLVE,
-                       stats=self.acc if fused else None)
+                       stats=self.acc if fused else None, split=self.i_split)
             if shard.active:
                 shard.exchange_rows(self.V_d, self.i_plan)
                 shard.exchange_rows(self.b_i_d, self.i_plan)

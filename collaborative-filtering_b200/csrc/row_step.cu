@@ -113,6 +113,34 @@ int b200als_step_workspace_bytes(int32_t k, int32_t path, int64_t n_f_rows, size
     return B200ALS_OK;
 }
 
+int b200als_split_plan_bytes(int32_t k, int64_t n_list, int64_t nnz, int32_t split_rows, int32_t split_piece,
+                             size_t* bytes_host) {
+    ALS_CHECK_ARG(bytes_host, "null");
+    ALS_CHECK_ARG(k >= 1 && k <= B200ALS_MAX_K, "k out of range");
+    ALS_CHECK_ARG(n_list >= 0 && n_list < (1ll << 31) && nnz >= 0, "count out of range");
+    SplitLayout L;
+    split_layout(k, n_list, nnz, split_rows, split_piece, 256, L);
+    *bytes_host = L.total;
+    return B200ALS_OK;
+}
+
+int b200als_split_plan_build(const int64_t* indptr, const int32_t* rows, int64_t n_list, int64_t nnz, int32_t k,
+                             int32_t split_rows, int32_t split_piece, void* plan_mem, size_t plan_bytes,
+                             b200als_split_plan* plan_host, b200als_stream_t stream) {
+    ALS_CHECK_ARG(indptr && plan_host, "null");
+    ALS_CHECK_ARG(k >= 1 && k <= B200ALS_MAX_K, "k out of range");
+    ALS_CHECK_ARG(n_list >= 0 && n_list < (1ll << 31) && nnz >= 0, "count out of range");
+    memset(plan_host, 0, sizeof(*plan_host));
+    plan_host->n_list = n_list;
+    SplitLayout L;
+    if (!split_layout(k, n_list, nnz, split_rows, split_piece, 256, L)) return B200ALS_OK;   // nothing can be split
+    if (!plan_mem || plan_bytes < L.total) {
+        set_error("b200als_split_plan_build: plan memory %zu < required %zu", plan_bytes, L.total);
+        return B200ALS_E_WORKSPACE;
+    }
+    return split_build(indptr, rows, n_list, L, static_cast<char*>(plan_mem), plan_host, as_stream(stream));
+}
+
 int b200als_row_step(const b200als_step_args* a, b200als_stream_t stream) {
     g_launch_count = 0;
     ALS_CHECK_ARG(a && a->struct_bytes == sizeof(b200als_step_args), "args struct size mismatch (ABI)");
@@ -152,6 +180,7 @@ int b200als_row_step(const b200als_step_args* a, b200als_stream_t stream) {
     p.chol_out = a->chol_out; p.aux_out = a->aux_out; p.status = a->status;
     p.stats = (a->mode == B200ALS_STEP_SOLVE) ? a->stats_acc : nullptr;
     p.cursor = reinterpret_cast<unsigned long long*>(a->workspace);
+    p.items = nullptr; p.split_hdr = nullptr; p.slot_np = nullptr; p.slot_ctr = nullptr; p.slot_acc = nullptr;
     ALS_CUDA(cudaMemsetAsync(a->workspace, 0, 256, s));
 
     if (path == B200ALS_PATH_UMMA) {
@@ -160,7 +189,7 @@ int b200als_row_step(const b200als_step_args* a, b200als_stream_t stream) {
                       (long long)a->ldf);
             return B200ALS_E_UNSUPPORTED;
         }
-        return launch_umma(p, a->n_f_rows, static_cast<char*>(a->workspace) + 256, a->workspace_bytes - 256, s);
+        return launch_umma(p, a->n_f_rows, a->split, static_cast<char*>(a->workspace), a->workspace_bytes, s);
     }
     return dispatch_ffma(p, s);
 }

@@ -36,6 +36,12 @@ struct RowStepParams {
     int32_t* status;
     double* stats;                // optional: [0] += sum d, [1] += sum d^2 over the rows solved (A10 fused)
     unsigned long long* cursor;   // zeroed before launch
+    // tcgen05 path only: work items of the schedule with long rows cut into pieces (split_plan.cuh)
+    const int4* items;            // {row, first rating (offset in the row), ratings, slot or -1}; null: rows[] as is
+    const int32_t* split_hdr;     // [0] = number of items
+    const int32_t* slot_np;       // pieces of split row `slot`
+    int32_t* slot_ctr;            // pieces of the slot accumulated so far (zeroed)
+    float* slot_acc;              // per slot: k rows x (k + 4) [normal matrix | c, s, -, -] | t, qq, -, -  (zeroed)
 };
 
 template <int KP, int T>

@@ -30,6 +30,7 @@
 #pragma once
 #include "row_ldl.cuh"
 #include "row_step_ffma.cuh"
+#include "split_plan.cuh"
 #include "umma_ptx.cuh"
 
 namespace b200als {
@@ -92,7 +93,7 @@ struct UmmaCfg {
     static constexpr int NBAR = (2 * META + 3 * STAGES + 2 * NBUF + 2 * UM_RD + 1) & ~1;   // even: RowDesc ring stays 16-byte aligned
     static constexpr size_t smem_bytes = 1024 /*align slack*/ + (size_t)STAGES * (STAGE_STRIDE + 128 + 16) +
                                          (size_t)META * META_BYTES + (size_t)MATS * MAT_FLOATS * 4 +
-                                         (size_t)RED_FLOATS * 4 + (size_t)NBAR * 8 + (size_t)UM_RD * 16 + 64 + 128;
+                                         (size_t)RED_FLOATS * 4 + (size_t)NBAR * 8 + (size_t)UM_RD * 16 + 128 + 128;
     static_assert(smem_bytes <= 232448, "tcgen05 Gram kernel exceeds 227 KB of shared memory");
     static_assert(NBUF * ACC_STRIDE <= 512, "TMEM columns");
 };
@@ -132,7 +133,7 @@ struct UmmaSmem {
     float* red;              // [NG][4][RPB][4]
     uint64_t *meta_full, *meta_empty, *full, *prep_full, *empty, *acc_full, *acc_empty, *rd_full, *rd_empty;
     RowDesc* rd;             // [UM_RD]
-    int32_t* bad;            // [16] non-SPD flags, one per matrix slot
+    int32_t* bad;            // [16] non-SPD flags, one per matrix slot | [16] split-row 'last piece' flags
     uint32_t* tmem_base;
 };
 
@@ -158,7 +159,7 @@ __device__ __forceinline__ void umma_carve(unsigned char* raw, UmmaSmem& s) {
     s.rd_empty = s.rd_full + UM_RD;
     s.rd = reinterpret_cast<RowDesc*>(bars + C::NBAR);
     s.bad = reinterpret_cast<int32_t*>(s.rd + UM_RD);
-    s.tmem_base = reinterpret_cast<uint32_t*>(s.bad + 16);
+    s.tmem_base = reinterpret_cast<uint32_t*>(s.bad + 32);
 }
 
 // shared-space loads (explicit .shared addressing: generic LD on the carved buffer takes the long-scoreboard path)
@@ -196,11 +197,13 @@ template <int K>
 __device__ __forceinline__ void umma_role_meta(const RowStepParams& p, const UmmaSmem& s, int lane) {
     using C = UmmaCfg<K>;
     uint32_t sg = 0;                                   // global stage counter of this CTA
-    const long long n_list = p.n_list;
+    // work list: the items of the split plan (rows cut into pieces) or the plain row list
+    const long long n_list = p.items ? (long long)p.split_hdr[0] : (long long)p.n_list;
     const long long G = gridDim.x;
     long long seen = 0;
 
     // one batch of claimed rows lives in registers: lane l holds entry l
+    // (row_l: the row, or -2 - item for a piece of a split row — the solver looks the item up)
     int nb = 0;
     int32_t row_l = 0;
     int64_t beg_l = 0, end_l = 0;
@@ -217,9 +220,16 @@ __device__ __forceinline__ void umma_role_meta(const RowStepParams& p, const Umm
         row_o = 0; beg_o = 0; end_o = 0;
         if (lane < nb_o) {
             const long long slot = (long long)base + lane;
-            row_o = p.rows ? p.rows[slot] : (int32_t)slot;
-            beg_o = p.indptr[row_o];
-            end_o = p.indptr[row_o + 1];
+            if (p.items) {
+                const int4 it = p.items[slot];
+                beg_o = p.indptr[it.x] + it.y;
+                end_o = beg_o + it.z;
+                row_o = it.w < 0 ? it.x : (int32_t)(-2 - slot);
+            } else {
+                row_o = p.rows ? p.rows[slot] : (int32_t)slot;
+                beg_o = p.indptr[row_o];
+                end_o = p.indptr[row_o + 1];
+            }
         }
     };
     claim(nb, row_l, beg_l, end_l);
@@ -492,6 +502,9 @@ __device__ __forceinline__ void umma_role_solver(const RowStepParams& p, const U
         for (int i = 8; i < 12; ++i) g_timing[i] = 0;
 #endif
 
+    int32_t* lastf = s.bad + 16 + g * C::RPB + h;      // split rows: "this group added the last piece"
+    constexpr int SLOT_LD = K + 4;                     // slot row: k matrix entries | c, s, -, -
+
     for (uint32_t pr = g;; pr += C::NG) {
         // descriptors of the rows in this accumulator buffer
         const uint32_t n0 = pr * C::RPB;
@@ -503,18 +516,28 @@ __device__ __forceinline__ void umma_role_solver(const RowStepParams& p, const U
         TICK(0);
         const int4 d0v = lds_s32x4(ptx::smem_u32(&s.rd[n0 % UM_RD]));
         const int4 dmv = lds_s32x4(ptx::smem_u32(&s.rd[(n0 + h) % UM_RD]));
-        RowDesc d0, dm;
-        d0.row = d0v.x; d0.cnt = d0v.y; d0.tsum = __int_as_float(d0v.z); d0.qq = __int_as_float(d0v.w);
-        dm.row = dmv.x; dm.cnt = dmv.y; dm.tsum = __int_as_float(dmv.z); dm.qq = __int_as_float(dmv.w);
+        const int drow = dmv.x;                        // row | -1: none | <= -2: piece (-2 - item) of a split row
+        int cnt = dmv.y;
+        float tsum = __int_as_float(dmv.z), qq = __int_as_float(dmv.w);
         named_bar_sync(phase_bar, 128);                // everyone holds its descriptor
         if (q == 0 && seg == 0) ptx::mbar_arrive(&s.rd_empty[(n0 + h) % UM_RD]);
-        if (d0.row < 0) break;                         // end of work (rows fill buffers in order)
-        const bool valid = dm.row >= 0;
-        const int64_t row = valid ? dm.row : d0.row;   // absent half: shadow a valid row, write nothing
+        if (d0v.x == -1) break;                        // end of work (rows fill buffers in order)
+        const bool part = drow <= -2;
+        int64_t row = drow >= 0 ? drow : d0v.x;        // absent half: shadow a valid row, write nothing
+        int slot = 0, npieces = 0;
+        if (part) {
+            const int4 it = p.items[-2 - drow];
+            row = it.x;
+            slot = it.w;
+            npieces = p.slot_np[slot];
+        } else if (row < 0) {                          // first half is a piece, this half is absent
+            row = p.items[-2 - d0v.x].x;
+        }
+        const bool any_part = __any_sync(0xffffffffu, part);   // both halves sit in every warp: group-uniform
         const float ridge = p.reg_row ? p.reg_row[row] : p.reg;
         const float lam_bias = p.lam_bias_row ? p.lam_bias_row[row] : p.lam_bias;
         const float bias_old = p.bias_own[row];
-        if (q == 0 && seg == 0) *bad = 0;
+        if (q == 0 && seg == 0) { *bad = 0; *lastf = 0; }
 
         const uint32_t buf = pr % C::NBUF;
         ptx::mbar_wait(&s.acc_full[buf], (pr / C::NBUF) & 1, 7, (int)pr);
@@ -523,16 +546,74 @@ __device__ __forceinline__ void umma_role_solver(const RowStepParams& p, const U
         const uint32_t trow = tmem + buf * C::ACC_STRIDE + ((uint32_t)(32 * q) << 16);
         float d2[4];
         ptx::tmem_ld4(trow + C::D2_COL, d2);
-        const float c_r = d2[0] + d2[1], s_r = d2[2];
+        float c_r = d2[0] + d2[1], s_r = d2[2];
         TICK(2);
 
-        // the matrix stays in TMEM; every phase pulls one RPW-column window of this thread's row
+        // ---- pieces of split rows: add the partial matrix to the row's slot; the last piece solves ----
+        bool from_slot = false;
+        float* gs = nullptr;
+        if (any_part) {
+            if (part) gs = p.slot_acc + (size_t)slot * split_slot_floats(K) + (size_t)r * SLOT_LD;
+#pragma unroll 1
+            for (int c0 = 0; c0 < K; c0 += 16) {
+                float v[16];
+                ptx::tmem_ld16(trow + c0, v);
+                if (part) {
+#pragma unroll
+                    for (int i = 0; i < 16; ++i) atomicAdd(gs + c0 + i, v[i]);
+                }
+            }
+            if (part) {
+                atomicAdd(gs + K, c_r);
+                atomicAdd(gs + K + 1, s_r);
+                if (q == 0 && seg == 0) {
+                    float* tq = p.slot_acc + (size_t)slot * split_slot_floats(K) + (size_t)K * SLOT_LD;
+                    atomicAdd(tq, tsum);
+                    atomicAdd(tq + 1, qq);
+                }
+                __threadfence();
+            }
+            named_bar_sync(phase_bar, 128);            // every thread's adds are fenced
+            if (part && q == 0 && seg == 0) {
+                const int old = atomicAdd(p.slot_ctr + slot, 1);
+                if (old == npieces - 1) *lastf = 1;
+            }
+            named_bar_sync(phase_bar, 128);
+            from_slot = part && (*reinterpret_cast<volatile int32_t*>(lastf) != 0);
+            if (from_slot) {
+                __threadfence();
+                c_r = __ldcg(gs + K);
+                s_r = __ldcg(gs + K + 1);
+                const float* tq = p.slot_acc + (size_t)slot * split_slot_floats(K) + (size_t)K * SLOT_LD;
+                tsum = __ldcg(tq);
+                qq = __ldcg(tq + 1);
+                cnt = (int)(p.indptr[row + 1] - p.indptr[row]);
+            }
+            // nothing to solve in this buffer: hand the accumulator back and move on
+            const bool solve_any = __any_sync(0xffffffffu, from_slot || drow >= 0);
+            if (!solve_any) {
+                ptx::tc_fence_before();
+                ptx::mbar_arrive(&s.acc_empty[buf]);
+                named_bar_sync(phase_bar, 128);        // lastf / bad free for the next pair
+                continue;
+            }
+        }
+        const bool valid = drow >= 0 || from_slot;
+
+        // the matrix stays in TMEM (or in its slot); every phase pulls one RPW-column window of this thread's row
         auto load_window = [&](const int ph, float (&w)[C::RPW], const bool is_last) {
             const uint32_t c0 = (uint32_t)(rev ? K - C::RPW * (ph + 1) : C::RPW * ph);
 #pragma unroll
             for (int cc = 0; cc < C::RPW; cc += 16) {
                 float v[16];
                 ptx::tmem_ld16(trow + c0 + cc, v);
+                if (from_slot) {
+#pragma unroll
+                    for (int i4 = 0; i4 < 16; i4 += 4) {
+                        const float4 gv = __ldcg(reinterpret_cast<const float4*>(gs + c0 + cc + i4));
+                        v[i4] = gv.x; v[i4 + 1] = gv.y; v[i4 + 2] = gv.z; v[i4 + 3] = gv.w;
+                    }
+                }
                 if (!rev) {
 #pragma unroll
                     for (int i = 0; i < 16; ++i) w[cc + i] = v[i];
@@ -575,15 +656,15 @@ __device__ __forceinline__ void umma_role_solver(const RowStepParams& p, const U
                     const float* rr = red + (w * C::RPB + h) * 4;
                     sx += rr[0]; cx += rr[1]; xx += rr[2];
                 }
-                const float cnt = (float)dm.cnt;
-                const float beta = (dm.tsum - sx) / (cnt + lam_bias);          // als.py:431-433 / 464-466
+                const float cntf = (float)cnt;
+                const float beta = (tsum - sx) / (cntf + lam_bias);            // als.py:431-433 / 464-466
                 p.bias_own[row] = beta;
                 // residuals of the row with the fresh x, beta:  d_e = q_e - beta - f_e.x
                 //   sum d   = t - cnt beta - s.x
                 //   sum d^2 = qq - 2 beta t + cnt beta^2 - 2 (c.x - beta s.x) + x^T G x,
                 //   x^T G x = x.(c - beta_old s) - ridge x.x      (x solves (G + ridge I) x = c - beta_old s)
-                const float sd = dm.tsum - cnt * beta - sx;
-                const float sd2 = dm.qq - 2.0f * beta * dm.tsum + cnt * beta * beta - cx +
+                const float sd = tsum - cntf * beta - sx;
+                const float sd2 = qq - 2.0f * beta * tsum + cntf * beta * beta - cx +
                                   (2.0f * beta - bias_old) * sx - ridge * xx;
                 acc_d += (double)sd;
                 acc_d2 += (double)sd2;
@@ -668,25 +749,43 @@ __global__ void __launch_bounds__(UmmaCfg<K>::THREADS, 1) row_step_umma_kernel(c
 
 static inline bool umma_supported(int k, int64_t ldf) { return (k == 64 || k == 128) && ldf == k; }
 
+// workspace: [256 B cursor] [bf16 copy of F]
 static inline size_t umma_workspace_bytes(int k, int64_t n_f_rows) {
     if (k != 64 && k != 128) return 256;
     return 256 + align_up((size_t)(n_f_rows > 0 ? n_f_rows : 0) * 4 * k, 256);
 }
 
 template <int K>
-static int launch_umma_k(const RowStepParams& p, int64_t n_f_rows, void* ws, size_t ws_bytes, cudaStream_t st) {
+static int launch_umma_k(RowStepParams& p, int64_t n_f_rows, const b200als_split_plan* plan, char* ws, size_t ws_bytes,
+                         cudaStream_t st) {
     using C = UmmaCfg<K>;
-    if (ws_bytes < (size_t)n_f_rows * C::REC_BYTES) {
+    if (ws_bytes < umma_workspace_bytes(K, n_f_rows)) {
         set_error("row_step (tcgen05): workspace too small for the bf16 split of %lld rows", (long long)n_f_rows);
         return B200ALS_E_WORKSPACE;
     }
-    __nv_bfloat16* H = static_cast<__nv_bfloat16*>(ws);
+    __nv_bfloat16* H = reinterpret_cast<__nv_bfloat16*>(ws + 256);
     {
         int64_t work = n_f_rows * (K / 4);
         int64_t blocks = ceil_div64(work, 256);
         if (blocks > (int64_t)kNumSMs * 16) blocks = (int64_t)kNumSMs * 16;
         split_bf16_kernel<<<(unsigned)blocks, 256, 0, st>>>(p.F, p.ldf, n_f_rows, K, H);
         ALS_LAUNCH_CHECK();
+    }
+    p.items = nullptr; p.split_hdr = nullptr; p.slot_np = nullptr; p.slot_ctr = nullptr; p.slot_acc = nullptr;
+    const bool split = plan && plan->items;
+    if (split) {
+        if (plan->n_list != p.n_list || plan->slot_floats != split_slot_floats(K)) {
+            set_error("row_step (tcgen05): split plan was built for another list / k (n_list %lld vs %lld)",
+                      (long long)plan->n_list, (long long)p.n_list);
+            return B200ALS_E_INVALID;
+        }
+        split_zero_kernel<<<kNumSMs * 2, 256, 0, st>>>(plan->hdr, plan->slot_floats, plan->slot_acc, plan->slot_ctr);
+        ALS_LAUNCH_CHECK();
+        p.items = static_cast<const int4*>(plan->items);
+        p.split_hdr = plan->hdr;
+        p.slot_np = plan->slot_np;
+        p.slot_ctr = plan->slot_ctr;
+        p.slot_acc = plan->slot_acc;
     }
     auto kern = row_step_umma_kernel<K>;
     static thread_local bool configured = false;
@@ -695,14 +794,16 @@ static int launch_umma_k(const RowStepParams& p, int64_t n_f_rows, void* ws, siz
         configured = true;
     }
     int64_t grid = p.n_list < kNumSMs ? p.n_list : kNumSMs;
+    if (split) grid = kNumSMs;                         // pieces: the item count is only known on the device
     kern<<<(unsigned)grid, C::THREADS, C::smem_bytes, st>>>(p, reinterpret_cast<const unsigned char*>(H));
     ALS_LAUNCH_CHECK();
     return B200ALS_OK;
 }
 
-static inline int launch_umma(const RowStepParams& p, int64_t n_f_rows, void* ws, size_t ws_bytes, cudaStream_t s) {
-    if (p.k == 64) return launch_umma_k<64>(p, n_f_rows, ws, ws_bytes, s);
-    return launch_umma_k<128>(p, n_f_rows, ws, ws_bytes, s);
+static inline int launch_umma(RowStepParams& p, int64_t n_f_rows, const b200als_split_plan* plan, char* ws,
+                              size_t ws_bytes, cudaStream_t s) {
+    if (p.k == 64) return launch_umma_k<64>(p, n_f_rows, plan, ws, ws_bytes, s);
+    return launch_umma_k<128>(p, n_f_rows, plan, ws, ws_bytes, s);
 }
 
 }  // namespace b200als

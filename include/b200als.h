@@ -31,7 +31,7 @@
 extern "C" {
 #endif
 
-#define B200ALS_ABI_VERSION 5
+#define B200ALS_ABI_VERSION 6
 
 #define B200ALS_OK            0
 #define B200ALS_E_INVALID    -1   /* bad argument */
@@ -135,6 +135,33 @@ int b200als_compose_z(const float* V, int64_t ldv, int64_t n, int32_t k,
 #define B200ALS_PATH_FFMA   1
 #define B200ALS_PATH_UMMA   2
 
+/* ------------------------------------------------------------------------
+ * Long rows (tcgen05 path).  One SM consumes a row's ratings 32 per pipeline stage, so a very popular
+ * item (als.py:436-441 visits it like any other) would bound the whole half-step.  A split plan cuts
+ * rows with more than split_rows ratings into pieces of about split_piece ratings that different SMs
+ * accumulate: the partial normal matrices [A | c s] are added into a per-row slot in global memory and
+ * the SM adding the last piece factors and solves — same sums, different summation order.
+ *   split_rows: 0 = default (a quarter of one SM's share of nnz, at least 8192), < 0 = never split
+ *   split_piece: ratings per piece, rounded up to 32; 0 = split_rows / 2
+ *   nnz: ratings held by the listed rows (bounds the number of slots)
+ * plan_mem is caller-owned device memory of b200als_split_plan_bytes(); *plan_host describes it.
+ * ---------------------------------------------------------------------- */
+typedef struct b200als_split_plan {
+    const void*    items;        /* int4 {row, first rating (offset in the row), ratings, slot or -1} */
+    const int32_t* hdr;          /* device: [0] items, [1] split rows */
+    const int32_t* slot_np;      /* pieces per split row */
+    int32_t*       slot_ctr;     /* pieces accumulated so far (zeroed by every step) */
+    float*         slot_acc;     /* per slot: k x (k + 4) [A | c s - -], then t, qq, -, - (zeroed by every step) */
+    int64_t        n_list;       /* list entries the plan was built for */
+    int32_t        slot_floats, thresh, piece, reserved;
+} b200als_split_plan;
+int b200als_split_plan_bytes(int32_t k, int64_t n_list, int64_t nnz, int32_t split_rows, int32_t split_piece,
+                             size_t* bytes_host);
+/* returns 0 and fills *plan_host; plan_host->items == NULL when no row can exceed the threshold */
+int b200als_split_plan_build(const int64_t* indptr, const int32_t* rows, int64_t n_list, int64_t nnz, int32_t k,
+                             int32_t split_rows, int32_t split_piece, void* plan_mem, size_t plan_bytes,
+                             b200als_split_plan* plan_host, b200als_stream_t stream);
+
 typedef struct b200als_step_args {
     uint32_t struct_bytes;       /* = sizeof(b200als_step_args) */
     int32_t  k;
@@ -160,6 +187,8 @@ typedef struct b200als_step_args {
     double*  stats_acc;          /* optional, SOLVE mode: A10 fused into the step (als.py:503-511 when Z == F-side
                                     factors are final): [0] += sum_e d_e, [1] += sum_e d_e^2 over the rows solved,
                                     d_e = R_e - (mu + bias_other + bias_own_new + F[idx_e].x_new).  Caller zeroes. */
+    const struct b200als_split_plan* split;   /* host pointer, optional (tcgen05 path, SOLVE mode): the plan built by
+                                    b200als_split_plan_build for exactly this (indptr, rows, n_list) */
     void*  workspace; size_t workspace_bytes;   /* see b200als_step_workspace_bytes */
 } b200als_step_args;
 

@@ -161,6 +161,36 @@ def test_heavy_rows_vs_oracle(cuda_device):
     assert np.abs(np.asarray(model.history["train_rmse"]) - np.asarray(o.history["train_rmse"])).max() < RMSE_TOL
 
 
+@pytest.mark.parametrize("k", [64, 128])
+@pytest.mark.parametrize("split", [(64, 32), (200, 96), (1000, 0), (-1, 0)])
+def test_split_rows_vs_oracle(cuda_device, k, split):
+    """tcgen05 path: rows longer than the threshold are cut into pieces accumulated by different SMs
+    (partial normal matrices added in global memory, the last piece solves).  Includes rows whose pieces
+    pair up with whole rows / other pieces in one k=64 accumulator pair, ragged tails, and the odd tail."""
+    import b200als
+    import als_oracle
+    rng = np.random.default_rng(11 + k)
+    m, n = 1500, 61
+    mask = rng.random((m, n)) < 0.03
+    mask[:, 0] = True                                   # 1500 ratings
+    mask[:, 1] = rng.random(m) < 0.7
+    mask[:, 2] = rng.random(m) < 0.31
+    mask[:, 3] = rng.random(m) < 0.1
+    mask[7, :] = True                                   # one 61-rating user (just under / over the thresholds)
+    mask[11, :40] = True
+    flat = np.flatnonzero(mask)
+    vals = rng.integers(1, 11, size=flat.size) / 2.0
+    cfg = b200als.ALSConfig(core=b200als.CoreConfig(n_factors=k, n_iters=3, lambda_u=3.0, lambda_v=2.0),
+                            biases=b200als.BiasesConfig(lambda_bu=2.0, lambda_bi=2.5))
+    o = als_oracle.SparseALSOracle(cfg).fit_sparse(als_oracle.csr_csc_from_flat(flat, vals, m, n), m, n, tol=None)
+    model = b200als.ALS(cfg)
+    model.split_rows, model.split_piece = split
+    model.fit_coo(flat, vals, (m, n), tol=None, verbose=0)
+    assert rel_err(model.U, o.U) < FACTOR_TOL and rel_err(model.V, o.V) < FACTOR_TOL
+    assert rel_err(model.b_u, o.b_u) < FACTOR_TOL and rel_err(model.b_i, o.b_i) < FACTOR_TOL
+    assert np.abs(np.asarray(model.history["train_rmse"]) - np.asarray(o.history["train_rmse"])).max() < RMSE_TOL
+
+
 def test_errors_match_reference_surface(cuda_device):
     import b200als
     c = load_case("small_feat1")
