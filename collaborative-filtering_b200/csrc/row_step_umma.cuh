@@ -35,7 +35,6 @@
 
 namespace b200als {
 
-constexpr int UM_R = 32;          // ratings per stage
 constexpr int UM_RD = 16;         // row-descriptor ring
 constexpr int UM_GATHER_WARPS = 4;
 
@@ -61,11 +60,19 @@ struct UmmaCfg {
     static constexpr int N_MB = REC_BYTES / 128;            // 128-byte atoms per record
     static constexpr int HI_ATOMS = N_MB / 2;
     static constexpr int NA = N_MB + 1;                     // atoms per 8-rating K-atom: hi.. | q | lo..
-    static constexpr int STAGE_DATA = (UM_R / 8) * NA * 1024;
+#ifndef B200ALS_R64
+#define B200ALS_R64 64
+#endif
+    // ratings per stage: every producer warp pays a fixed latency chain per stage (barrier waits, header,
+    // commit), so k = 64 — whose stages are half the bytes — takes 64 ratings per stage
+    static constexpr int R = (K == 64) ? B200ALS_R64 : 32;
+    static constexpr int RL = R / 32;                       // ratings per lane of a single-warp role
+    static constexpr int STAGE_DATA = (R / 8) * NA * 1024;
     static constexpr int STAGE_STRIDE = STAGE_DATA;         // data ring (1024-byte aligned atoms)
     static constexpr int META = 32;                         // (index, rating) ring: runs far ahead of the data ring
-    static constexpr int META_BYTES = 288;                  // idx[32] int32 | val[32] float | StageHdr | pad
-    static constexpr int STAGES = (K == 64) ? 6 : 4;
+    static constexpr int META_BYTES = 8 * R + 32;           // idx[R] int32 | val[R] float | StageHdr | pad
+    static constexpr int BIAS_BYTES = 4 * R;
+    static constexpr int STAGES = (K == 64) ? (R == 64 ? 4 : 6) : 4;
 #ifndef B200ALS_NG64
 #define B200ALS_NG64 4
 #endif
@@ -91,7 +98,7 @@ struct UmmaCfg {
     static constexpr int MAT_FLOATS = ldl_mat_floats<K>();
     static constexpr int RED_FLOATS = NG * 4 * RPB * 4;     // per group: [warp][matrix][4]
     static constexpr int NBAR = (2 * META + 3 * STAGES + 2 * NBUF + 2 * UM_RD + 1) & ~1;   // even: RowDesc ring stays 16-byte aligned
-    static constexpr size_t smem_bytes = 1024 /*align slack*/ + (size_t)STAGES * (STAGE_STRIDE + 128 + 16) +
+    static constexpr size_t smem_bytes = 1024 /*align slack*/ + (size_t)STAGES * (STAGE_STRIDE + BIAS_BYTES + 16) +
                                          (size_t)META * META_BYTES + (size_t)MATS * MAT_FLOATS * 4 +
                                          (size_t)RED_FLOATS * 4 + (size_t)NBAR * 8 + (size_t)UM_RD * 16 + 128 + 128;
     static_assert(smem_bytes <= 232448, "tcgen05 Gram kernel exceeds 227 KB of shared memory");
@@ -143,8 +150,8 @@ __device__ __forceinline__ void umma_carve(unsigned char* raw, UmmaSmem& s) {
     unsigned char* base = reinterpret_cast<unsigned char*>((reinterpret_cast<uintptr_t>(raw) + 1023) & ~(uintptr_t)1023);
     s.stages = base;
     s.bias = s.stages + (size_t)C::STAGES * C::STAGE_STRIDE;
-    s.sflags = reinterpret_cast<int32_t*>(s.bias + (size_t)C::STAGES * 128);
-    s.meta = s.bias + (size_t)C::STAGES * (128 + 16);
+    s.sflags = reinterpret_cast<int32_t*>(s.bias + (size_t)C::STAGES * C::BIAS_BYTES);
+    s.meta = s.bias + (size_t)C::STAGES * (C::BIAS_BYTES + 16);
     s.mats = reinterpret_cast<float*>(s.meta + (size_t)C::META * C::META_BYTES);
     s.red = s.mats + (size_t)C::MATS * C::MAT_FLOATS;
     uint64_t* bars = reinterpret_cast<uint64_t*>(s.red + C::RED_FLOATS);
@@ -186,7 +193,7 @@ __device__ __forceinline__ void sts_s32x4(uint32_t a, int4 v) {
 }
 template <int K>
 __device__ __forceinline__ StageHdr stage_hdr(const UmmaSmem& s, uint32_t ms) {
-    const int4 v = lds_s32x4(ptx::smem_u32(s.meta + (size_t)ms * UmmaCfg<K>::META_BYTES + 256));
+    const int4 v = lds_s32x4(ptx::smem_u32(s.meta + (size_t)ms * UmmaCfg<K>::META_BYTES + 8 * UmmaCfg<K>::R));
     StageHdr h;
     h.live_n = v.x; h.row = v.y; h.flags = v.z; h.cnt = v.w;
     return h;
@@ -241,27 +248,30 @@ __device__ __forceinline__ void umma_role_meta(const RowStepParams& p, const Umm
             const int64_t beg = __shfl_sync(0xffffffffu, beg_l, e);
             const int64_t end = __shfl_sync(0xffffffffu, end_l, e);
             const int32_t row = __shfl_sync(0xffffffffu, row_l, e);
-            for (int64_t t0 = beg; t0 < end; t0 += UM_R, ++sg) {
+            for (int64_t t0 = beg; t0 < end; t0 += C::R, ++sg) {
                 const uint32_t ms = sg % C::META, mph = (sg / C::META) & 1;
                 ptx::mbar_wait(&s.meta_empty[ms], mph ^ 1, 1, (int)sg);
                 unsigned char* mt = s.meta + (size_t)ms * C::META_BYTES;
-                const int64_t ee = t0 + lane;
-                const bool live = ee < end;
-                const int64_t es = live ? ee : beg;        // any valid address for the zero-fill form
-                asm volatile("cp.async.ca.shared.global [%0], [%1], 4, %2;" ::"r"(ptx::smem_u32(mt + lane * 4)),
-                             "l"(p.indices + es), "r"(live ? 4u : 0u)
-                             : "memory");
-                asm volatile("cp.async.ca.shared.global [%0], [%1], 4, %2;" ::"r"(ptx::smem_u32(mt + 128 + lane * 4)),
-                             "l"(p.vals + es), "r"(live ? 4u : 0u)
-                             : "memory");
+#pragma unroll
+                for (int j = 0; j < C::RL; ++j) {
+                    const int64_t ee = t0 + lane + 32 * j;
+                    const bool live = ee < end;
+                    const int64_t es = live ? ee : beg;    // any valid address for the zero-fill form
+                    asm volatile("cp.async.ca.shared.global [%0], [%1], 4, %2;" ::"r"(ptx::smem_u32(mt + (lane + 32 * j) * 4)),
+                                 "l"(p.indices + es), "r"(live ? 4u : 0u)
+                                 : "memory");
+                    asm volatile("cp.async.ca.shared.global [%0], [%1], 4, %2;" ::"r"(ptx::smem_u32(mt + 4 * C::R + (lane + 32 * j) * 4)),
+                                 "l"(p.vals + es), "r"(live ? 4u : 0u)
+                                 : "memory");
+                }
                 ptx::cp_async_mbar_arrive_noinc(&s.meta_full[ms]);
                 if (lane == 0) {
                     StageHdr h;
-                    h.live_n = (int32_t)((end - t0) < UM_R ? (end - t0) : UM_R);
+                    h.live_n = (int32_t)((end - t0) < C::R ? (end - t0) : C::R);
                     h.row = row;
-                    h.flags = (t0 == beg ? HDR_FIRST : 0) | (t0 + UM_R >= end ? HDR_LAST : 0);
+                    h.flags = (t0 == beg ? HDR_FIRST : 0) | (t0 + C::R >= end ? HDR_LAST : 0);
                     h.cnt = (int32_t)(end - beg);
-                    sts_s32x4(ptx::smem_u32(mt + 256), make_int4(h.live_n, h.row, h.flags, h.cnt));
+                    sts_s32x4(ptx::smem_u32(mt + 8 * C::R), make_int4(h.live_n, h.row, h.flags, h.cnt));
                     ptx::mbar_arrive(&s.meta_full[ms]);    // release: header visible to the waiters
                 }
             }
@@ -276,7 +286,7 @@ __device__ __forceinline__ void umma_role_meta(const RowStepParams& p, const Umm
         unsigned char* mt = s.meta + (size_t)ms * C::META_BYTES;
         ptx::cp_async_mbar_arrive_noinc(&s.meta_full[ms]);
         if (lane == 0) {
-            sts_s32x4(ptx::smem_u32(mt + 256), make_int4(0, -1, HDR_END, 0));
+            sts_s32x4(ptx::smem_u32(mt + 8 * C::R), make_int4(0, -1, HDR_END, 0));
             ptx::mbar_arrive(&s.meta_full[ms]);
         }
     }
@@ -302,13 +312,16 @@ __device__ __forceinline__ void umma_role_gather(const RowStepParams& p, const U
         ptx::mbar_wait(&s.empty[slot], ph ^ 1, 11, (int)sg);
         const uint32_t idx_a = ptx::smem_u32(s.meta + (size_t)ms * C::META_BYTES);
         const uint32_t st_addr = ptx::smem_u32(s.stages + (size_t)slot * C::STAGE_STRIDE);
-        const int32_t ixb = lds_s32(idx_a + 4u * (uint32_t)lane);
+        int32_t ixb[C::RL];
 #pragma unroll
-        for (int t = 0; t < UM_R / 4; ++t) {
+        for (int j = 0; j < C::RL; ++j) ixb[j] = lds_s32(idx_a + 4u * (uint32_t)(lane + 32 * j));
+#pragma unroll
+        for (int t = 0; t < C::R / 4; ++t) {
+            if ((t & ~3) * 4 >= live_n) break;         // 16-rating MMA steps past the ragged end are not issued
             const int rating = 4 * t + r4;             // = 8 kb + rr
             const int kb = t >> 1, rr = (t & 1) * 4 + r4;
             const bool live = rating < live_n;
-            const int32_t ix = __shfl_sync(0xffffffffu, ixb, rating);
+            const int32_t ix = __shfl_sync(0xffffffffu, ixb[t / 8], rating & 31);
             const unsigned char* src = H + (size_t)ix * C::REC_BYTES + ch * 16;
             const uint32_t dst = st_addr + (uint32_t)(kb * C::NA * 1024 + rr * 128 + ((ch ^ rr) << 4));
 #pragma unroll
@@ -317,10 +330,11 @@ __device__ __forceinline__ void umma_role_gather(const RowStepParams& p, const U
                 ptx::cp_async16_zfill(dst + at * 1024, src + mb * 128, live ? 16u : 0u);
             }
         }
-        {
-            const bool live = lane < live_n;
-            asm volatile("cp.async.ca.shared.global [%0], [%1], 4, %2;" ::"r"(ptx::smem_u32(s.bias + slot * 128 + lane * 4)),
-                         "l"(p.bias_other + ixb), "r"(live ? 4u : 0u)
+#pragma unroll
+        for (int j = 0; j < C::RL; ++j) {
+            const bool live = lane + 32 * j < live_n;
+            asm volatile("cp.async.ca.shared.global [%0], [%1], 4, %2;" ::"r"(ptx::smem_u32(s.bias + slot * C::BIAS_BYTES + (lane + 32 * j) * 4)),
+                         "l"(p.bias_other + ixb[j]), "r"(live ? 4u : 0u)
                          : "memory");
         }
         ptx::cp_async_mbar_arrive_noinc(&s.full[slot]);
@@ -368,27 +382,27 @@ __device__ __forceinline__ void umma_role_prep(const RowStepParams& p, const Umm
         }
         if (flags & HDR_FIRST) { tsum = 0.0f; qq = 0.0f; }
         ptx::mbar_wait(&s.full[slot], ph, 5, (int)sg);
-        const bool live = lane < live_n;
-        const float v = lds_f32v(ptx::smem_u32(s.meta + (size_t)ms * C::META_BYTES + 128) + 4u * (uint32_t)lane);
-        const float bo = lds_f32v(ptx::smem_u32(s.bias + slot * 128) + 4u * (uint32_t)lane);
-        const float q = live ? v - (mu + bo) : 0.0f;
-        tsum += q;
-        qq = fmaf(q, q, qq);
-        const __nv_bfloat16 qh = __float2bfloat16_rn(q);
-        const __nv_bfloat16 ql = __float2bfloat16_rn(q - __bfloat162float(qh));
-        const __nv_bfloat162 w0 = __halves2bfloat162(qh, ql);
-        const __nv_bfloat162 w1 = __halves2bfloat162(__float2bfloat16_rn(live ? 1.0f : 0.0f), __float2bfloat16_rn(0.0f));
-        uint4 c0;
-        c0.x = *reinterpret_cast<const uint32_t*>(&w0);
-        c0.y = *reinterpret_cast<const uint32_t*>(&w1);
-        c0.z = 0u; c0.w = 0u;
-        unsigned char* qa = s.stages + (size_t)slot * C::STAGE_STRIDE + q_off;
-        sts_s32x4(ptx::smem_u32(qa + (rr << 4)), make_int4((int)c0.x, (int)c0.y, 0, 0));    // columns 0..7  (chunk 0 ^ rr)
-        sts_s32x4(ptx::smem_u32(qa + ((rr ^ 1) << 4)), make_int4(0, 0, 0, 0));              // columns 8..15 (chunk 1 ^ rr)
+#pragma unroll
+        for (int j = 0; j < C::RL; ++j) {
+            const uint32_t rating = (uint32_t)lane + 32u * j;
+            const bool live = (int)rating < live_n;
+            const float v = lds_f32v(ptx::smem_u32(s.meta + (size_t)ms * C::META_BYTES + 4 * C::R) + 4u * rating);
+            const float bo = lds_f32v(ptx::smem_u32(s.bias + slot * C::BIAS_BYTES) + 4u * rating);
+            const float q = live ? v - (mu + bo) : 0.0f;
+            tsum += q;
+            qq = fmaf(q, q, qq);
+            const __nv_bfloat16 qh = __float2bfloat16_rn(q);
+            const __nv_bfloat16 ql = __float2bfloat16_rn(q - __bfloat162float(qh));
+            const __nv_bfloat162 w0 = __halves2bfloat162(qh, ql);
+            const __nv_bfloat162 w1 = __halves2bfloat162(__float2bfloat16_rn(live ? 1.0f : 0.0f), __float2bfloat16_rn(0.0f));
+            const uint32_t qa = ptx::smem_u32(s.stages + (size_t)slot * C::STAGE_STRIDE + q_off) + 4u * j * C::NA * 1024u;
+            sts_s32x4(qa + (rr << 4), make_int4(*reinterpret_cast<const int*>(&w0), *reinterpret_cast<const int*>(&w1), 0, 0));   // columns 0..7  (chunk 0 ^ rr)
+            sts_s32x4(qa + ((rr ^ 1) << 4), make_int4(0, 0, 0, 0));                                                              // columns 8..15 (chunk 1 ^ rr)
+        }
         ptx::fence_proxy_async();
         __syncwarp();
         if (lane == 0) {
-            sts_s32(ptx::smem_u32(s.sflags + slot), flags);
+            sts_s32(ptx::smem_u32(s.sflags + slot), flags | (live_n << 8));
             ptx::mbar_arrive(&s.prep_full[slot]);                    // release: atom + flags visible to the mma warp
             ptx::mbar_arrive(&s.meta_empty[ms]);                     // idx/hdr (gather) and val (this warp) consumed
         }
@@ -434,7 +448,8 @@ __device__ __forceinline__ void umma_role_mma(const RowStepParams& p, const Umma
     for (uint32_t sg = 0;; ++sg) {
         const uint32_t slot = sg % C::STAGES, ph = (sg / C::STAGES) & 1;
         ptx::mbar_wait(&s.prep_full[slot], ph, 13, (int)sg);
-        const int flags = lds_s32(ptx::smem_u32(s.sflags + slot));
+        const int sflag = lds_s32(ptx::smem_u32(s.sflags + slot));
+        const int flags = sflag & 0xff, live_n = sflag >> 8;
         if (flags & HDR_END) break;
         if (flags & HDR_FIRST) {
             const uint32_t pr = nrow / C::RPB, h = nrow % C::RPB;
@@ -447,7 +462,8 @@ __device__ __forceinline__ void umma_role_mma(const RowStepParams& p, const Umma
         if (ptx::elect_one()) {
             const uint64_t d0 = tmpl + (uint64_t)(stage0 + slot * (uint32_t)(C::STAGE_STRIDE >> 4));
 #pragma unroll
-            for (int ks = 0; ks < UM_R / 16; ++ks) {
+            for (int ks = 0; ks < C::R / 16; ++ks) {
+                if (ks * 16 >= live_n) break;                       // 16-rating steps past the ragged end hold nothing
                 const uint64_t hi_desc = d0 + (uint64_t)(ks * (2 * SBO >> 4));
                 const uint64_t lo_desc = hi_desc + (uint64_t)(LO_OFF >> 4);
                 // [A | c s] += hi^T [hi | q] + lo^T [hi | q] + hi^T lo : TMEM lane i = row i of A, then (F^T q, F^T 1)
