@@ -36,7 +36,6 @@
 namespace b200als {
 
 constexpr int UM_RD = 16;         // row-descriptor ring
-constexpr int UM_GATHER_WARPS = 4;
 
 constexpr int HDR_FIRST = 1, HDR_LAST = 2, HDR_END = 4;
 
@@ -69,14 +68,17 @@ struct UmmaCfg {
     static constexpr int RL = R / 32;                       // ratings per lane of a single-warp role
     static constexpr int STAGE_DATA = (R / 8) * NA * 1024;
     static constexpr int STAGE_STRIDE = STAGE_DATA;         // data ring (1024-byte aligned atoms)
-    static constexpr int META = 32;                         // (index, rating) ring: runs far ahead of the data ring
+#ifndef B200ALS_NG128
+#define B200ALS_NG128 3
+#endif
+    static constexpr int META = (K == 64) ? 32 : (B200ALS_NG128 > 3 ? 16 : 32);   // (index, rating) ring: runs far ahead of the data ring
     static constexpr int META_BYTES = 8 * R + 32;           // idx[R] int32 | val[R] float | StageHdr | pad
     static constexpr int BIAS_BYTES = 4 * R;
-    static constexpr int STAGES = (K == 64) ? (R == 64 ? 4 : 6) : 4;
+    static constexpr int STAGES = (K == 64) ? (R == 64 ? 4 : 6) : (B200ALS_NG128 > 3 ? 3 : 4);
 #ifndef B200ALS_NG64
 #define B200ALS_NG64 4
 #endif
-    static constexpr int NG = (K == 64) ? B200ALS_NG64 : 3; // solver groups (4 warps each); 3 named barriers per group
+    static constexpr int NG = (K == 64) ? B200ALS_NG64 : B200ALS_NG128; // solver groups (4 warps each); 3 named barriers per group
     static constexpr int RPB = (K == 64) ? 2 : 1;           // rows per TMEM accumulator buffer
     static constexpr int RPW = (K == 64) ? 16 : 32;         // matrix rows per solver warp
     static constexpr int NBUF = (K == 64) ? 6 : 3;          // TMEM accumulator buffers
@@ -85,7 +87,10 @@ struct UmmaCfg {
     static constexpr int SOLVER_WARPS = NG * 4;
     static constexpr int WARP_META = SOLVER_WARPS;
     static constexpr int WARP_GATHER0 = SOLVER_WARPS + 1;
-    static constexpr int WARP_PREP = SOLVER_WARPS + 1 + UM_GATHER_WARPS;
+    // gather warps stride the stage sequence; more warps than ring slots would let a warp wait on a slot two
+    // uses ahead, where the mbarrier phase parity aliases
+    static constexpr int GATHER_WARPS = STAGES < 4 ? STAGES : 4;
+    static constexpr int WARP_PREP = SOLVER_WARPS + 1 + GATHER_WARPS;
     static constexpr int WARP_MMA = WARP_PREP + 1;
     static constexpr int THREADS = (SOLVER_WARPS + 8) * 32;  // whole warpgroups: solvers | 7 producer warps + 1 idle
     // setmaxnreg split of the CTA's register allocation (launch: 65536 / THREADS rounded down to 8)
@@ -97,7 +102,7 @@ struct UmmaCfg {
     static constexpr int MATS = NG * RPB;
     static constexpr int MAT_FLOATS = ldl_mat_floats<K>();
     static constexpr int RED_FLOATS = NG * 4 * RPB * 4;     // per group: [warp][matrix][4]
-    static constexpr int NBAR = (2 * META + 3 * STAGES + 2 * NBUF + 2 * UM_RD + 1) & ~1;   // even: RowDesc ring stays 16-byte aligned
+    static constexpr int NBAR = (2 * META + 3 * STAGES + NBUF + NG + 2 * UM_RD + 1) & ~1;   // even: RowDesc ring stays 16-byte aligned
     static constexpr size_t smem_bytes = 1024 /*align slack*/ + (size_t)STAGES * (STAGE_STRIDE + BIAS_BYTES + 16) +
                                          (size_t)META * META_BYTES + (size_t)MATS * MAT_FLOATS * 4 +
                                          (size_t)RED_FLOATS * 4 + (size_t)NBAR * 8 + (size_t)UM_RD * 16 + 128 + 128;
@@ -161,7 +166,7 @@ __device__ __forceinline__ void umma_carve(unsigned char* raw, UmmaSmem& s) {
     s.prep_full = s.full + C::STAGES;
     s.empty = s.prep_full + C::STAGES;
     s.acc_full = s.empty + C::STAGES;
-    s.acc_empty = s.acc_full + C::NBUF;
+    s.acc_empty = s.acc_full + C::NG;
     s.rd_full = s.acc_empty + C::NBUF;
     s.rd_empty = s.rd_full + UM_RD;
     s.rd = reinterpret_cast<RowDesc*>(bars + C::NBAR);
@@ -280,7 +285,7 @@ __device__ __forceinline__ void umma_role_meta(const RowStepParams& p, const Umm
     }
     // end-of-work stages: one per gather warp (each walks its own stride of the stage sequence);
     // the prep and mma warps stop at the first
-    for (int e = 0; e < UM_GATHER_WARPS; ++e, ++sg) {
+    for (int e = 0; e < C::GATHER_WARPS; ++e, ++sg) {
         const uint32_t ms = sg % C::META, mph = (sg / C::META) & 1;
         ptx::mbar_wait(&s.meta_empty[ms], mph ^ 1, 1, (int)sg);
         unsigned char* mt = s.meta + (size_t)ms * C::META_BYTES;
@@ -302,7 +307,7 @@ __device__ __forceinline__ void umma_role_gather(const RowStepParams& p, const U
     using C = UmmaCfg<K>;
     const int ch = lane & 7;               // 16-byte chunk inside the 128-byte line
     const int r4 = lane >> 3;              // rating inside its group of 4
-    for (uint32_t sg = (uint32_t)w;; sg += UM_GATHER_WARPS) {
+    for (uint32_t sg = (uint32_t)w;; sg += C::GATHER_WARPS) {
         const uint32_t slot = sg % C::STAGES, ph = (sg / C::STAGES) & 1;
         const uint32_t ms = sg % C::META, mph = (sg / C::META) & 1;
         ptx::mbar_wait(&s.meta_full[ms], mph, 2, (int)sg);
@@ -443,7 +448,7 @@ __device__ __forceinline__ void umma_role_mma(const RowStepParams& p, const Umma
     const uint64_t tmpl = ptx::smem_desc(0u, LBO, SBO, ptx::SWZ_128B);
     const uint32_t stage0 = ptx::smem_u32(s.stages) >> 4;
     uint32_t nrow = 0;                                 // rows started so far
-    uint32_t buf = 0, d_main = 0;
+    uint32_t buf = 0, grp = 0, d_main = 0;             // accumulator buffer / solver group of the current pair
     bool first = true;
     for (uint32_t sg = 0;; ++sg) {
         const uint32_t slot = sg % C::STAGES, ph = (sg / C::STAGES) & 1;
@@ -454,6 +459,7 @@ __device__ __forceinline__ void umma_role_mma(const RowStepParams& p, const Umma
         if (flags & HDR_FIRST) {
             const uint32_t pr = nrow / C::RPB, h = nrow % C::RPB;
             buf = pr % C::NBUF;
+            grp = pr % C::NG;
             if (h == 0) ptx::mbar_wait(&s.acc_empty[buf], ((pr / C::NBUF) & 1) ^ 1, 3, (int)nrow);   // drained by its solver group
             d_main = tmem + buf * C::ACC_STRIDE + ((h * 16u) << 16);
             first = true;
@@ -472,7 +478,7 @@ __device__ __forceinline__ void umma_role_mma(const RowStepParams& p, const Umma
                 ptx::umma_bf16(d_main, hi_desc, lo_desc, IDESC_LO, 1u);
             }
             ptx::umma_commit(&s.empty[slot]);                        // stage reusable once these MMAs finish
-            if (flags & HDR_LAST) ptx::umma_commit(&s.acc_full[buf]);
+            if (flags & HDR_LAST) ptx::umma_commit(&s.acc_full[grp]);      // one 'accumulator ready' barrier per solver group
         }
         __syncwarp();
         first = false;
@@ -480,7 +486,7 @@ __device__ __forceinline__ void umma_role_mma(const RowStepParams& p, const Umma
     }
     // odd tail: the second half of the last accumulator pair holds no row
     if (nrow % C::RPB != 0) {
-        if (lane == 0) ptx::mbar_arrive(&s.acc_full[buf]);
+        if (lane == 0) ptx::mbar_arrive(&s.acc_full[grp]);
     }
 }
 
@@ -556,7 +562,7 @@ __device__ __forceinline__ void umma_role_solver(const RowStepParams& p, const U
         if (q == 0 && seg == 0) { *bad = 0; *lastf = 0; }
 
         const uint32_t buf = pr % C::NBUF;
-        ptx::mbar_wait(&s.acc_full[buf], (pr / C::NBUF) & 1, 7, (int)pr);
+        ptx::mbar_wait(&s.acc_full[g], (pr / C::NG) & 1, 7, (int)pr);   // per group: with NG > NBUF a per-buffer barrier's parity would alias
         ptx::tc_fence_after();
         TICK(1);
         const uint32_t trow = tmem + buf * C::ACC_STRIDE + ((uint32_t)(32 * q) << 16);
@@ -724,10 +730,8 @@ __global__ void __launch_bounds__(UmmaCfg<K>::THREADS, 1) row_step_umma_kernel(c
             ptx::mbar_init(&s.prep_full[i], 1);
             ptx::mbar_init(&s.empty[i], 1);
         }
-        for (int i = 0; i < C::NBUF; ++i) {
-            ptx::mbar_init(&s.acc_full[i], C::RPB);
-            ptx::mbar_init(&s.acc_empty[i], 128);
-        }
+        for (int i = 0; i < C::NG; ++i) ptx::mbar_init(&s.acc_full[i], C::RPB);
+        for (int i = 0; i < C::NBUF; ++i) ptx::mbar_init(&s.acc_empty[i], 128);
         for (int i = 0; i < UM_RD; ++i) {
             ptx::mbar_init(&s.rd_full[i], 1);
             ptx::mbar_init(&s.rd_empty[i], 1);
