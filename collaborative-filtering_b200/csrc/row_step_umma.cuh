@@ -84,6 +84,11 @@ struct UmmaCfg {
     static constexpr int NBUF = (K == 64) ? 6 : 3;          // TMEM accumulator buffers
     static constexpr int ACC_STRIDE = K + 16;               // TMEM columns per buffer: main | [c_hi,c_lo,s,..]
     static constexpr int D2_COL = K;
+    // 'accumulator ready' barriers, indexed pair % ACCF.  Per buffer when buffers outnumber groups (the MMA warp
+    // may finish two pairs of one group before it looks), per group when groups outnumber buffers (a group
+    // may wait for a buffer's next use before the previous one completed) — either way a waiter never
+    // sees the phase parity alias.
+    static constexpr int ACCF = NG > NBUF ? NG : NBUF;
     static constexpr int SOLVER_WARPS = NG * 4;
     static constexpr int WARP_META = SOLVER_WARPS;
     static constexpr int WARP_GATHER0 = SOLVER_WARPS + 1;
@@ -102,7 +107,7 @@ struct UmmaCfg {
     static constexpr int MATS = NG * RPB;
     static constexpr int MAT_FLOATS = ldl_mat_floats<K>();
     static constexpr int RED_FLOATS = NG * 4 * RPB * 4;     // per group: [warp][matrix][4]
-    static constexpr int NBAR = (2 * META + 3 * STAGES + NBUF + NG + 2 * UM_RD + 1) & ~1;   // even: RowDesc ring stays 16-byte aligned
+    static constexpr int NBAR = (2 * META + 3 * STAGES + NBUF + ACCF + 2 * UM_RD + 1) & ~1;   // even: RowDesc ring stays 16-byte aligned
     static constexpr size_t smem_bytes = 1024 /*align slack*/ + (size_t)STAGES * (STAGE_STRIDE + BIAS_BYTES + 16) +
                                          (size_t)META * META_BYTES + (size_t)MATS * MAT_FLOATS * 4 +
                                          (size_t)RED_FLOATS * 4 + (size_t)NBAR * 8 + (size_t)UM_RD * 16 + 128 + 128;
@@ -166,7 +171,7 @@ __device__ __forceinline__ void umma_carve(unsigned char* raw, UmmaSmem& s) {
     s.prep_full = s.full + C::STAGES;
     s.empty = s.prep_full + C::STAGES;
     s.acc_full = s.empty + C::STAGES;
-    s.acc_empty = s.acc_full + C::NG;
+    s.acc_empty = s.acc_full + C::ACCF;
     s.rd_full = s.acc_empty + C::NBUF;
     s.rd_empty = s.rd_full + UM_RD;
     s.rd = reinterpret_cast<RowDesc*>(bars + C::NBAR);
@@ -459,7 +464,7 @@ __device__ __forceinline__ void umma_role_mma(const RowStepParams& p, const Umma
         if (flags & HDR_FIRST) {
             const uint32_t pr = nrow / C::RPB, h = nrow % C::RPB;
             buf = pr % C::NBUF;
-            grp = pr % C::NG;
+            grp = pr % C::ACCF;
             if (h == 0) ptx::mbar_wait(&s.acc_empty[buf], ((pr / C::NBUF) & 1) ^ 1, 3, (int)nrow);   // drained by its solver group
             d_main = tmem + buf * C::ACC_STRIDE + ((h * 16u) << 16);
             first = true;
@@ -478,7 +483,7 @@ __device__ __forceinline__ void umma_role_mma(const RowStepParams& p, const Umma
                 ptx::umma_bf16(d_main, hi_desc, lo_desc, IDESC_LO, 1u);
             }
             ptx::umma_commit(&s.empty[slot]);                        // stage reusable once these MMAs finish
-            if (flags & HDR_LAST) ptx::umma_commit(&s.acc_full[grp]);      // one 'accumulator ready' barrier per solver group
+            if (flags & HDR_LAST) ptx::umma_commit(&s.acc_full[grp]);
         }
         __syncwarp();
         first = false;
@@ -562,7 +567,7 @@ __device__ __forceinline__ void umma_role_solver(const RowStepParams& p, const U
         if (q == 0 && seg == 0) { *bad = 0; *lastf = 0; }
 
         const uint32_t buf = pr % C::NBUF;
-        ptx::mbar_wait(&s.acc_full[g], (pr / C::NG) & 1, 7, (int)pr);   // per group: with NG > NBUF a per-buffer barrier's parity would alias
+        ptx::mbar_wait(&s.acc_full[pr % C::ACCF], (pr / C::ACCF) & 1, 7, (int)pr);
         ptx::tc_fence_after();
         TICK(1);
         const uint32_t trow = tmem + buf * C::ACC_STRIDE + ((uint32_t)(32 * q) << 16);
@@ -730,7 +735,7 @@ __global__ void __launch_bounds__(UmmaCfg<K>::THREADS, 1) row_step_umma_kernel(c
             ptx::mbar_init(&s.prep_full[i], 1);
             ptx::mbar_init(&s.empty[i], 1);
         }
-        for (int i = 0; i < C::NG; ++i) ptx::mbar_init(&s.acc_full[i], C::RPB);
+        for (int i = 0; i < C::ACCF; ++i) ptx::mbar_init(&s.acc_full[i], C::RPB);
         for (int i = 0; i < C::NBUF; ++i) ptx::mbar_init(&s.acc_empty[i], 128);
         for (int i = 0; i < UM_RD; ++i) {
             ptx::mbar_init(&s.rd_full[i], 1);
