@@ -45,11 +45,13 @@ struct StageHdr {                 // 16 bytes at the end of a meta slot
     int32_t flags;
     int32_t cnt;
 };
-struct RowDesc {                  // 16 bytes
-    int32_t row;                  // < 0: no row (odd tail / end of work)
+struct RowDesc {                  // 32 bytes: one 16-byte half per prep warp
+    int32_t row;                  // -1: no row (odd tail / end of work), <= -2: piece of a split row
     int32_t cnt;
-    float tsum;                   // sum q
+    float tsum;                   // sum q   over the stages of prep warp 0
     float qq;                     // sum q^2
+    float tsum1, qq1;             // the same over the stages of prep warp 1
+    int32_t pad[2];
 };
 
 template <int K>
@@ -96,7 +98,8 @@ struct UmmaCfg {
     // uses ahead, where the mbarrier phase parity aliases
     static constexpr int GATHER_WARPS = STAGES < 4 ? STAGES : 4;
     static constexpr int WARP_PREP = SOLVER_WARPS + 1 + GATHER_WARPS;
-    static constexpr int WARP_MMA = WARP_PREP + 1;
+    static constexpr int PREP_WARPS = 2;                     // stage sg is prepared by warp sg % 2
+    static constexpr int WARP_MMA = WARP_PREP + PREP_WARPS;
     static constexpr int THREADS = (SOLVER_WARPS + 8) * 32;  // whole warpgroups: solvers | 7 producer warps + 1 idle
     // setmaxnreg split of the CTA's register allocation (launch: 65536 / THREADS rounded down to 8)
     static constexpr int REG_PRODUCER = 48;
@@ -110,7 +113,7 @@ struct UmmaCfg {
     static constexpr int NBAR = (2 * META + 3 * STAGES + NBUF + ACCF + 2 * UM_RD + 1) & ~1;   // even: RowDesc ring stays 16-byte aligned
     static constexpr size_t smem_bytes = 1024 /*align slack*/ + (size_t)STAGES * (STAGE_STRIDE + BIAS_BYTES + 16) +
                                          (size_t)META * META_BYTES + (size_t)MATS * MAT_FLOATS * 4 +
-                                         (size_t)RED_FLOATS * 4 + (size_t)NBAR * 8 + (size_t)UM_RD * 16 + 128 + 128;
+                                         (size_t)RED_FLOATS * 4 + (size_t)NBAR * 8 + (size_t)UM_RD * 32 + 128 + 128;
     static_assert(smem_bytes <= 232448, "tcgen05 Gram kernel exceeds 227 KB of shared memory");
     static_assert(NBUF * ACC_STRIDE <= 512, "TMEM columns");
 };
@@ -354,21 +357,37 @@ __device__ __forceinline__ void umma_role_gather(const RowStepParams& p, const U
 
 // ---- prep warp: q = rating - mu - bias, the [q_hi, q_lo, 1] atom of the stage, row descriptors ----
 template <int K>
-__device__ __forceinline__ void umma_publish_desc(const UmmaSmem& s, uint32_t n, int lane, int32_t row, int32_t cnt,
-                                                  float tsum, float qq) {
+__device__ __forceinline__ void umma_publish_desc(const UmmaSmem& s, uint32_t n, int lane, int pw, bool owner,
+                                                  int32_t row, int32_t cnt, float tsum, float qq) {
+    // both prep warps write their half of descriptor n (the owner of the row's last stage also the row and count)
     const uint32_t rd = n % UM_RD, rph = (n / UM_RD) & 1;
     ptx::mbar_wait(&s.rd_empty[rd], rph ^ 1, 6, (int)n);
     if (lane == 0) {
-        RowDesc d;
-        d.row = row; d.cnt = cnt; d.tsum = tsum; d.qq = qq;
-        sts_s32x4(ptx::smem_u32(&s.rd[rd]), make_int4(d.row, d.cnt, __float_as_int(d.tsum), __float_as_int(d.qq)));
-        ptx::mbar_arrive(&s.rd_full[rd]);                  // release
+        const uint32_t a = ptx::smem_u32(&s.rd[rd]);
+        if (pw == 0) {
+            if (owner) {
+                sts_s32x4(a, make_int4(row, cnt, __float_as_int(tsum), __float_as_int(qq)));
+            } else {
+                sts_s32(a + 8, __float_as_int(tsum));
+                sts_s32(a + 12, __float_as_int(qq));
+            }
+        } else {
+            if (owner) {
+                sts_s32(a, row);
+                sts_s32(a + 4, cnt);
+            }
+            sts_s32(a + 16, __float_as_int(tsum));
+            sts_s32(a + 20, __float_as_int(qq));
+        }
+        ptx::mbar_arrive(&s.rd_full[rd]);                  // release (count 2: one per prep warp)
     }
     __syncwarp();
 }
 
+// Two prep warps; warp pw prepares the stages sg % 2 == pw and only reads the headers of the others (row
+// boundaries).  Each keeps the row's sum q / sum q^2 over ITS stages and publishes its half of the row descriptor.
 template <int K>
-__device__ __forceinline__ void umma_role_prep(const RowStepParams& p, const UmmaSmem& s, int lane) {
+__device__ __forceinline__ void umma_role_prep(const RowStepParams& p, const UmmaSmem& s, int pw, int lane) {
     using C = UmmaCfg<K>;
     const float mu = *p.mu;
     uint32_t nrow = 0;                                 // rows finished so far
@@ -379,57 +398,65 @@ __device__ __forceinline__ void umma_role_prep(const RowStepParams& p, const Umm
     for (uint32_t sg = 0;; ++sg) {
         const uint32_t slot = sg % C::STAGES, ph = (sg / C::STAGES) & 1;
         const uint32_t ms = sg % C::META, mph = (sg / C::META) & 1;
+        const bool mine = (int)(sg & 1) == pw;
         ptx::mbar_wait(&s.meta_full[ms], mph, 4, (int)sg);
         const StageHdr hd = stage_hdr<K>(s, ms);
         const int flags = hd.flags, live_n = hd.live_n, hrow = hd.row, hcnt = hd.cnt;
         if (flags & HDR_END) {
-            ptx::mbar_wait(&s.empty[slot], ph ^ 1, 12, (int)sg);      // the slot's previous MMAs (and flag read) are done
-            if (lane == 0) {
-                sts_s32(ptx::smem_u32(s.sflags + slot), HDR_END);
-                ptx::mbar_arrive(&s.prep_full[slot]);
+            if (mine) {
+                ptx::mbar_wait(&s.empty[slot], ph ^ 1, 12, (int)sg);  // the slot's previous MMAs (and flag read) are done
+                if (lane == 0) {
+                    sts_s32(ptx::smem_u32(s.sflags + slot), HDR_END);
+                    ptx::mbar_arrive(&s.prep_full[slot]);
+                }
             }
             break;
         }
         if (flags & HDR_FIRST) { tsum = 0.0f; qq = 0.0f; }
-        ptx::mbar_wait(&s.full[slot], ph, 5, (int)sg);
+        if (mine) {
+            ptx::mbar_wait(&s.full[slot], ph, 5, (int)sg);
 #pragma unroll
-        for (int j = 0; j < C::RL; ++j) {
-            const uint32_t rating = (uint32_t)lane + 32u * j;
-            const bool live = (int)rating < live_n;
-            const float v = lds_f32v(ptx::smem_u32(s.meta + (size_t)ms * C::META_BYTES + 4 * C::R) + 4u * rating);
-            const float bo = lds_f32v(ptx::smem_u32(s.bias + slot * C::BIAS_BYTES) + 4u * rating);
-            const float q = live ? v - (mu + bo) : 0.0f;
-            tsum += q;
-            qq = fmaf(q, q, qq);
-            const __nv_bfloat16 qh = __float2bfloat16_rn(q);
-            const __nv_bfloat16 ql = __float2bfloat16_rn(q - __bfloat162float(qh));
-            const __nv_bfloat162 w0 = __halves2bfloat162(qh, ql);
-            const __nv_bfloat162 w1 = __halves2bfloat162(__float2bfloat16_rn(live ? 1.0f : 0.0f), __float2bfloat16_rn(0.0f));
-            const uint32_t qa = ptx::smem_u32(s.stages + (size_t)slot * C::STAGE_STRIDE + q_off) + 4u * j * C::NA * 1024u;
-            sts_s32x4(qa + (rr << 4), make_int4(*reinterpret_cast<const int*>(&w0), *reinterpret_cast<const int*>(&w1), 0, 0));   // columns 0..7  (chunk 0 ^ rr)
-            sts_s32x4(qa + ((rr ^ 1) << 4), make_int4(0, 0, 0, 0));                                                              // columns 8..15 (chunk 1 ^ rr)
-        }
-        ptx::fence_proxy_async();
-        __syncwarp();
-        if (lane == 0) {
-            sts_s32(ptx::smem_u32(s.sflags + slot), flags | (live_n << 8));
-            ptx::mbar_arrive(&s.prep_full[slot]);                    // release: atom + flags visible to the mma warp
-            ptx::mbar_arrive(&s.meta_empty[ms]);                     // idx/hdr (gather) and val (this warp) consumed
+            for (int j = 0; j < C::RL; ++j) {
+                const uint32_t rating = (uint32_t)lane + 32u * j;
+                const bool live = (int)rating < live_n;
+                const float v = lds_f32v(ptx::smem_u32(s.meta + (size_t)ms * C::META_BYTES + 4 * C::R) + 4u * rating);
+                const float bo = lds_f32v(ptx::smem_u32(s.bias + slot * C::BIAS_BYTES) + 4u * rating);
+                const float q = live ? v - (mu + bo) : 0.0f;
+                tsum += q;
+                qq = fmaf(q, q, qq);
+                const __nv_bfloat16 qh = __float2bfloat16_rn(q);
+                const __nv_bfloat16 ql = __float2bfloat16_rn(q - __bfloat162float(qh));
+                const __nv_bfloat162 w0 = __halves2bfloat162(qh, ql);
+                const __nv_bfloat162 w1 = __halves2bfloat162(__float2bfloat16_rn(live ? 1.0f : 0.0f), __float2bfloat16_rn(0.0f));
+                const uint32_t qa = ptx::smem_u32(s.stages + (size_t)slot * C::STAGE_STRIDE + q_off) + 4u * j * C::NA * 1024u;
+                sts_s32x4(qa + (rr << 4), make_int4(*reinterpret_cast<const int*>(&w0), *reinterpret_cast<const int*>(&w1), 0, 0));   // columns 0..7  (chunk 0 ^ rr)
+                sts_s32x4(qa + ((rr ^ 1) << 4), make_int4(0, 0, 0, 0));                                                              // columns 8..15 (chunk 1 ^ rr)
+            }
+            ptx::fence_proxy_async();
+            __syncwarp();
+            if (lane == 0) {
+                sts_s32(ptx::smem_u32(s.sflags + slot), flags | (live_n << 8));
+                ptx::mbar_arrive(&s.prep_full[slot]);                // release: atom + flags visible to the mma warp
+                ptx::mbar_arrive(&s.meta_empty[ms]);                 // header and ratings consumed
+            }
+        } else {
+            __syncwarp();
+            if (lane == 0) ptx::mbar_arrive(&s.meta_empty[ms]);      // header consumed
         }
         if (flags & HDR_LAST) {
             // (row, cnt, sum q, sum q^2) -> solver
             const float ts = warp_sum(tsum), qs = warp_sum(qq);
-            umma_publish_desc<K>(s, nrow, lane, hrow, hcnt, ts, qs);
+            umma_publish_desc<K>(s, nrow, lane, pw, mine, hrow, hcnt, ts, qs);
             ++nrow;
         }
     }
     // odd tail: the second half of the last accumulator pair holds no row
     if (nrow % C::RPB != 0) {
-        umma_publish_desc<K>(s, nrow, lane, -1, 0, 0.0f, 0.0f);
+        umma_publish_desc<K>(s, nrow, lane, pw, pw == 0, -1, 0, 0.0f, 0.0f);
         ++nrow;
     }
     // end-of-work descriptors: one empty pair per solver group
-    for (int i = 0; i < C::NG * C::RPB; ++i, ++nrow) umma_publish_desc<K>(s, nrow, lane, -1, 0, 0.0f, 0.0f);
+    for (int i = 0; i < C::NG * C::RPB; ++i, ++nrow) umma_publish_desc<K>(s, nrow, lane, pw, pw == 0, -1, 0, 0.0f, 0.0f);
 }
 
 // ---- mma warp: nothing but tcgen05 issue ------------------------------------------------------
@@ -543,9 +570,10 @@ __device__ __forceinline__ void umma_role_solver(const RowStepParams& p, const U
         TICK(0);
         const int4 d0v = lds_s32x4(ptx::smem_u32(&s.rd[n0 % UM_RD]));
         const int4 dmv = lds_s32x4(ptx::smem_u32(&s.rd[(n0 + h) % UM_RD]));
+        const int4 dm1 = lds_s32x4(ptx::smem_u32(&s.rd[(n0 + h) % UM_RD]) + 16u);
         const int drow = dmv.x;                        // row | -1: none | <= -2: piece (-2 - item) of a split row
         int cnt = dmv.y;
-        float tsum = __int_as_float(dmv.z), qq = __int_as_float(dmv.w);
+        float tsum = __int_as_float(dmv.z) + __int_as_float(dm1.x), qq = __int_as_float(dmv.w) + __int_as_float(dm1.y);
         named_bar_sync(phase_bar, 128);                // everyone holds its descriptor
         if (q == 0 && seg == 0) ptx::mbar_arrive(&s.rd_empty[(n0 + h) % UM_RD]);
         if (d0v.x == -1) break;                        // end of work (rows fill buffers in order)
@@ -728,7 +756,7 @@ __global__ void __launch_bounds__(UmmaCfg<K>::THREADS, 1) row_step_umma_kernel(c
     if (threadIdx.x == 0) {
         for (int i = 0; i < C::META; ++i) {
             ptx::mbar_init(&s.meta_full[i], 33);
-            ptx::mbar_init(&s.meta_empty[i], 1);
+            ptx::mbar_init(&s.meta_empty[i], C::PREP_WARPS);
         }
         for (int i = 0; i < C::STAGES; ++i) {
             ptx::mbar_init(&s.full[i], 32);
@@ -738,7 +766,7 @@ __global__ void __launch_bounds__(UmmaCfg<K>::THREADS, 1) row_step_umma_kernel(c
         for (int i = 0; i < C::ACCF; ++i) ptx::mbar_init(&s.acc_full[i], C::RPB);
         for (int i = 0; i < C::NBUF; ++i) ptx::mbar_init(&s.acc_empty[i], 128);
         for (int i = 0; i < UM_RD; ++i) {
-            ptx::mbar_init(&s.rd_full[i], 1);
+            ptx::mbar_init(&s.rd_full[i], C::PREP_WARPS);
             ptx::mbar_init(&s.rd_empty[i], 1);
         }
         ptx::fence_barrier_init();
@@ -757,8 +785,8 @@ __global__ void __launch_bounds__(UmmaCfg<K>::THREADS, 1) row_step_umma_kernel(c
             umma_role_meta<K>(p, s, lane);
         } else if (warp < C::WARP_PREP) {
             umma_role_gather<K>(p, s, H, warp - C::WARP_GATHER0, lane);
-        } else if (warp == C::WARP_PREP) {
-            umma_role_prep<K>(p, s, lane);
+        } else if (warp < C::WARP_MMA) {
+            umma_role_prep<K>(p, s, warp - C::WARP_PREP, lane);
         } else if (warp == C::WARP_MMA) {
             umma_role_mma<K>(p, s, lane);
         }
