@@ -28,11 +28,15 @@
 // All shared-memory traffic uses explicit .shared addresses (32-bit): generic LD/ST on
 // the carved dynamic buffer would cost the long-scoreboard path.
 #pragma once
+#include <cuda_bf16.h>
+
 #include "common.cuh"
+#include "umma_ptx.cuh"
 
 namespace b200als {
 
 #ifdef B200ALS_TIMING
+__device__ float g_dbg[64];
 __device__ unsigned long long g_timing[16];
 #define LDL_TICK(i) do { if (blockIdx.x == 0 && threadIdx.x == 96) { const long long t__ = clock64(); g_timing[i] += (unsigned long long)(t__ - tl__); tl__ = t__; } } while (0)
 #else
@@ -96,6 +100,17 @@ __device__ __forceinline__ void sts_f32_if(uint32_t a, float v, bool on) {
         : "memory");
 }
 
+__device__ __forceinline__ void sts_b64_if(uint32_t a, uint32_t x, uint32_t y, bool on) {
+    asm volatile(
+        "{\n"
+        ".reg .pred p;\n"
+        "setp.ne.b32 p, %3, 0;\n"
+        "@p st.shared.v2.b32 [%0], {%1, %2};\n"
+        "}\n" ::"r"(a), "r"(x), "r"(y), "r"((int)on)
+        : "memory");
+}
+__device__ __forceinline__ uint32_t bf162_bits(__nv_bfloat162 v) { return *reinterpret_cast<uint32_t*>(&v); }
+
 template <int K, int RPW>
 struct Ldl {
     static constexpr int NW = K / RPW;       // warps per group (4)
@@ -107,6 +122,30 @@ struct Ldl {
     static constexpr uint32_t X_OFF = Z_OFF + 4u * K;
     static constexpr uint32_t INV_OFF = X_OFF + 4u * K;
     static constexpr uint32_t RAW_OFF = INV_OFF + 4u * K;
+
+    // ---- trailing update on the tensor core ----------------------------------------------------
+    // After phase p (p < MMA_PHASES) the rank-RPW update of everything below/right of the panel,
+    //   A[m][n] -= sum_{j in phase p} w_mj w_nj,   w_mj = u_mj / sqrt(d_j),
+    // is ONE tcgen05.mma group accumulating (negated) into the matrix's own TMEM accumulator.  The panel
+    // W is written by the row threads as bf16 hi + lo (three products, like the Gram) in the K-major
+    // no-swizzle canonical layout: 8-row x 16-byte core matrices, 128 B apart along the panel columns,
+    // TILE_SBO apart along the rows.  It lives in the part of the packed column store that only later
+    // phases fill (columns >= RPW (p+1)), which is free until this MMA has completed.  The last phase's
+    // panel would not fit there, so phase NW-1 folds phase NW-2 in with FFMA (left4).
+#ifndef B200ALS_MMA_PHASES
+#define B200ALS_MMA_PHASES (NW - 2)
+#endif
+    static constexpr int MMA_PHASES = B200ALS_MMA_PHASES;
+    static constexpr uint32_t TILE_SBO = (RPW / 8) * 128u;
+    static __host__ __device__ constexpr uint32_t tile_off(int p) {          // bytes from the matrix buffer
+        // first stored element of column J = RPW (p+1) is (J, J) at ldl_col_base(J) + J
+        return ((4u * (uint32_t)(ldl_col_base<K>(RPW * (p + 1)) + RPW * (p + 1))) + 127u) & ~127u;
+    }
+    static __host__ __device__ constexpr uint32_t tile_half(int p) {         // bytes of the hi (or lo) panel
+        return (uint32_t)((K - RPW * (p + 1)) / 8) * TILE_SBO;
+    }
+    static_assert(tile_off(0) + 2 * tile_half(0) <= Z_OFF, "phase-0 panel must fit behind the phase-0 columns");
+    static_assert(tile_off(1) + 2 * tile_half(1) <= Z_OFF, "phase-1 panel must fit behind the phase-1 columns");
 
     // element (i, 4 g) of the column store at col_block(g) + 4 i; the block's columns are S4(g) bytes apart
     static __device__ __forceinline__ uint32_t col_block(const uint32_t cbs, const int g) {
@@ -150,9 +189,13 @@ struct Ldl {
     // nthr = threads of the warps that still own a row >= j0.  `last` (warp-uniform): j0 + 3 is this
     // warp's last row — its pivot rows are all in this warp, nothing below them is ours to update;
     // the warp then signs off on start_bar, which the warps below wait on before their next phase.
+    // tile_on (warp-uniform): the phase feeds a tensor-core update; tile_w: this thread's row lies below the
+    // phase's panel, tile_row = .shared address of its hi-panel row, tile_lo = bytes from there to the lo panel.
     static __device__ __forceinline__ void body4(float (&a)[RPW], float& rhs, bool& ok, const float ridge,
                                                  const int r, const uint32_t cbs, const int j0, const int bar_id,
-                                                 const int start_bar, const int nthr, const bool last) {
+                                                 const int start_bar, const int nthr, const bool last,
+                                                 const uint32_t tile_row, const uint32_t tile_lo, const bool tile_on,
+                                                 const bool tile_w) {
         const int g = j0 >> 2;
         const uint32_t zb = cbs + Z_OFF;
         const uint32_t raw = cbs + RAW_OFF + (uint32_t)(g & 1) * (4u * RAWSZ);           // raw[parity][4][K] | zraw[4]
@@ -194,6 +237,22 @@ struct Ldl {
         sts_f32_if(col0 + S4 + 4u * r, u1, dr >= 1);
         sts_f32_if(col0 + 2u * S4 + 4u * r, u2, dr >= 2);
         sts_f32_if(col0 + 3u * S4 + 4u * r, u3, dr >= 3);
+        if (tile_on) {                                   // warp-uniform: this phase feeds the tensor-core update
+            // w_k = u_k / sqrt(d_k) as bf16 hi + lo, four panel columns = 8 bytes of the row's core-matrix line
+#ifdef B200ALS_MMA_NULL
+            const float w0 = 0.0f, w1 = 0.0f, w2 = 0.0f, w3 = 0.0f;
+#else
+            const float w0 = u0 * rsqrtf(d0), w1 = u1 * rsqrtf(d1), w2 = u2 * rsqrtf(d2), w3 = u3 * rsqrtf(d3);
+#endif
+            const __nv_bfloat162 h01 = __floats2bfloat162_rn(w0, w1), h23 = __floats2bfloat162_rn(w2, w3);
+            const float2 f01 = __bfloat1622float2(h01), f23 = __bfloat1622float2(h23);
+            const __nv_bfloat162 l01 = __floats2bfloat162_rn(w0 - f01.x, w1 - f01.y);
+            const __nv_bfloat162 l23 = __floats2bfloat162_rn(w2 - f23.x, w3 - f23.y);
+            const int jj = j0 % RPW;
+            const uint32_t ta = tile_row + (uint32_t)((jj >> 3) * 128 + (jj & 7) * 2);
+            sts_b64_if(ta, bf162_bits(h01), bf162_bits(h23), tile_w);
+            sts_b64_if(ta + tile_lo, bf162_bits(l01), bf162_bits(l23), tile_w);
+        }
         // rhs of the block rows, forward-substituted; the pivot rows keep theirs in the z array
         const float z0 = zr.x;
         const float z1 = fmaf(-l10, z0, zr.y);
@@ -234,33 +293,104 @@ struct Ldl {
 
     // Factor + forward substitution.  load_window(p, a, is_last) fills a[c] = A[r][RPW p + c] from
     // TMEM (and releases the accumulator after this thread's last load); rhs = this row's
-    // right-hand-side entry, ridge is added on the pivot.  r / q = row and warp in ELIMINATION order.
+    // right-hand-side entry, ridge is added on the pivot.  r / q = row and warp in ELIMINATION order,
+    // r_phys = the row's TMEM lane row (K-1-r for the reversed groups), d_tmem = the matrix's accumulator,
+    // upd_bar = an mbarrier (count 1) of this matrix for the tensor-core updates.
     // Returns true if thread r's pivot was positive.
     template <class LoadWindow>
     static __device__ __forceinline__ bool factor(float rhs, const float ridge, const int r, const int q,
-                                                  const uint32_t cbs, const int bar_id, const int start_bar,
+                                                  const int r_phys, const uint32_t cbs, const int bar_id,
+                                                  const int start_bar, const uint32_t d_tmem, uint64_t* upd_bar,
                                                   LoadWindow&& load_window) {
         bool ok = true;
         float a[RPW];
-#pragma unroll 1
+        const bool rev = r_phys != r;
 #ifdef B200ALS_TIMING
         long long tl__ = clock64();
 #endif
-        for (int p = 0; p <= q; ++p) {
-            load_window(p, a, p == q);
-            LDL_TICK(8);
-            const int nthr = 32 * (NW - p);
-            if (p > 0) {
-                named_bar_sync(start_bar, nthr + 32);          // phase p-1 fully in the column store
-                LDL_TICK(9);
 #pragma unroll 1
+        for (int p = 0; p <= q; ++p) {
+            const int nthr = 32 * (NW - p);
+#ifdef B200ALS_TIMING
+            float before[RPW];
+#endif
+            if (p > 0) {
+                ptx::fence_proxy_async();                      // this thread's panel rows -> async proxy
+                ptx::tc_fence_before();                        // its window loads precede the update MMA
+                named_bar_sync(start_bar, nthr + 32);          // phase p-1 fully in the column store / panel
+                LDL_TICK(9);
+#ifdef B200ALS_TIMING
+                if (p == 1) load_window(1, before, false);
+#endif
+                if (p - 1 < MMA_PHASES) {
+                    if (r == RPW * p) {                        // one thread per matrix issues the update of phase p-1
+                        ptx::tc_fence_after();
+                        const int R0 = RPW * p;
+                        // physical rows needed: [R0, K) forward, [0, K-R0) reversed; the descriptor base is
+                        // moved so that row 0 of the MMA lands R0 rows before the panel (garbage rows only
+                        // touch rows / columns of the accumulator that are finished)
+                        const uint32_t base = cbs + tile_off(p - 1) - (rev ? 0u : (uint32_t)(R0 / 8) * TILE_SBO);
+                        const uint32_t lo = tile_half(p - 1);
+#ifdef B200ALS_MMA_NONEG
+                        constexpr uint32_t IDESC = ptx::idesc_bf16_kk_nega(K, K) & ~(1u << 13);
+#else
+                        constexpr uint32_t IDESC = ptx::idesc_bf16_kk_nega(K, K);
+#endif
+#pragma unroll
+                        for (int ks = 0; ks < RPW / 16; ++ks) {
+#ifdef B200ALS_MMA_ZDESC
+                            // debug: every row / chunk reads the first (zeroed) 16 bytes of the written panel
+                            const uint32_t zb = cbs + tile_off(p - 1) + (rev ? 0u : 0u);
+                            const uint64_t hi_d = ptx::smem_desc(zb, 0u, 0u, ptx::SWZ_NONE);
+                            const uint64_t lo_d = hi_d;
+                            (void)base; (void)lo;
+#else
+                            const uint64_t hi_d = ptx::smem_desc(base + ks * 256u, 128u, TILE_SBO, ptx::SWZ_NONE);
+                            const uint64_t lo_d = ptx::smem_desc(base + lo + ks * 256u, 128u, TILE_SBO, ptx::SWZ_NONE);
+#endif
+#ifndef B200ALS_MMA_SKIP
+                            ptx::umma_bf16(d_tmem, hi_d, hi_d, IDESC, 1u);
+                            ptx::umma_bf16(d_tmem, hi_d, lo_d, IDESC, 1u);
+                            ptx::umma_bf16(d_tmem, lo_d, hi_d, IDESC, 1u);
+#endif
+                        }
+                        ptx::umma_commit(upd_bar);
+                    }
+                    ptx::mbar_wait(upd_bar, (uint32_t)((p - 1) & 1));
+                    ptx::tc_fence_after();
+                }
+            }
+            load_window(p, a, p == q);
+#ifdef B200ALS_TIMING
+            if (p == 1 && blockIdx.x == 0 && bar_id == 1 && r == RPW && g_dbg[63] == 0.0f) {
+                for (int i = 0; i < 16; ++i) { g_dbg[i] = before[i]; g_dbg[16 + i] = a[i]; }
+                g_dbg[63] = 1.0f;
+            }
+#endif
+            LDL_TICK(8);
+#ifdef B200ALS_MMA_NULL
+            if (p > 0) {
+#else
+            if (p > MMA_PHASES) {
+#endif
+                // columns of the phases the tensor core did not fold in
+#pragma unroll 1
+#ifdef B200ALS_MMA_NULL
                 for (int jb = 0; jb < p * (RPW / 4); ++jb) left4(a, r, cbs, jb, p * RPW);
+#else
+                for (int jb = MMA_PHASES * (RPW / 4); jb < p * (RPW / 4); ++jb) left4(a, r, cbs, jb, p * RPW);
+#endif
                 LDL_TICK(10);
             }
+            // this thread's panel row for the update after this phase
+            const bool tile_on = p < MMA_PHASES;
+            const int trow = rev ? r_phys : r - RPW * (p + 1);
+            const uint32_t tile_row = cbs + tile_off(p < MMA_PHASES ? p : 0) + (uint32_t)((trow >> 3) * (int)TILE_SBO + (trow & 7) * 16);
+            const uint32_t tile_lo = tile_half(p < MMA_PHASES ? p : 0);
 #pragma unroll 1
             for (int it = 0; it < RPW / 4; ++it)
                 body4(a, rhs, ok, ridge, r, cbs, p * RPW + 4 * it, bar_id, start_bar, nthr,
-                      p == q && it == RPW / 4 - 1);
+                      p == q && it == RPW / 4 - 1, tile_row, tile_lo, tile_on, tile_on && r >= RPW * (p + 1));
             LDL_TICK(11);
         }
         return ok;

@@ -195,6 +195,9 @@ int b200als_row_step(const b200als_step_args* a, b200als_stream_t stream) {
 }
 
 #ifdef B200ALS_TIMING
+int b200als_debug_floats(float* out64_host) {
+    return cudaMemcpyFromSymbol(out64_host, b200als::g_dbg, 64 * sizeof(float)) == cudaSuccess ? 0 : -2;
+}
 int b200als_debug_timing(unsigned long long* out16_host) {
     return cudaMemcpyFromSymbol(out16_host, b200als::g_timing, 16 * sizeof(unsigned long long)) == cudaSuccess ? 0 : -2;
 }

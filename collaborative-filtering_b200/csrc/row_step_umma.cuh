@@ -110,7 +110,7 @@ struct UmmaCfg {
     static constexpr int MATS = NG * RPB;
     static constexpr int MAT_FLOATS = ldl_mat_floats<K>();
     static constexpr int RED_FLOATS = NG * 4 * RPB * 4;     // per group: [warp][matrix][4]
-    static constexpr int NBAR = (2 * META + 3 * STAGES + NBUF + ACCF + 2 * UM_RD + 1) & ~1;   // even: RowDesc ring stays 16-byte aligned
+    static constexpr int NBAR = (2 * META + 3 * STAGES + NBUF + ACCF + 2 * UM_RD + MATS + 1) & ~1;   // even: RowDesc ring stays 16-byte aligned
     static constexpr size_t smem_bytes = 1024 /*align slack*/ + (size_t)STAGES * (STAGE_STRIDE + BIAS_BYTES + 16) +
                                          (size_t)META * META_BYTES + (size_t)MATS * MAT_FLOATS * 4 +
                                          (size_t)RED_FLOATS * 4 + (size_t)NBAR * 8 + (size_t)UM_RD * 32 + 128 + 128;
@@ -151,7 +151,7 @@ struct UmmaSmem {
     unsigned char* meta;     // [META][META_BYTES]
     float* mats;             // [MATS][MAT_FLOATS]
     float* red;              // [NG][4][RPB][4]
-    uint64_t *meta_full, *meta_empty, *full, *prep_full, *empty, *acc_full, *acc_empty, *rd_full, *rd_empty;
+    uint64_t *meta_full, *meta_empty, *full, *prep_full, *empty, *acc_full, *acc_empty, *rd_full, *rd_empty, *upd;
     RowDesc* rd;             // [UM_RD]
     int32_t* bad;            // [16] non-SPD flags, one per matrix slot | [16] split-row 'last piece' flags
     uint32_t* tmem_base;
@@ -177,6 +177,7 @@ __device__ __forceinline__ void umma_carve(unsigned char* raw, UmmaSmem& s) {
     s.acc_empty = s.acc_full + C::ACCF;
     s.rd_full = s.acc_empty + C::NBUF;
     s.rd_empty = s.rd_full + UM_RD;
+    s.upd = s.rd_empty + UM_RD;                        // [MATS] tensor-core trailing updates of the solver
     s.rd = reinterpret_cast<RowDesc*>(bars + C::NBAR);
     s.bad = reinterpret_cast<int32_t*>(s.rd + UM_RD);
     s.tmem_base = reinterpret_cast<uint32_t*>(s.bad + 32);
@@ -644,6 +645,26 @@ __device__ __forceinline__ void umma_role_solver(const RowStepParams& p, const U
                 qq = __ldcg(tq + 1);
                 cnt = (int)(p.indptr[row + 1] - p.indptr[row]);
             }
+            // the last piece solves from the slot: bring the summed matrix back into the accumulator, where the
+            // factorisation (window loads and tensor-core trailing updates) works on it
+            if (__any_sync(0xffffffffu, from_slot)) {
+#pragma unroll 1
+                for (int c0 = 0; c0 < K; c0 += 16) {
+                    float v[16];
+                    ptx::tmem_ld16(trow + c0, v);
+                    if (from_slot) {
+#pragma unroll
+                        for (int i4 = 0; i4 < 16; i4 += 4) {
+                            const float4 gv = __ldcg(reinterpret_cast<const float4*>(gs + c0 + i4));
+                            v[i4] = gv.x; v[i4 + 1] = gv.y; v[i4 + 2] = gv.z; v[i4 + 3] = gv.w;
+                        }
+                    }
+                    ptx::tmem_st16(trow + c0, v);
+                }
+                ptx::tc_fence_before();
+                named_bar_sync(phase_bar, 128);
+                ptx::tc_fence_after();
+            }
             // nothing to solve in this buffer: hand the accumulator back and move on
             const bool solve_any = __any_sync(0xffffffffu, from_slot || drow >= 0);
             if (!solve_any) {
@@ -655,20 +676,13 @@ __device__ __forceinline__ void umma_role_solver(const RowStepParams& p, const U
         }
         const bool valid = drow >= 0 || from_slot;
 
-        // the matrix stays in TMEM (or in its slot); every phase pulls one RPW-column window of this thread's row
+        // the matrix stays in TMEM; every phase pulls one RPW-column window of this thread's row
         auto load_window = [&](const int ph, float (&w)[C::RPW], const bool is_last) {
             const uint32_t c0 = (uint32_t)(rev ? K - C::RPW * (ph + 1) : C::RPW * ph);
 #pragma unroll
             for (int cc = 0; cc < C::RPW; cc += 16) {
                 float v[16];
                 ptx::tmem_ld16(trow + c0 + cc, v);
-                if (from_slot) {
-#pragma unroll
-                    for (int i4 = 0; i4 < 16; i4 += 4) {
-                        const float4 gv = __ldcg(reinterpret_cast<const float4*>(gs + c0 + cc + i4));
-                        v[i4] = gv.x; v[i4 + 1] = gv.y; v[i4 + 2] = gv.z; v[i4 + 3] = gv.w;
-                    }
-                }
                 if (!rev) {
 #pragma unroll
                     for (int i = 0; i < 16; ++i) w[cc + i] = v[i];
@@ -682,7 +696,9 @@ __device__ __forceinline__ void umma_role_solver(const RowStepParams& p, const U
                 ptx::mbar_arrive(&s.acc_empty[buf]);   // this thread is done with the accumulator
             }
         };
-        const bool ok = L::factor(c_r - bias_old * s_r, ridge, re, qe, cbs, col_bar, start_bar, load_window);
+        const bool ok = L::factor(c_r - bias_old * s_r, ridge, re, qe, r, cbs, col_bar, start_bar,
+                                  tmem + buf * C::ACC_STRIDE + ((uint32_t)(16 * h) << 16), &s.upd[g * C::RPB + h],
+                                  load_window);
         if (!ok && valid) *bad = 1;
         TICK(3);
         const float x = L::backsolve(re, qe, sege, rev ? C::RPW - 1 : 0, cbs, phase_bar);   // barriers inside publish *bad too
@@ -765,6 +781,7 @@ __global__ void __launch_bounds__(UmmaCfg<K>::THREADS, 1) row_step_umma_kernel(c
         }
         for (int i = 0; i < C::ACCF; ++i) ptx::mbar_init(&s.acc_full[i], C::RPB);
         for (int i = 0; i < C::NBUF; ++i) ptx::mbar_init(&s.acc_empty[i], 128);
+        for (int i = 0; i < C::MATS; ++i) ptx::mbar_init(&s.upd[i], 1);
         for (int i = 0; i < UM_RD; ++i) {
             ptx::mbar_init(&s.rd_full[i], C::PREP_WARPS);
             ptx::mbar_init(&s.rd_empty[i], 1);

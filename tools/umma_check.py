@@ -18,7 +18,11 @@ for k in (64, 128):
         for name, path in (("ffma", 1), ("umma", 2)):
             mdl = b200als.ALS(cfg); mdl.gram_path = path
             t0 = time.time()
-            mdl.fit_coo(flat, vals, (m, n), tol=None, verbose=0, sorted_input=True)
+            try:
+                mdl.fit_coo(flat, vals, (m, n), tol=None, verbose=0, sorted_input=True)
+            except Exception as e:
+                print(f"k={k} {m}x{n} {name}: {type(e).__name__} {e}", flush=True)
+                continue
             res[name] = mdl
             print(f"k={k} {m}x{n} nnz={nnz} it={iters} {name}: U {rel(mdl.U,o.U):.2e} V {rel(mdl.V,o.V):.2e} "
                   f"bu {rel(mdl.b_u,o.b_u):.2e} bi {rel(mdl.b_i,o.b_i):.2e} "
