@@ -228,6 +228,9 @@ struct Ldl {
         const float u32 = fmaf(-l31, u21, fmaf(-l30, p0.z, p2.w));
         const float l32 = u32 * i2;
         const float d3 = fmaf(-l32, u32, fmaf(-l31, u31, fmaf(-l30, p0.w, p3.w))), i3 = rcp_approx(d3);
+        // 1/sqrt(d_k) for the tensor-core panel (MUFU.RSQ next to the reciprocals, off the chain)
+        float rs0 = 0.0f, rs1 = 0.0f, rs2 = 0.0f, rs3 = 0.0f;
+        if (tile_on) { rs0 = rsqrtf(d0); rs1 = rsqrtf(d1); rs2 = rsqrtf(d2); rs3 = rsqrtf(d3); }
         // own row: unscaled entries u_k = l_rk d_k and multipliers t_k = l_rk
         const float u0 = a[0], t0 = u0 * i0;
         const float u1 = fmaf(-t0, p0.y, a[1]), t1 = u1 * i1;
@@ -237,22 +240,6 @@ struct Ldl {
         sts_f32_if(col0 + S4 + 4u * r, u1, dr >= 1);
         sts_f32_if(col0 + 2u * S4 + 4u * r, u2, dr >= 2);
         sts_f32_if(col0 + 3u * S4 + 4u * r, u3, dr >= 3);
-        if (tile_on) {                                   // warp-uniform: this phase feeds the tensor-core update
-            // w_k = u_k / sqrt(d_k) as bf16 hi + lo, four panel columns = 8 bytes of the row's core-matrix line
-#ifdef B200ALS_MMA_NULL
-            const float w0 = 0.0f, w1 = 0.0f, w2 = 0.0f, w3 = 0.0f;
-#else
-            const float w0 = u0 * rsqrtf(d0), w1 = u1 * rsqrtf(d1), w2 = u2 * rsqrtf(d2), w3 = u3 * rsqrtf(d3);
-#endif
-            const __nv_bfloat162 h01 = __floats2bfloat162_rn(w0, w1), h23 = __floats2bfloat162_rn(w2, w3);
-            const float2 f01 = __bfloat1622float2(h01), f23 = __bfloat1622float2(h23);
-            const __nv_bfloat162 l01 = __floats2bfloat162_rn(w0 - f01.x, w1 - f01.y);
-            const __nv_bfloat162 l23 = __floats2bfloat162_rn(w2 - f23.x, w3 - f23.y);
-            const int jj = j0 % RPW;
-            const uint32_t ta = tile_row + (uint32_t)((jj >> 3) * 128 + (jj & 7) * 2);
-            sts_b64_if(ta, bf162_bits(h01), bf162_bits(h23), tile_w);
-            sts_b64_if(ta + tile_lo, bf162_bits(l01), bf162_bits(l23), tile_w);
-        }
         // rhs of the block rows, forward-substituted; the pivot rows keep theirs in the z array
         const float z0 = zr.x;
         const float z1 = fmaf(-l10, z0, zr.y);
@@ -288,6 +275,23 @@ struct Ldl {
             a[c4 - 3] = fmaf(-w3, v3.y, fmaf(-w2, v2.y, fmaf(-w1, v1.y, fmaf(-w0, v0.y, a[c4 + 1]))));
             a[c4 - 2] = fmaf(-w3, v3.z, fmaf(-w2, v2.z, fmaf(-w1, v1.z, fmaf(-w0, v0.z, a[c4 + 2]))));
             a[c4 - 1] = fmaf(-w3, v3.w, fmaf(-w2, v2.w, fmaf(-w1, v1.w, fmaf(-w0, v0.w, a[c4 + 3]))));
+        }
+        // after the rank-4 update: the conversions and the two stores stay off the pivot chain
+        if (tile_on) {                                   // warp-uniform: this phase feeds the tensor-core update
+            // w_k = u_k / sqrt(d_k) as bf16 hi + lo, four panel columns = 8 bytes of the row's core-matrix line
+#ifdef B200ALS_MMA_NULL
+            const float w0 = 0.0f, w1 = 0.0f, w2 = 0.0f, w3 = 0.0f;
+#else
+            const float w0 = u0 * rs0, w1 = u1 * rs1, w2 = u2 * rs2, w3 = u3 * rs3;
+#endif
+            const __nv_bfloat162 h01 = __floats2bfloat162_rn(w0, w1), h23 = __floats2bfloat162_rn(w2, w3);
+            const float2 f01 = __bfloat1622float2(h01), f23 = __bfloat1622float2(h23);
+            const __nv_bfloat162 l01 = __floats2bfloat162_rn(w0 - f01.x, w1 - f01.y);
+            const __nv_bfloat162 l23 = __floats2bfloat162_rn(w2 - f23.x, w3 - f23.y);
+            const int jj = j0 % RPW;
+            const uint32_t ta = tile_row + (uint32_t)((jj >> 3) * 128 + (jj & 7) * 2);
+            sts_b64_if(ta, bf162_bits(h01), bf162_bits(h23), tile_w);
+            sts_b64_if(ta + tile_lo, bf162_bits(l01), bf162_bits(l23), tile_w);
         }
     }
 
