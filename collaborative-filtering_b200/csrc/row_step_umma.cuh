@@ -99,6 +99,7 @@ struct UmmaCfg {
     static constexpr int GATHER_WARPS = STAGES < 4 ? STAGES : 4;
     static constexpr int WARP_PREP = SOLVER_WARPS + 1 + GATHER_WARPS;
     static constexpr int PREP_WARPS = 2;                     // stage sg is prepared by warp sg % 2
+    static_assert(STAGES % PREP_WARPS == 0, "a ring slot must always be prepared by the same warp (barrier phase parity)");
     static constexpr int WARP_MMA = WARP_PREP + PREP_WARPS;
     static constexpr int THREADS = (SOLVER_WARPS + 8) * 32;  // whole warpgroups: solvers | 7 producer warps + 1 idle
     // setmaxnreg split of the CTA's register allocation (launch: 65536 / THREADS rounded down to 8)
