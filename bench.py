@@ -43,8 +43,9 @@ WORKLOADS = {
     "tiny": (3000, 2000, 200_000, 64),
 }
 # DRAM bytes (read + write) of one row_step launch, from `ncu --set full` on a single GPU; None = not captured.
-# Source: profiles/r01_ncu_c3_umma_k64_v5.txt (the algorithmic bytes are mostly served by the 126 MB L2).
-NCU_DRAM_BYTES = {("c3", "user"): 198.4e6, ("c3", "item"): 209.2e6}
+# Sources: profiles/r01_ncu_c3_umma_k64_v8.txt, profiles/r01_ncu_c4_umma_k128_v6.txt (at c3 the algorithmic bytes
+# are mostly served by the 126 MB L2; at c4 the item half-step's gathered matrix no longer fits).
+NCU_DRAM_BYTES = {("c3", "user"): 204.5e6, ("c3", "item"): 211.2e6, ("c4", "user"): 1.195e9, ("c4", "item"): 22.23e9}
 WORKLOAD_NAMES = {"c1": "c1_bundled_shape_uv_biases", "c3": "c3_movielens20m_shape",
                   "c4": "c4_netflix_shape", "c4k64": "c4_netflix_shape_k64", "tiny": "tiny_debug"}
 HYPER = dict(lambda_u=5.0, lambda_v=5.0, lambda_bu=3.0, lambda_bi=3.0)
