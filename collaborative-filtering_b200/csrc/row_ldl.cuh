@@ -366,7 +366,7 @@ struct Ldl {
             }
             load_window(p, a, p == q);
 #ifdef B200ALS_TIMING
-            if (p == 1 && blockIdx.x == 0 && bar_id == 1 && r == RPW && g_dbg[63] == 0.0f) {
+            if (p == 1 && blockIdx.x == 0 && start_bar == 3 && r == RPW && g_dbg[63] == 0.0f) {
                 for (int i = 0; i < 16; ++i) { g_dbg[i] = before[i]; g_dbg[16 + i] = a[i]; }
                 g_dbg[63] = 1.0f;
             }
