@@ -56,7 +56,7 @@ __host__ __device__ constexpr int ldl_cols_floats() { return K * K / 2 + 2 * K; 
 // so that the two interleaved matrices of a k=64 group sit 16 banks apart
 template <int K>
 __host__ __device__ constexpr int ldl_mat_floats() {
-    const int raw = ldl_cols_floats<K>() + 3 * K + 2 * (4 * K + 4);   // columns | z | x | 1/d | raw-row scratch (2 buffers)
+    const int raw = ldl_cols_floats<K>() + 3 * K + 2 * (4 * K + 8);   // columns | z | x | 1/d | raw-row scratch (2 buffers)
     return ((raw + 31) / 32) * 32 + 16;
 }
 
@@ -69,6 +69,12 @@ __device__ __forceinline__ float fast_rcp(float d) {
 __device__ __forceinline__ float rcp_approx(float d) {
     float r;
     asm("rcp.approx.ftz.f32 %0, %1;" : "=f"(r) : "f"(d));
+    return r;
+}
+
+__device__ __forceinline__ float rsqrt_approx(float d) {
+    float r;
+    asm("rsqrt.approx.ftz.f32 %0, %1;" : "=f"(r) : "f"(d));
     return r;
 }
 
@@ -109,12 +115,20 @@ __device__ __forceinline__ void sts_b64_if(uint32_t a, uint32_t x, uint32_t y, b
         "}\n" ::"r"(a), "r"(x), "r"(y), "r"((int)on)
         : "memory");
 }
+// Stores WITHOUT a memory clobber: the compiler may batch later (non-aliasing) loads ahead of them; they stay
+// ordered before every later volatile asm (barriers, fences).  Only for addresses the thread does not read back.
+__device__ __forceinline__ void sts_f32_nc(uint32_t a, float v) {
+    asm volatile("st.shared.f32 [%0], %1;" ::"r"(a), "f"(v));
+}
+__device__ __forceinline__ void sts_b64_nc(uint32_t a, uint32_t x, uint32_t y) {
+    asm volatile("st.shared.v2.b32 [%0], {%1, %2};" ::"r"(a), "r"(x), "r"(y));
+}
 __device__ __forceinline__ uint32_t bf162_bits(__nv_bfloat162 v) { return *reinterpret_cast<uint32_t*>(&v); }
 
 template <int K, int RPW>
 struct Ldl {
     static constexpr int NW = K / RPW;       // warps per group (4)
-    static constexpr int RAWSZ = 4 * K + 4;  // floats of one raw-row scratch buffer: rho[4][K] | rhs[4]
+    static constexpr int RAWSZ = 4 * K + 8;  // floats of one raw-row scratch buffer: rho[4][K] | rhs[4] | 4 dummy words (stores of lanes that have nothing to store)
     static_assert(NW == 4, "a solver group is the four TMEM lane quadrants");
 
     // byte offsets inside a matrix buffer
@@ -133,11 +147,13 @@ struct Ldl {
     // phases fill (columns >= RPW (p+1)), which is free until this MMA has completed.  The last phase's
     // panel would not fit there, so phase NW-1 folds phase NW-2 in with FFMA (left4).
 #ifndef B200ALS_MMA_PHASES
-#define B200ALS_MMA_PHASES (NW - 2)
+#define B200ALS_MMA_PHASES (NW - 1)
 #endif
     static constexpr int MMA_PHASES = B200ALS_MMA_PHASES;
     static constexpr uint32_t TILE_SBO = (RPW / 8) * 128u;
     static __host__ __device__ constexpr uint32_t tile_off(int p) {          // bytes from the matrix buffer
+        // the panel of phase NW-2 (one warp's rows) lives in the raw-row scratch, idle between the diagonal blocks
+        if (p == NW - 2) return RAW_OFF;
         // first stored element of column J = RPW (p+1) is (J, J) at ldl_col_base(J) + J
         return ((4u * (uint32_t)(ldl_col_base<K>(RPW * (p + 1)) + RPW * (p + 1))) + 127u) & ~127u;
     }
@@ -146,6 +162,7 @@ struct Ldl {
     }
     static_assert(tile_off(0) + 2 * tile_half(0) <= Z_OFF, "phase-0 panel must fit behind the phase-0 columns");
     static_assert(tile_off(1) + 2 * tile_half(1) <= Z_OFF, "phase-1 panel must fit behind the phase-1 columns");
+    static_assert(2 * tile_half(NW - 2) <= 2u * 4u * RAWSZ && RAW_OFF % 16 == 0, "phase-(NW-2) panel must fit in the raw-row scratch");
 
     // element (i, 4 g) of the column store at col_block(g) + 4 i; the block's columns are S4(g) bytes apart
     static __device__ __forceinline__ uint32_t col_block(const uint32_t cbs, const int g) {
@@ -177,25 +194,25 @@ struct Ldl {
         }
     }
 
-    // Four columns J = j0 .. j0+3 (j0 % 4 == 0) in ONE barrier ("block pivot") on the row window:
-    // a[c] holds the row's entry for column j0 + c (c < the columns left in this phase).
-    //   every row r >= j0 publishes its four raw entries rho_r = a[0..3] (and the four pivot rows
-    //   their rhs); barrier; every thread reads the 4 x 4 pivot block P (+ its rhs), factors it
-    //   redundantly in registers (P = L4 D4 L4^T), forward-substitutes its own four entries
-    //   (u_k = l_rk d_k go to the column store, t_k = l_rk), and applies the rank-4 update in terms
-    //   of the RAW published rows:  a[c] -= (t L4^-1) . rho_c  — the same four FFMAs per element as
-    //   four single-column steps, fed by the same broadcast LDS.128s, with a quarter of the barriers
-    //   and of the latency chain.  The update writes four registers down, so the window slides.
-    // nthr = threads of the warps that still own a row >= j0.  `last` (warp-uniform): j0 + 3 is this
-    // warp's last row — its pivot rows are all in this warp, nothing below them is ours to update;
-    // the warp then signs off on start_bar, which the warps below wait on before their next phase.
-    // tile_on (warp-uniform): the phase feeds a tensor-core update; tile_w: this thread's row lies below the
-    // phase's panel, tile_row = .shared address of its hi-panel row, tile_lo = bytes from there to the lo panel.
-    static __device__ __forceinline__ void body4(float (&a)[RPW], float& rhs, bool& ok, const float ridge,
-                                                 const int r, const uint32_t cbs, const int j0, const int bar_id,
-                                                 const int start_bar, const int nthr, const bool last,
-                                                 const uint32_t tile_row, const uint32_t tile_lo, const bool tile_on,
-                                                 const bool tile_w) {
+    // Phase p has two parts.  (1) The warp that owns the diagonal block (rows RPW p .. RPW (p+1) - 1) factors it
+    // ALONE, four columns per step (diag4), synchronising with __syncwarp only.  (2) One named barrier later
+    // every row below forward-substitutes its RPW window entries against the finished block (subst): no
+    // barrier, no redundant pivot work, a pure LDS.128 + FFMA stream.  (The first version ran all rows through
+    // the four-column steps in lock step: RPW/4 block-wide barriers per phase and a ~1.4 k-cycle chain each.)
+    //
+    // diag4: four columns J = j0 .. j0+3 (j0 % 4 == 0) on the row window, a[c] = entry for column j0 + c.
+    //   every row r >= j0 of the warp publishes its four raw entries rho_r = a[0..3] (the four pivot rows also
+    //   their rhs); __syncwarp; every thread reads the 4 x 4 pivot block P (+ its rhs), factors it redundantly
+    //   in registers (P = L4 D4 L4^T), forward-substitutes its own four entries (u_k = l_rk d_k go to the
+    //   column store, t_k = l_rk) and applies the rank-4 update in terms of the RAW published rows:
+    //   a[c] -= (t L4^-1) . rho_c.  The update writes four registers down, so the window slides and every
+    //   register index is static while the loop over the steps stays rolled.
+    // tile_on (warp-uniform): the phase feeds a tensor-core update, so 1/sqrt(d) of the pivots is kept (in the
+    // x array, unused until the back substitution) for the rows below.  final_step: the block's last four
+    // columns — nothing of this warp is left to update.
+    static __device__ __forceinline__ void diag4(float (&a)[RPW], float& rhs, bool& ok, const float ridge,
+                                                 const int r, const uint32_t cbs, const int j0, const bool tile_on,
+                                                 const bool final_step) {
         const int g = j0 >> 2;
         const uint32_t zb = cbs + Z_OFF;
         const uint32_t raw = cbs + RAW_OFF + (uint32_t)(g & 1) * (4u * RAWSZ);           // raw[parity][4][K] | zraw[4]
@@ -204,15 +221,14 @@ struct Ldl {
         const int dr = r - j0;                                                           // row position relative to the block
 #pragma unroll
         for (int s = 0; s < 4; ++s) a[s] += (dr == s) ? ridge : 0.0f;
+        // every store below is unconditional: a lane with nothing to store writes a dummy word instead (a predicated
+        // store compiles to a divergent branch region here, and this loop is one long dependent chain).  Finished
+        // lanes (dr < 0) may publish their stale window: nobody reads raw rows above the block.
+        const uint32_t dmy = raw + 4u * (uint32_t)(4 * K + 4);
 #pragma unroll
-        for (int s = 0; s < 4; ++s) sts_f32_if(raw + 4u * (uint32_t)(s * K + r), a[s], dr >= 0);
-        sts_f32_if(raw + 4u * (uint32_t)(4 * K + dr), rhs, (unsigned)dr < 4u);
-        if (last) {
-            if (nthr > 32) named_bar_arrive(bar_id, nthr);
-            __syncwarp();
-        } else {
-            named_bar_sync(bar_id, nthr);
-        }
+        for (int s = 0; s < 4; ++s) sts_f32(raw + 4u * (uint32_t)(s * K + r), a[s]);
+        sts_f32(raw + 4u * (uint32_t)(4 * K) + 4u * min((uint32_t)dr, 4u), rhs);
+        __syncwarp();
         const float4 p0 = lds_f32x4(raw + 4u * (uint32_t)(0 * K + j0));     // P[0..3][0]
         const float4 p1 = lds_f32x4(raw + 4u * (uint32_t)(1 * K + j0));     // P[0..3][1]
         const float4 p2 = lds_f32x4(raw + 4u * (uint32_t)(2 * K + j0));
@@ -228,18 +244,15 @@ struct Ldl {
         const float u32 = fmaf(-l31, u21, fmaf(-l30, p0.z, p2.w));
         const float l32 = u32 * i2;
         const float d3 = fmaf(-l32, u32, fmaf(-l31, u31, fmaf(-l30, p0.w, p3.w))), i3 = rcp_approx(d3);
-        // 1/sqrt(d_k) for the tensor-core panel (MUFU.RSQ next to the reciprocals, off the chain)
-        float rs0 = 0.0f, rs1 = 0.0f, rs2 = 0.0f, rs3 = 0.0f;
-        if (tile_on) { rs0 = rsqrtf(d0); rs1 = rsqrtf(d1); rs2 = rsqrtf(d2); rs3 = rsqrtf(d3); }
         // own row: unscaled entries u_k = l_rk d_k and multipliers t_k = l_rk
         const float u0 = a[0], t0 = u0 * i0;
         const float u1 = fmaf(-t0, p0.y, a[1]), t1 = u1 * i1;
         const float u2 = fmaf(-t1, u21, fmaf(-t0, p0.z, a[2])), t2 = u2 * i2;
         const float u3 = fmaf(-t2, u32, fmaf(-t1, u31, fmaf(-t0, p0.w, a[3]))), t3 = u3 * i3;
-        sts_f32_if(col0 + 4u * r, u0, dr >= 0);
-        sts_f32_if(col0 + S4 + 4u * r, u1, dr >= 1);
-        sts_f32_if(col0 + 2u * S4 + 4u * r, u2, dr >= 2);
-        sts_f32_if(col0 + 3u * S4 + 4u * r, u3, dr >= 3);
+        sts_f32(dr >= 0 ? col0 + 4u * r : dmy, u0);
+        sts_f32(dr >= 1 ? col0 + S4 + 4u * r : dmy, u1);
+        sts_f32(dr >= 2 ? col0 + 2u * S4 + 4u * r : dmy, u2);
+        sts_f32(dr >= 3 ? col0 + 3u * S4 + 4u * r : dmy, u3);
         // rhs of the block rows, forward-substituted; the pivot rows keep theirs in the z array
         const float z0 = zr.x;
         const float z1 = fmaf(-l10, z0, zr.y);
@@ -247,17 +260,17 @@ struct Ldl {
         const float z3 = fmaf(-l32, z2, fmaf(-l31, z1, fmaf(-l30, z0, zr.w)));
         {
             const bool piv = (unsigned)dr < 4u;
-            const float zsel = dr == 0 ? z0 : (dr == 1 ? z1 : (dr == 2 ? z2 : z3));
-            const float dsel = dr == 0 ? d0 : (dr == 1 ? d1 : (dr == 2 ? d2 : d3));
-            const float isel = dr == 0 ? i0 : (dr == 1 ? i1 : (dr == 2 ? i2 : i3));
-            sts_f32_if(zb + 4u * r, zsel, piv);
-            sts_f32_if(cbs + INV_OFF + 4u * r, isel, piv);
+            // flat select chains (FSEL): a nested ?: became a divergent branch region
+            const bool e1 = dr == 1, e2 = dr == 2, e3 = dr == 3;
+            float zsel = e1 ? z1 : z0, dsel = e1 ? d1 : d0, isel = e1 ? i1 : i0;
+            zsel = e2 ? z2 : zsel; dsel = e2 ? d2 : dsel; isel = e2 ? i2 : isel;
+            zsel = e3 ? z3 : zsel; dsel = e3 ? d3 : dsel; isel = e3 ? i3 : isel;
+            sts_f32(piv ? zb + 4u * r : dmy, zsel);
+            sts_f32(piv ? cbs + INV_OFF + 4u * r : dmy, isel);
+            if (tile_on) sts_f32(piv ? cbs + X_OFF + 4u * r : dmy, rsqrt_approx(dsel));   // 1/sqrt(d) for the panel of the rows below
             ok = piv ? (dsel > 0.0f) : ok;
         }
-        if (last) {
-            if (nthr > 32) named_bar_arrive(start_bar, nthr);
-            return;
-        }
+        if (final_step) return;
         rhs = fmaf(-t3, z3, fmaf(-t2, z2, fmaf(-t1, z1, fmaf(-t0, z0, rhs))));
         // tau = t L4^-1, so that l_r D4 l_c^T = tau . rho_c
         const float w3 = t3;
@@ -276,22 +289,73 @@ struct Ldl {
             a[c4 - 2] = fmaf(-w3, v3.z, fmaf(-w2, v2.z, fmaf(-w1, v1.z, fmaf(-w0, v0.z, a[c4 + 2]))));
             a[c4 - 1] = fmaf(-w3, v3.w, fmaf(-w2, v2.w, fmaf(-w1, v1.w, fmaf(-w0, v0.w, a[c4 + 3]))));
         }
-        // after the rank-4 update: the conversions and the two stores stay off the pivot chain
-        if (tile_on) {                                   // warp-uniform: this phase feeds the tensor-core update
-            // w_k = u_k / sqrt(d_k) as bf16 hi + lo, four panel columns = 8 bytes of the row's core-matrix line
+    }
+
+    // Rows below the diagonal block J0 .. J0 + RPW - 1 (finished, in the column store): forward substitution of the
+    // row's window a[c] = A[r][J0 + c] (already updated for every earlier phase),
+    //   u_j = a_j - sum_{i < j} t_i U[J0+j][J0+i],   t_j = u_j / d_j,   rhs -= sum_j t_j z_j,
+    // four columns at a time: the earlier column groups fold in with four broadcast LDS.128 + 16 FFMA each, the
+    // group's own 4 x 4 triangle sits in three more.  Every index is static (fully unrolled: RPW/4 (RPW/4 - 1)/2
+    // group pairs), the multipliers t_j replace a[j] in place.  u_j go to the column store; tile_on: w_j = u_j / sqrt(d_j)
+    // as bf16 hi + lo into this row's line of the tensor-core panel (tile_row: .shared address of the hi-panel row,
+    // tile_lo: bytes from there to the lo panel).
+    static __device__ __forceinline__ void subst(float (&a)[RPW], float& rhs, const int r, const uint32_t cbs,
+                                                 const int J0, const uint32_t tile_row, const uint32_t tile_lo,
+                                                 const bool tile_on) {
+        const int g0 = J0 >> 2;
+#pragma unroll
+        for (int gb = 0; gb < RPW / 4; ++gb) {
+            const int g = g0 + gb;
+            const uint32_t S4 = 4u * (uint32_t)(K - 4 * g);
+            const uint32_t colb = col_block(cbs, g);                 // element (i, 4 g + s) at colb + s S4 + 4 i
+            const uint32_t rowoff = 16u * (uint32_t)g;               // rows 4 g .. 4 g + 3
+#pragma unroll
+            for (int ib = 0; ib < gb; ++ib) {
+                const int gi = g0 + ib;
+                const uint32_t S4i = 4u * (uint32_t)(K - 4 * gi);
+                const uint32_t ci = col_block(cbs, gi) + rowoff;     // U[4g .. 4g+3][4 gi + s] at ci + s S4i
+                const float4 v0 = lds_f32x4(ci);
+                const float4 v1 = lds_f32x4(ci + S4i);
+                const float4 v2 = lds_f32x4(ci + 2u * S4i);
+                const float4 v3 = lds_f32x4(ci + 3u * S4i);
+                const float t0 = a[4 * ib], t1 = a[4 * ib + 1], t2 = a[4 * ib + 2], t3 = a[4 * ib + 3];
+                a[4 * gb + 0] = fmaf(-t3, v3.x, fmaf(-t2, v2.x, fmaf(-t1, v1.x, fmaf(-t0, v0.x, a[4 * gb + 0]))));
+                a[4 * gb + 1] = fmaf(-t3, v3.y, fmaf(-t2, v2.y, fmaf(-t1, v1.y, fmaf(-t0, v0.y, a[4 * gb + 1]))));
+                a[4 * gb + 2] = fmaf(-t3, v3.z, fmaf(-t2, v2.z, fmaf(-t1, v1.z, fmaf(-t0, v0.z, a[4 * gb + 2]))));
+                a[4 * gb + 3] = fmaf(-t3, v3.w, fmaf(-t2, v2.w, fmaf(-t1, v1.w, fmaf(-t0, v0.w, a[4 * gb + 3]))));
+            }
+            const float4 c0 = lds_f32x4(colb + rowoff);              // d, U10, U20, U30 of the group's triangle
+            const float4 c1 = lds_f32x4(colb + S4 + rowoff);         // -, -,   U21, U31
+            const float4 c2 = lds_f32x4(colb + 2u * S4 + rowoff);    // -, -,   -,   U32
+            const float4 inv = lds_f32x4(cbs + INV_OFF + rowoff);
+            const float4 zz = lds_f32x4(cbs + Z_OFF + rowoff);
+            const float u0 = a[4 * gb], t0 = u0 * inv.x;
+            const float u1 = fmaf(-t0, c0.y, a[4 * gb + 1]), t1 = u1 * inv.y;
+            const float u2 = fmaf(-t1, c1.z, fmaf(-t0, c0.z, a[4 * gb + 2])), t2 = u2 * inv.z;
+            const float u3 = fmaf(-t2, c2.w, fmaf(-t1, c1.w, fmaf(-t0, c0.w, a[4 * gb + 3]))), t3 = u3 * inv.w;
+            rhs = fmaf(-t3, zz.w, fmaf(-t2, zz.z, fmaf(-t1, zz.y, fmaf(-t0, zz.x, rhs))));
+            sts_f32_nc(colb + 4u * r, u0);
+            sts_f32_nc(colb + S4 + 4u * r, u1);
+            sts_f32_nc(colb + 2u * S4 + 4u * r, u2);
+            sts_f32_nc(colb + 3u * S4 + 4u * r, u3);
+            a[4 * gb] = t0; a[4 * gb + 1] = t1; a[4 * gb + 2] = t2; a[4 * gb + 3] = t3;
+            if (tile_on) {                                   // warp-uniform: this phase feeds the tensor-core update
+                // w_k = u_k / sqrt(d_k) as bf16 hi + lo, four panel columns = 8 bytes of the row's core-matrix line
+                const float4 rs = lds_f32x4(cbs + X_OFF + rowoff);
 #ifdef B200ALS_MMA_NULL
-            const float w0 = 0.0f, w1 = 0.0f, w2 = 0.0f, w3 = 0.0f;
+                const float w0 = 0.0f, w1 = 0.0f, w2 = 0.0f, w3 = 0.0f;
 #else
-            const float w0 = u0 * rs0, w1 = u1 * rs1, w2 = u2 * rs2, w3 = u3 * rs3;
+                const float w0 = u0 * rs.x, w1 = u1 * rs.y, w2 = u2 * rs.z, w3 = u3 * rs.w;
 #endif
-            const __nv_bfloat162 h01 = __floats2bfloat162_rn(w0, w1), h23 = __floats2bfloat162_rn(w2, w3);
-            const float2 f01 = __bfloat1622float2(h01), f23 = __bfloat1622float2(h23);
-            const __nv_bfloat162 l01 = __floats2bfloat162_rn(w0 - f01.x, w1 - f01.y);
-            const __nv_bfloat162 l23 = __floats2bfloat162_rn(w2 - f23.x, w3 - f23.y);
-            const int jj = j0 % RPW;
-            const uint32_t ta = tile_row + (uint32_t)((jj >> 3) * 128 + (jj & 7) * 2);
-            sts_b64_if(ta, bf162_bits(h01), bf162_bits(h23), tile_w);
-            sts_b64_if(ta + tile_lo, bf162_bits(l01), bf162_bits(l23), tile_w);
+                const __nv_bfloat162 h01 = __floats2bfloat162_rn(w0, w1), h23 = __floats2bfloat162_rn(w2, w3);
+                const float2 f01 = __bfloat1622float2(h01), f23 = __bfloat1622float2(h23);
+                const __nv_bfloat162 l01 = __floats2bfloat162_rn(w0 - f01.x, w1 - f01.y);
+                const __nv_bfloat162 l23 = __floats2bfloat162_rn(w2 - f23.x, w3 - f23.y);
+                const int jj = 4 * gb;                       // column inside the panel
+                const uint32_t ta = tile_row + (uint32_t)((jj >> 3) * 128 + (jj & 7) * 2);
+                sts_b64_nc(ta, bf162_bits(h01), bf162_bits(h23));
+                sts_b64_nc(ta + tile_lo, bf162_bits(l01), bf162_bits(l23));
+            }
         }
     }
 
@@ -299,12 +363,13 @@ struct Ldl {
     // TMEM (and releases the accumulator after this thread's last load); rhs = this row's
     // right-hand-side entry, ridge is added on the pivot.  r / q = row and warp in ELIMINATION order,
     // r_phys = the row's TMEM lane row (K-1-r for the reversed groups), d_tmem = the matrix's accumulator,
-    // upd_bar = an mbarrier (count 1) of this matrix for the tensor-core updates.
+    // upd_bar = an mbarrier (count 1) of this matrix for the tensor-core updates, upd_base = updates it has completed so far
+    // (MMA_PHASES per factorisation; the wait parity follows the running count).
     // Returns true if thread r's pivot was positive.
     template <class LoadWindow>
     static __device__ __forceinline__ bool factor(float rhs, const float ridge, const int r, const int q,
                                                   const int r_phys, const uint32_t cbs, const int bar_id,
-                                                  const int start_bar, const uint32_t d_tmem, uint64_t* upd_bar,
+                                                  const int start_bar, const uint32_t d_tmem, uint64_t* upd_bar, const uint32_t upd_base,
                                                   LoadWindow&& load_window) {
         bool ok = true;
         float a[RPW];
@@ -360,7 +425,7 @@ struct Ldl {
                         }
                         ptx::umma_commit(upd_bar);
                     }
-                    ptx::mbar_wait(upd_bar, (uint32_t)((p - 1) & 1));
+                    ptx::mbar_wait(upd_bar, (upd_base + (uint32_t)(p - 1)) & 1u);
                     ptx::tc_fence_after();
                 }
             }
@@ -388,14 +453,25 @@ struct Ldl {
             }
             // this thread's panel row for the update after this phase
             const bool tile_on = p < MMA_PHASES;
-            const int trow = rev ? r_phys : r - RPW * (p + 1);
-            const uint32_t tile_row = cbs + tile_off(p < MMA_PHASES ? p : 0) + (uint32_t)((trow >> 3) * (int)TILE_SBO + (trow & 7) * 16);
-            const uint32_t tile_lo = tile_half(p < MMA_PHASES ? p : 0);
+            if (p == q) {
+                // the diagonal block: this warp alone, four columns per step
 #pragma unroll 1
-            for (int it = 0; it < RPW / 4; ++it)
-                body4(a, rhs, ok, ridge, r, cbs, p * RPW + 4 * it, bar_id, start_bar, nthr,
-                      p == q && it == RPW / 4 - 1, tile_row, tile_lo, tile_on, tile_on && r >= RPW * (p + 1));
-            LDL_TICK(11);
+                for (int it = 0; it < RPW / 4; ++it)
+                    diag4(a, rhs, ok, ridge, r, cbs, p * RPW + 4 * it, tile_on, it == RPW / 4 - 1);
+                if (nthr > 32) {
+                    named_bar_arrive(bar_id, nthr);        // block, z, 1/d, 1/sqrt(d) published: the rows below substitute
+                    named_bar_arrive(start_bar, nthr);     // and this warp signs off on the phase
+                }
+                LDL_TICK(11);
+            } else {
+                const int trow = rev ? r_phys : r - RPW * (p + 1);
+                const uint32_t tile_row = cbs + tile_off(tile_on ? p : 0) + (uint32_t)((trow >> 3) * (int)TILE_SBO + (trow & 7) * 16);
+                const uint32_t tile_lo = tile_half(tile_on ? p : 0);
+                named_bar_sync(bar_id, nthr);
+                LDL_TICK(12);
+                subst(a, rhs, r, cbs, p * RPW, tile_row, tile_lo, tile_on);
+                LDL_TICK(13);
+            }
         }
         return ok;
     }

@@ -555,9 +555,10 @@ __device__ __forceinline__ void umma_role_solver(const RowStepParams& p, const U
     long long tacc[8] = {0, 0, 0, 0, 0, 0, 0, 0};
     long long tlast = clock64();
     if (blockIdx.x == 0 && threadIdx.x == 96)
-        for (int i = 8; i < 12; ++i) g_timing[i] = 0;
+        for (int i = 8; i < 16; ++i) g_timing[i] = 0;
 #endif
 
+    uint32_t nfac = 0;                                 // factorisations so far (parity of the tensor-core update barrier)
     int32_t* lastf = s.bad + 16 + g * C::RPB + h;      // split rows: "this group added the last piece"
     constexpr int SLOT_LD = K + 4;                     // slot row: k matrix entries | c, s, -, -
 
@@ -699,7 +700,8 @@ __device__ __forceinline__ void umma_role_solver(const RowStepParams& p, const U
         };
         const bool ok = L::factor(c_r - bias_old * s_r, ridge, re, qe, r, cbs, col_bar, start_bar,
                                   tmem + buf * C::ACC_STRIDE + ((uint32_t)(16 * h) << 16), &s.upd[g * C::RPB + h],
-                                  load_window);
+                                  (uint32_t)L::MMA_PHASES * nfac, load_window);
+        ++nfac;
         if (!ok && valid) *bad = 1;
         TICK(3);
         const float x = L::backsolve(re, qe, sege, rev ? C::RPW - 1 : 0, cbs, phase_bar);   // barriers inside publish *bad too

@@ -247,6 +247,59 @@ __global__ void __launch_bounds__(256) predict_pairs_kernel(const float* __restr
     }
 }
 
+// N1 — squared error over flat indices u*n+i without the dense prediction (tune_params.py:147-167), split by an
+// item bin when given (evaluate_models.py:173-191, 263-274).  8 lanes per entry (16-byte factor loads), float64
+// per-bin sums per warp in shared memory, one atomic per bin and block.
+constexpr int SSE_MAX_BINS = 32;
+__global__ void __launch_bounds__(256) sse_on_flat_kernel(const float* __restrict__ U, int64_t ldu,
+                                                          const float* __restrict__ Z, int64_t ldz,
+                                                          const float* __restrict__ b_u, const float* __restrict__ b_i,
+                                                          const float* __restrict__ mu_p,
+                                                          const int64_t* __restrict__ flat, const float* __restrict__ y,
+                                                          int64_t count, int64_t n, int k,
+                                                          const int32_t* __restrict__ item_bin, int n_bins,
+                                                          double* __restrict__ sse, long long* __restrict__ cnt) {
+    __shared__ double sh_sse[SSE_MAX_BINS];
+    __shared__ unsigned long long sh_cnt[SSE_MAX_BINS];
+    if (threadIdx.x < SSE_MAX_BINS) { sh_sse[threadIdx.x] = 0.0; sh_cnt[threadIdx.x] = 0ull; }
+    __syncthreads();
+    const int g8 = threadIdx.x & 7;
+    const int64_t grp = ((int64_t)blockIdx.x * blockDim.x + threadIdx.x) >> 3;
+    const int64_t ngrp = ((int64_t)gridDim.x * blockDim.x) >> 3;
+    const int kq = (k + 3) >> 2;
+    const float mu = *mu_p;
+    const int64_t iters = (count + ngrp - 1) / ngrp;   // same trip count for every lane of a warp
+    for (int64_t it = 0; it < iters; ++it) {
+        const int64_t e = grp + it * ngrp;
+        const bool live = e < count;
+        const int64_t f = live ? flat[e] : 0;
+        const int64_t u = f / n, i = f - u * n;        // als.py's row-major flat convention (create_folds.py:73-84)
+        float dot = 0.0f;
+        for (int q = g8; q < kq; q += 8) {
+            const float4 a = *reinterpret_cast<const float4*>(U + (size_t)u * ldu + q * 4);
+            const float4 z = *reinterpret_cast<const float4*>(Z + (size_t)i * ldz + q * 4);
+            dot = fmaf(a.x, z.x, dot); dot = fmaf(a.y, z.y, dot);
+            dot = fmaf(a.z, z.z, dot); dot = fmaf(a.w, z.w, dot);
+        }
+        dot += __shfl_xor_sync(0xffffffffu, dot, 4);
+        dot += __shfl_xor_sync(0xffffffffu, dot, 2);
+        dot += __shfl_xor_sync(0xffffffffu, dot, 1);
+        if (live && g8 == 0) {
+            const double d = (double)y[e] - (double)(dot + mu + b_u[u] + b_i[i]);
+            const int b = item_bin ? item_bin[i] : 0;
+            if (b >= 0 && b < n_bins) {
+                atomicAdd(&sh_sse[b], d * d);
+                atomicAdd(&sh_cnt[b], 1ull);
+            }
+        }
+    }
+    __syncthreads();
+    if (threadIdx.x < n_bins && sh_cnt[threadIdx.x]) {
+        atomicAdd(&sse[threadIdx.x], sh_sse[threadIdx.x]);
+        atomicAdd(reinterpret_cast<unsigned long long*>(cnt) + threadIdx.x, sh_cnt[threadIdx.x]);
+    }
+}
+
 static int grid_for(int64_t work, int threads, int per_sm = 8) {
     int64_t b = ceil_div64(work, threads);
     int64_t cap = (int64_t)kNumSMs * per_sm;
@@ -352,6 +405,21 @@ int b200als_predict_pairs(const float* U, int64_t ldu, const float* Z, int64_t l
     if (count <= 0) return B200ALS_OK;
     predict_pairs_kernel<<<grid_for(count * 8, 256, 8), 256, 0, as_stream(stream)>>>(U, ldu, Z, ldz, b_u, b_i, mu,
                                                                                     rows, cols, count, k, out);
+    ALS_LAUNCH_CHECK();
+    return B200ALS_OK;
+}
+
+int b200als_sse_on_flat(const float* U, int64_t ldu, const float* Z, int64_t ldz, const float* b_u,
+                        const float* b_i, const float* mu, const int64_t* flat_idx, const float* y_true,
+                        int64_t count, int64_t n, int32_t k, const int32_t* item_bin, int32_t n_bins,
+                        double* sse, int64_t* cnt, b200als_stream_t stream) {
+    ALS_CHECK_ARG(U && Z && b_u && b_i && mu && flat_idx && y_true && sse && cnt, "null pointer");
+    ALS_CHECK_ARG(k >= 1 && k <= B200ALS_MAX_K && (ldu & 3) == 0 && (ldz & 3) == 0, "bad k / ld");
+    ALS_CHECK_ARG(n > 0 && n_bins >= 1 && n_bins <= SSE_MAX_BINS, "n_bins outside [1, 32]");
+    if (count <= 0) return B200ALS_OK;
+    sse_on_flat_kernel<<<grid_for(count * 8, 256, 8), 256, 0, as_stream(stream)>>>(
+        U, ldu, Z, ldz, b_u, b_i, mu, flat_idx, y_true, count, n, k, item_bin, n_bins, sse,
+        reinterpret_cast<long long*>(cnt));
     ALS_LAUNCH_CHECK();
     return B200ALS_OK;
 }

@@ -272,6 +272,20 @@ int b200als_predict_pairs(const float* U, int64_t ldu, const float* Z, int64_t l
                           const int32_t* rows, const int32_t* cols, int64_t count, int32_t k,
                           float* out, b200als_stream_t stream);
 
+/* ------------------------------------------------------------------------
+ * N1 — `_rmse_on_indices` (tune_params.py:147-167) and the popularity-bin
+ * split of it (evaluate_models.py:173-191, 263-274) without the dense (m, n)
+ * prediction: for every flat index f = u*n + i (create_folds.py:73-84),
+ *   d = y_true - (U[u]·Z[i] + mu + b_u[u] + b_i[i]),
+ *   sse[b] += d^2, cnt[b] += 1,  b = item_bin[i]  (b = 0 when item_bin is NULL).
+ * sse / cnt (n_bins entries, n_bins <= 32) are accumulated into: zero them first.
+ * ---------------------------------------------------------------------- */
+int b200als_sse_on_flat(const float* U, int64_t ldu, const float* Z, int64_t ldz,
+                        const float* b_u, const float* b_i, const float* mu,
+                        const int64_t* flat_idx, const float* y_true, int64_t count,
+                        int64_t n, int32_t k, const int32_t* item_bin, int32_t n_bins,
+                        double* sse, int64_t* cnt, b200als_stream_t stream);
+
 #ifdef __cplusplus
 }
 #endif
