@@ -10,7 +10,7 @@ import os
 
 _HERE = os.path.dirname(os.path.abspath(__file__))
 LIB_PATH = os.path.join(_HERE, "libb200als.so")
-ABI_VERSION = 6
+ABI_VERSION = 7
 MAX_K = 160
 MAX_FEATURES = 8
 STATUS_WORDS = 4
@@ -49,7 +49,7 @@ class StepArgs(C.Structure):
         ("X", vp), ("ldx", C.c_int64),
         ("bias_own", vp),
         ("chol_out", vp), ("aux_out", vp),
-        ("status", vp), ("stats_acc", vp),
+        ("status", vp), ("stats_acc", vp), ("norm_acc", vp),
         ("split", vp),
         ("workspace", vp), ("workspace_bytes", C.c_size_t),
     ]
@@ -92,6 +92,10 @@ _SIGNATURES = {
                               C.c_int64, C.c_int64, C.c_int32, vp, vp],
     "b200als_predict_pairs": [vp, C.c_int64, vp, C.c_int64, vp, vp, vp, vp, vp,
                               C.c_int64, C.c_int32, vp, vp],
+    "b200als_fold_split_workspace_bytes": [C.c_int64, C.POINTER(C.c_size_t)],
+    "b200als_fold_split": [vp, vp, C.c_int64, vp, C.c_int64, vp, vp, vp, vp, vp, vp, C.c_size_t, vp],
+    "b200als_sse_on_flat": [vp, C.c_int64, vp, C.c_int64, vp, vp, vp, vp, vp, C.c_int64, C.c_int64, C.c_int32,
+                            vp, C.c_int32, vp, vp, vp],
 }
 _RESTYPES = {"b200als_last_error": C.c_char_p}
 

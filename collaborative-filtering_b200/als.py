@@ -270,14 +270,53 @@ class ALS:
                                             torch.cuda.current_stream().cuda_stream), "predict_pairs")
             return out[:r.numel()].double().cpu().numpy()
 
+    def sse_on_flat(self, flat_idx, y_true, features=None, item_bin=None, n_bins: int = 1):
+        """Squared-error sums and counts over flat indices u*n+i, split by `item_bin[i]` when given, computed on
+        the device without the dense (m, n) prediction (b200als_sse_on_flat).  `flat_idx` / `y_true` may be numpy
+        arrays or tensors already on the device.  Returns (sse float64[n_bins], cnt int64[n_bins]) as numpy."""
+        if self.U is None or self.V is None:
+            raise RuntimeError("Model must be fitted before prediction.")
+        features = features or {}
+        self._check_features(features, self.V.shape[0], "predict")
+        if not (1 <= int(n_bins) <= 32):
+            raise ValueError("n_bins must be in [1, 32]")
+        lib = _lib.load()
+        _lib.require_device()
+        dev = self._dev()
+        with torch.cuda.device(dev):
+            s = self._upload_model(features, dev)
+            f = torch.as_tensor(flat_idx).to(device=dev, dtype=torch.int64).contiguous()
+            y = torch.as_tensor(y_true).to(device=dev, dtype=torch.float32).contiguous()
+            if f.numel() != y.numel():
+                raise ValueError("flat_idx and y_true differ in length")
+            if f.numel() and (int(f.min()) < 0 or int(f.max()) >= s["m"] * s["n"]):
+                raise IndexError("flat index outside the (m, n) matrix")
+            b = None
+            if item_bin is not None:
+                b = torch.as_tensor(np.asarray(item_bin)).to(device=dev, dtype=torch.int32).contiguous()
+                if b.numel() != s["n"]:
+                    raise ValueError("item_bin must have one entry per item")
+            sse = torch.zeros(n_bins, dtype=torch.float64, device=dev)
+            cnt = torch.zeros(n_bins, dtype=torch.int64, device=dev)
+            check(lib.b200als_sse_on_flat(ptr(s["U"]), s["ld"], ptr(s["Z"]), s["ld"], ptr(s["b_u"]), ptr(s["b_i"]),
+                                          ptr(s["mu"]), ptr(f), ptr(y), f.numel(), s["n"], s["k"], ptr(b),
+                                          int(n_bins), ptr(sse), ptr(cnt), torch.cuda.current_stream().cuda_stream),
+                  "sse_on_flat")
+            return sse.cpu().numpy(), cnt.cpu().numpy()
+
     def rmse_on_flat(self, flat_idx, y_true, features=None) -> float:
-        """RMSE over flat indices u*n+i (`_rmse_on_indices`, tune_params.py:147-167)."""
-        flat_idx = np.asarray(flat_idx, dtype=np.int64)
-        if flat_idx.size == 0:
-            return float("nan")
-        n = self.V.shape[0]
-        pred = self.predict_pairs(flat_idx // n, flat_idx % n, features)
-        return float(np.sqrt(np.mean((np.asarray(y_true, dtype=np.float64) - pred) ** 2)))
+        """RMSE over flat indices u*n+i (`_rmse_on_indices`, tune_params.py:147-167); NaN for an empty set."""
+        sse, cnt = self.sse_on_flat(flat_idx, y_true, features)
+        return float(np.sqrt(sse[0] / cnt[0])) if cnt[0] else float("nan")
+
+    def rmse_by_item_bin(self, flat_idx, y_true, item_bin, n_bins: int, features=None):
+        """(overall RMSE, [RMSE of bin 0, ..., bin n_bins-1]) in one pass — the overall and `rmse_pop_b` fold
+        metrics of evaluate_models.py:263-274 (`_split_val_indices_by_popularity` + `_rmse_on_indices`)."""
+        sse, cnt = self.sse_on_flat(flat_idx, y_true, features, item_bin, n_bins)
+        with np.errstate(invalid="ignore", divide="ignore"):
+            per_bin = [float(np.sqrt(sse[b] / cnt[b])) if cnt[b] else float("nan") for b in range(n_bins)]
+        tot = int(cnt.sum())
+        return (float(np.sqrt(sse.sum() / tot)) if tot else float("nan")), per_bin
 
 
 class FitSession:
@@ -421,7 +460,19 @@ class FitSession:
             self.wptr = (C.c_void_p * len(names))(*[w.data_ptr() for w in W_d])
             self.dims = (C.c_int32 * len(names))(*[int(x.shape[1]) for x in self.X_d])
         self.launches = 0
-        self.fused_stats = False
+        # A10 fused into the steps (residual sums by the item step, norms by both): possible when Z == V and no
+        # Gauss-Seidel sweep follows, i.e. the item step sees every residual of the iteration's final state.
+        # Rows without ratings are never solved: their constant share of the norms is added up front (by rank 0).
+        self.fused_stats = (not names) and (not use_graph)
+        if self.fused_stats:
+            base = torch.zeros(6, dtype=f64, device=dev)
+            if shard.rank == 0 or not shard.active:
+                ue, ie = u_order[u_nonempty:].long(), i_order[i_nonempty:].long()
+                base[2] = U_d.index_select(0, ue).double().pow(2).sum()
+                base[3] = V_d.index_select(0, ie).double().pow(2).sum()
+                base[4] = self.b_u_d.index_select(0, ue).double().pow(2).sum()
+                base[5] = self.b_i_d.index_select(0, ie).double().pow(2).sum()
+            self.acc_base = base
 
     # ---- small wrappers ---------------------------------------------------------
     def _stream(self):
@@ -455,7 +506,7 @@ class FitSession:
         return plan
 
     def _step(self, indptr, indices, vals, n_rows, rows, F, n_f_rows, bias_other, reg, reg_row, lamb, X, bias_own,
-              mode, stats=None, split=None):
+              mode, stats=None, split=None, norms=None):
         a = StepArgs()
         a.struct_bytes = C.sizeof(StepArgs)
         a.k, a.mode, a.path = self.k, mode, self.model.gram_path
@@ -472,6 +523,7 @@ class FitSession:
         a.aux_out = ptr(self.aux_d) if mode == _lib.STEP_FACTOR else None
         a.status = ptr(self.status)
         a.stats_acc = ptr(stats)
+        a.norm_acc = norms
         a.split = C.addressof(split) if split is not None else None
         a.workspace, a.workspace_bytes = ptr(self.ws), self.ws.numel()
         check(self.lib.b200als_row_step(C.byref(a), self._stream()), "row_step")
@@ -499,13 +551,18 @@ class FitSession:
         names = self.names
         stream = self._stream()
         self.launches = 0
+        fused = self.fused_stats
         self._mark("compose")
         if names:
             self._compose(self.Z_d)                                     # als.py:411
+        if fused:
+            self.acc.copy_(self.acc_base)
+            self.launches += 1
         # (1) users (als.py:414-433)
         self._mark("user")
         self._step(rt.indptr, rt.indices, rt.vals, m, self.u_list, self.Z_d, n, self.b_i_d, self.reg_user, None,
-                   self.lam_bu, self.U_d, self.b_u_d, _lib.STEP_SOLVE, split=self.u_split)
+                   self.lam_bu, self.U_d, self.b_u_d, _lib.STEP_SOLVE, split=self.u_split,
+                   norms=(self.acc.data_ptr() + 16) if fused else None)
         if shard.active:
             shard.exchange_rows(self.U_d, self.u_plan)
             shard.exchange_rows(self.b_u_d, self.u_plan)
@@ -525,12 +582,10 @@ class FitSession:
         else:
             # A10 fused: with Z == V and no sweep after it, the item step sees every residual of
             # the iteration's final state, so it accumulates sum d / sum d^2 itself
-            fused = self.fused_stats = not names
-            if fused:
-                self.acc.zero_()
             self._step(rt.cindptr, rt.cindices, rt.cvals, n, self.i_list, self.U_d, m, self.b_u_d, 0.0,
                        self.reg_item_d, self.lam_bi, self.V_d, self.b_i_d, _lib.STEP_SOLVE,
-                       stats=self.acc if fused else None, split=self.i_split)
+                       stats=self.acc if fused else None, split=self.i_split,
+                       norms=(self.acc.data_ptr() + 24) if fused else None)
             if shard.active:
                 shard.exchange_rows(self.V_d, self.i_plan)
                 shard.exchange_rows(self.b_i_d, self.i_plan)
@@ -559,7 +614,6 @@ class FitSession:
         if names:
             self._compose(self.Z_d)
         acc = self.acc
-        fused = (not self.use_graph) and self.fused_stats
         ulo, uhi = self.ulo, self.uhi
         if not fused:
             acc.zero_()
@@ -569,15 +623,17 @@ class FitSession:
                   "residual_stats")
             self.launches += 1
         if shard.active:
-            shard.all_reduce_sum(acc[:2])
-        check(lib.b200als_sumsq(ptr(self.U_d), m, k, ld, acc.data_ptr() + 16, stream), "sumsq")
-        check(lib.b200als_sumsq(ptr(self.V_d), n, k, ld, acc.data_ptr() + 24, stream), "sumsq")
-        check(lib.b200als_sumsq(ptr(self.b_u_d), 1, m, m, acc.data_ptr() + 32, stream), "sumsq")
-        check(lib.b200als_sumsq(ptr(self.b_i_d), 1, n, n, acc.data_ptr() + 40, stream), "sumsq")
+            shard.all_reduce_sum(acc if fused else acc[:2])
+        if not fused:
+            check(lib.b200als_sumsq(ptr(self.U_d), m, k, ld, acc.data_ptr() + 16, stream), "sumsq")
+            check(lib.b200als_sumsq(ptr(self.V_d), n, k, ld, acc.data_ptr() + 24, stream), "sumsq")
+            check(lib.b200als_sumsq(ptr(self.b_u_d), 1, m, m, acc.data_ptr() + 32, stream), "sumsq")
+            check(lib.b200als_sumsq(ptr(self.b_i_d), 1, n, n, acc.data_ptr() + 40, stream), "sumsq")
+            self.launches += 4
         slot = it % self.hist.shape[0]
         fin = lib.b200als_finalize_iter_fused if fused else lib.b200als_finalize_iter
         check(fin(ptr(acc), rt.nnz, ptr(self.mu_d), self.hist.data_ptr() + 48 * slot, stream), "finalize_iter")
-        self.launches += 5
+        self.launches += 1
         self._mark("end")
 
     # ---- host sync points -----------------------------------------------------------------

@@ -300,6 +300,7 @@ struct RowEpilogueArgs {
     int32_t* status;
     float qq;                     // sum q^2 of the row (fused residual statistics)
     double* stats_d; double* stats_d2;   // thread-0 accumulators, may be null
+    double* stats_xx; double* stats_bb;  // thread-0 accumulators of |x|^2 and bias^2
 };
 
 // Preconditions: the lower-triangle tiles of F^T F are in S.Gt (tile rows 0..kt-1), c_s = F^T q
@@ -363,6 +364,8 @@ __device__ __forceinline__ void row_epilogue_tiles(const SolveSmem& S, const flo
             const float fc = (float)cnt;
             const float beta = (t_sum - part) / (fc + a.lam_bias);
             a.bias_own[r] = beta;
+            *a.stats_xx += (double)xx;
+            *a.stats_bb += (double)beta * (double)beta;
             if (a.stats_d) {
                 // d_e = q_e - beta - f_e.x over the row, from the quantities already at hand:
                 //   sum d^2 = qq - 2 beta t + cnt beta^2 - 2 (c.x - beta s.x) + x^T G x,

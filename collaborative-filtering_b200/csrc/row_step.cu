@@ -179,6 +179,7 @@ int b200als_row_step(const b200als_step_args* a, b200als_stream_t stream) {
     p.X = a->X; p.ldx = a->ldx; p.bias_own = a->bias_own;
     p.chol_out = a->chol_out; p.aux_out = a->aux_out; p.status = a->status;
     p.stats = (a->mode == B200ALS_STEP_SOLVE) ? a->stats_acc : nullptr;
+    p.norms = (a->mode == B200ALS_STEP_SOLVE) ? a->norm_acc : nullptr;
     p.cursor = reinterpret_cast<unsigned long long*>(a->workspace);
     p.items = nullptr; p.split_hdr = nullptr; p.slot_np = nullptr; p.slot_ctr = nullptr; p.slot_acc = nullptr;
     ALS_CUDA(cudaMemsetAsync(a->workspace, 0, 256, s));

@@ -35,6 +35,7 @@ struct RowStepParams {
     float* chol_out; float* aux_out;
     int32_t* status;
     double* stats;                // optional: [0] += sum d, [1] += sum d^2 over the rows solved (A10 fused)
+    double* norms;                // optional: [0] += sum |x|^2, [2] += sum bias^2 over the rows solved (als.py:513-516 fused)
     unsigned long long* cursor;   // zeroed before launch
     // tcgen05 path only: work items of the schedule with long rows cut into pieces (split_plan.cuh)
     const int4* items;            // {row, first rating (offset in the row), ratings, slot or -1}; null: rows[] as is
@@ -91,6 +92,7 @@ __global__ void __launch_bounds__(FfmaCfg<KP, T>::THREADS) row_step_ffma_kernel(
         tj = tid - ti * (ti + 1) / 2;
     }
     double stat_d = 0.0, stat_d2 = 0.0;    // fused residual statistics (thread 0)
+    double stat_xx = 0.0, stat_bb = 0.0;   // fused norms (thread 0)
     // zero the tile ring once: columns [k4, KP) are never written by cp.async
     for (int e = tid; e < FF_STAGES * FF_TR * LDT; e += NTHR) tiles[e] = 0.0f;
 
@@ -254,6 +256,7 @@ __global__ void __launch_bounds__(FfmaCfg<KP, T>::THREADS) row_step_ffma_kernel(
         ea.X = p.X; ea.ldx = p.ldx; ea.bias_own = p.bias_own;
         ea.chol_out = p.chol_out; ea.aux_out = p.aux_out; ea.status = p.status;
         ea.stats_d = &stat_d; ea.stats_d2 = &stat_d2;
+        ea.stats_xx = &stat_xx; ea.stats_bb = &stat_bb;
         const float t_sum = red_s[31];
         ea.qq = red_s[30];
         row_epilogue_tiles(S, c_s, s_s, t_sum, cnt, r, ea, tid, NTHR, 1);
@@ -261,6 +264,10 @@ __global__ void __launch_bounds__(FfmaCfg<KP, T>::THREADS) row_step_ffma_kernel(
     if (p.stats && tid == 0) {
         atomicAdd(&p.stats[0], stat_d);
         atomicAdd(&p.stats[1], stat_d2);
+    }
+    if (p.norms && tid == 0) {
+        atomicAdd(&p.norms[0], stat_xx);
+        atomicAdd(&p.norms[2], stat_bb);
     }
 }
 

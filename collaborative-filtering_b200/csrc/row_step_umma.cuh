@@ -551,6 +551,7 @@ __device__ __forceinline__ void umma_role_solver(const RowStepParams& p, const U
     float* red = s.red + (size_t)g * 4 * C::RPB * 4;
     int32_t* bad = s.bad + g * C::RPB + h;
     double acc_d = 0.0, acc_d2 = 0.0;                  // fused residual statistics (thread r == 0 of each matrix)
+    double acc_xx = 0.0, acc_bb = 0.0;                 // fused norms: sum |x|^2, sum bias^2 over the rows solved
 #ifdef B200ALS_TIMING
     long long tacc[8] = {0, 0, 0, 0, 0, 0, 0, 0};
     long long tlast = clock64();
@@ -742,6 +743,8 @@ __device__ __forceinline__ void umma_role_solver(const RowStepParams& p, const U
                                   (2.0f * beta - bias_old) * sx - ridge * xx;
                 acc_d += (double)sd;
                 acc_d2 += (double)sd2;
+                acc_xx += (double)xx;
+                acc_bb += (double)beta * (double)beta;
             } else if (valid && p.status) {
                 if (atomicAdd(&p.status[0], 1) == 0) p.status[1] = (int32_t)row;
             }
@@ -760,6 +763,10 @@ __device__ __forceinline__ void umma_role_solver(const RowStepParams& p, const U
     if (p.stats && q == 0 && seg == 0) {
         atomicAdd(&p.stats[0], acc_d);
         atomicAdd(&p.stats[1], acc_d2);
+    }
+    if (p.norms && q == 0 && seg == 0) {
+        atomicAdd(&p.norms[0], acc_xx);
+        atomicAdd(&p.norms[2], acc_bb);
     }
 }
 

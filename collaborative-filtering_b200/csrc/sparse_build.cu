@@ -55,6 +55,105 @@ __global__ void __launch_bounds__(1024) scan_inclusive_i64_kernel(int64_t* data,
     }
 }
 
+// ---- N2: fold split on the resident observed set (create_folds.py:177-208) ------------------------------
+// The observed entries are one ascending flat-index array; a fold's validation indices are looked up in it
+// (binary search), flagged in a bitset, and the unflagged entries are compacted in order — the sorted
+// `setdiff1d(all_obs, val_idx)` of create_folds.py:200 — with a block count, a single-CTA scan of the block
+// counts and an order-preserving scatter.  Pure integer work: bit-exact by construction.
+__global__ void __launch_bounds__(256) fold_mark_kernel(const int64_t* __restrict__ flat, const float* __restrict__ vals,
+                                                        int64_t nnz, const int64_t* __restrict__ val_idx, int64_t n_val,
+                                                        uint32_t* __restrict__ bits, float* __restrict__ val_vals,
+                                                        int32_t* __restrict__ status) {
+    const int64_t stride = (int64_t)gridDim.x * blockDim.x;
+    for (int64_t j = (int64_t)blockIdx.x * blockDim.x + threadIdx.x; j < n_val; j += stride) {
+        const int64_t v = val_idx[j];
+        int64_t lo = 0, hi = nnz;                       // lower bound
+        while (lo < hi) {
+            const int64_t mid = (lo + hi) >> 1;
+            if (flat[mid] < v) lo = mid + 1; else hi = mid;
+        }
+        if (lo < nnz && flat[lo] == v) {
+            const uint32_t bit = 1u << (lo & 31);
+            const uint32_t old = atomicOr(&bits[lo >> 5], bit);
+            if (old & bit) atomicAdd(&status[1], 1);    // the same entry listed twice
+            val_vals[j] = vals[lo];
+        } else {
+            atomicAdd(&status[0], 1);                   // not an observed entry
+            val_vals[j] = __int_as_float(0x7fc00000);   // NaN, what the reference would read there
+        }
+    }
+}
+
+constexpr int FOLD_BLOCK_ENTRIES = 8192;                // 8 warps x 32 words x 32 entries
+
+__global__ void __launch_bounds__(256) fold_count_kernel(const uint32_t* __restrict__ bits, int64_t nnz,
+                                                         int64_t* __restrict__ block_cnt) {
+    __shared__ int wsum[8];
+    const int64_t word = (int64_t)blockIdx.x * 256 + threadIdx.x;
+    const int64_t first = word * 32;
+    int c = 0;
+    if (first < nnz) {
+        uint32_t keep = ~bits[word];
+        const int64_t left = nnz - first;
+        if (left < 32) keep &= (1u << left) - 1u;
+        c = __popc(keep);
+    }
+#pragma unroll
+    for (int o = 16; o > 0; o >>= 1) c += __shfl_xor_sync(0xffffffffu, c, o);
+    if ((threadIdx.x & 31) == 0) wsum[threadIdx.x >> 5] = c;
+    __syncthreads();
+    if (threadIdx.x == 0) {
+        int t = 0;
+#pragma unroll
+        for (int w = 0; w < 8; ++w) t += wsum[w];
+        block_cnt[blockIdx.x] = t;
+    }
+}
+
+// block_off = inclusive scan of block_cnt (scan_inclusive_i64_kernel); warp w of block b compacts its 1024 entries
+__global__ void __launch_bounds__(256) fold_scatter_kernel(const int64_t* __restrict__ flat, const float* __restrict__ vals,
+                                                           int64_t nnz, const uint32_t* __restrict__ bits,
+                                                           const int64_t* __restrict__ block_incl,
+                                                           int64_t* __restrict__ out_flat, float* __restrict__ out_vals,
+                                                           int64_t* __restrict__ n_train) {
+    __shared__ int wsum[8];
+    const int lane = threadIdx.x & 31, wid = threadIdx.x >> 5;
+    const int64_t word = (int64_t)blockIdx.x * 256 + threadIdx.x;   // this lane's word of the warp's 32
+    const int64_t first = word * 32;
+    uint32_t keep = 0;
+    if (first < nnz) {
+        keep = ~bits[word];
+        const int64_t left = nnz - first;
+        if (left < 32) keep &= (1u << left) - 1u;
+    }
+    const int c = __popc(keep);
+    int incl = c;                                       // inclusive scan of the word counts inside the warp
+#pragma unroll
+    for (int o = 1; o < 32; o <<= 1) {
+        const int t = __shfl_up_sync(0xffffffffu, incl, o);
+        if (lane >= o) incl += t;
+    }
+    if (lane == 31) wsum[wid] = incl;
+    __syncthreads();
+    int64_t base = blockIdx.x ? block_incl[blockIdx.x - 1] : 0;
+    for (int w = 0; w < wid; ++w) base += wsum[w];
+    const int excl = incl - c;
+    // the warp walks its 32 words together: lane l takes entry l of word w (coalesced reads, in-order writes)
+    const int64_t warp_first = ((int64_t)blockIdx.x * 256 + wid * 32) * 32;
+    for (int w = 0; w < 32; ++w) {
+        const uint32_t kw = __shfl_sync(0xffffffffu, keep, w);
+        const int ew = __shfl_sync(0xffffffffu, excl, w);
+        if (kw == 0) continue;
+        const int64_t e = warp_first + (int64_t)w * 32 + lane;
+        if ((kw >> lane) & 1u) {
+            const int64_t dst = base + ew + __popc(kw & ((1u << lane) - 1u));
+            out_flat[dst] = flat[e];
+            out_vals[dst] = vals[e];
+        }
+    }
+    if (n_train && blockIdx.x == gridDim.x - 1 && threadIdx.x == 0) *n_train = block_incl[gridDim.x - 1];
+}
+
 // ---- dense input ----------------------------------------------------------
 // warp per row: row count → indptr[u+1]; per-column counts via atomics (integer
 // adds commute, so the result is exact regardless of order).
@@ -383,6 +482,47 @@ int b200als_row_order(const int64_t* indptr, int64_t n_rows, int32_t* order, int
     ALS_CUDA(cub::DeviceRadixSort::SortPairs(cub_tmp, cub_bytes, (const uint32_t*)keys, keys_out, (const int32_t*)ids,
                                              order, (size_t)n_rows, 0, 32, s));
     g_launch_count += 4;
+    return B200ALS_OK;
+}
+
+int b200als_fold_split_workspace_bytes(int64_t nnz, size_t* bytes_host) {
+    ALS_CHECK_ARG(bytes_host && nnz >= 0, "bad args");
+    const size_t words = (size_t)ceil_div64(nnz, 32);
+    const size_t blocks = (size_t)ceil_div64(nnz, FOLD_BLOCK_ENTRIES);
+    *bytes_host = align_up(words * 4, 256) + align_up(blocks * 8, 256) + 256;
+    return B200ALS_OK;
+}
+
+int b200als_fold_split(const int64_t* flat_sorted, const float* vals, int64_t nnz, const int64_t* val_idx,
+                       int64_t n_val, int64_t* train_flat, float* train_vals, float* val_vals, int64_t* n_train,
+                       int32_t* status, void* workspace, size_t workspace_bytes, b200als_stream_t stream) {
+    ALS_CHECK_ARG(nnz > 0 && n_val >= 0 && flat_sorted && vals && train_flat && train_vals && n_train && status,
+                  "null pointer / empty observed set");
+    ALS_CHECK_ARG(n_val == 0 || (val_idx && val_vals), "null validation arrays");
+    size_t need = 0;
+    b200als_fold_split_workspace_bytes(nnz, &need);
+    if (!workspace || workspace_bytes < need) {
+        set_error("b200als_fold_split: workspace %zu < required %zu", workspace_bytes, need);
+        return B200ALS_E_WORKSPACE;
+    }
+    cudaStream_t s = as_stream(stream);
+    const int64_t words = ceil_div64(nnz, 32), blocks = ceil_div64(nnz, FOLD_BLOCK_ENTRIES);
+    uint32_t* bits = static_cast<uint32_t*>(workspace);
+    int64_t* block_cnt = reinterpret_cast<int64_t*>(static_cast<char*>(workspace) + align_up((size_t)words * 4, 256));
+    ALS_CUDA(cudaMemsetAsync(bits, 0, (size_t)words * 4, s));
+    ALS_CUDA(cudaMemsetAsync(status, 0, 2 * sizeof(int32_t), s));
+    if (n_val > 0) {
+        fold_mark_kernel<<<grid_for(n_val, 256), 256, 0, s>>>(flat_sorted, vals, nnz, val_idx, n_val, bits, val_vals,
+                                                              status);
+        ALS_LAUNCH_CHECK();
+    }
+    fold_count_kernel<<<(unsigned)blocks, 256, 0, s>>>(bits, nnz, block_cnt);
+    ALS_LAUNCH_CHECK();
+    scan_inclusive_i64_kernel<<<1, 1024, 0, s>>>(block_cnt, blocks);
+    ALS_LAUNCH_CHECK();
+    fold_scatter_kernel<<<(unsigned)blocks, 256, 0, s>>>(flat_sorted, vals, nnz, bits, block_cnt, train_flat, train_vals,
+                                                         n_train);
+    ALS_LAUNCH_CHECK();
     return B200ALS_OK;
 }
 

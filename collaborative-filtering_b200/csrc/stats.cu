@@ -413,10 +413,10 @@ int b200als_sse_on_flat(const float* U, int64_t ldu, const float* Z, int64_t ldz
                         const float* b_i, const float* mu, const int64_t* flat_idx, const float* y_true,
                         int64_t count, int64_t n, int32_t k, const int32_t* item_bin, int32_t n_bins,
                         double* sse, int64_t* cnt, b200als_stream_t stream) {
+    ALS_CHECK_ARG(n > 0 && n_bins >= 1 && n_bins <= SSE_MAX_BINS, "n_bins outside [1, 32]");
+    if (count <= 0) return B200ALS_OK;                  // an empty fold: nothing to add (the RMSE is NaN, tune_params.py:162)
     ALS_CHECK_ARG(U && Z && b_u && b_i && mu && flat_idx && y_true && sse && cnt, "null pointer");
     ALS_CHECK_ARG(k >= 1 && k <= B200ALS_MAX_K && (ldu & 3) == 0 && (ldz & 3) == 0, "bad k / ld");
-    ALS_CHECK_ARG(n > 0 && n_bins >= 1 && n_bins <= SSE_MAX_BINS, "n_bins outside [1, 32]");
-    if (count <= 0) return B200ALS_OK;
     sse_on_flat_kernel<<<grid_for(count * 8, 256, 8), 256, 0, as_stream(stream)>>>(
         U, ldu, Z, ldz, b_u, b_i, mu, flat_idx, y_true, count, n, k, item_bin, n_bins, sse,
         reinterpret_cast<long long*>(cnt));

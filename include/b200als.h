@@ -31,7 +31,7 @@
 extern "C" {
 #endif
 
-#define B200ALS_ABI_VERSION 6
+#define B200ALS_ABI_VERSION 7
 
 #define B200ALS_OK            0
 #define B200ALS_E_INVALID    -1   /* bad argument */
@@ -187,6 +187,11 @@ typedef struct b200als_step_args {
     double*  stats_acc;          /* optional, SOLVE mode: A10 fused into the step (als.py:503-511 when Z == F-side
                                     factors are final): [0] += sum_e d_e, [1] += sum_e d_e^2 over the rows solved,
                                     d_e = R_e - (mu + bias_other + bias_own_new + F[idx_e].x_new).  Caller zeroes. */
+    double*  norm_acc;           /* optional, SOLVE mode: the Frobenius norms of als.py:513-516 fused into the step:
+                                    [0] += sum over the rows solved of |x_new|^2, [2] += sum of bias_own_new^2
+                                    (stride 2: acc6 + 2 for the user step, acc6 + 3 for the item step fill the
+                                    layout b200als_finalize_iter reads).  Rows not in the list keep their values:
+                                    the caller adds their (constant) share. */
     const struct b200als_split_plan* split;   /* host pointer, optional (tcgen05 path, SOLVE mode): the plan built by
                                     b200als_split_plan_build for exactly this (indptr, rows, n_list) */
     void*  workspace; size_t workspace_bytes;   /* see b200als_step_workspace_bytes */
@@ -271,6 +276,23 @@ int b200als_predict_pairs(const float* U, int64_t ldu, const float* Z, int64_t l
                           const float* b_u, const float* b_i, const float* mu,
                           const int32_t* rows, const int32_t* cols, int64_t count, int32_t k,
                           float* out, b200als_stream_t stream);
+
+/* ------------------------------------------------------------------------
+ * N2 — `make_train_valid_split` (create_folds.py:177-208) on the resident observed
+ * set, no dense matrices.  flat_sorted: the ascending flat indices u*n+i of every
+ * observed entry (`flatnonzero(~isnan(R))`, create_folds.py:73-76), vals their ratings.
+ * train_flat / train_vals (capacity nnz) receive, in ascending order, the entries
+ * not listed in val_idx — the sorted `setdiff1d` of create_folds.py:200 —, *n_train
+ * (device) their number; val_vals[j] = rating at val_idx[j] (NaN when val_idx[j] is
+ * not an observed entry).  status (device, 2 ints): [0] validation indices that are
+ * not observed entries, [1] validation indices listed more than once.
+ * ---------------------------------------------------------------------- */
+int b200als_fold_split_workspace_bytes(int64_t nnz, size_t* bytes_host);
+int b200als_fold_split(const int64_t* flat_sorted, const float* vals, int64_t nnz,
+                       const int64_t* val_idx, int64_t n_val,
+                       int64_t* train_flat, float* train_vals, float* val_vals,
+                       int64_t* n_train, int32_t* status,
+                       void* workspace, size_t workspace_bytes, b200als_stream_t stream);
 
 /* ------------------------------------------------------------------------
  * N1 — `_rmse_on_indices` (tune_params.py:147-167) and the popularity-bin
