@@ -219,8 +219,8 @@ struct Ldl {
         const uint32_t S4 = 4u * (uint32_t)(K - 4 * g);                                  // column stride (bytes)
         const uint32_t col0 = col_block(cbs, g);                                         // element (i, j0) at col0 + 4 i
         const int dr = r - j0;                                                           // row position relative to the block
-#pragma unroll
-        for (int s = 0; s < 4; ++s) a[s] += (dr == s) ? ridge : 0.0f;
+        // The ridge is added where the pivot block is read: its diagonal is the only place a pivot row's own
+        // diagonal entry is used (the column store's (j, j) slot is never read: 1/d lives in the inv array).
         // every store below is unconditional: a lane with nothing to store writes a dummy word instead (a predicated
         // store compiles to a divergent branch region here, and this loop is one long dependent chain).  Finished
         // lanes (dr < 0) may publish their stale window: nobody reads raw rows above the block.
@@ -235,15 +235,15 @@ struct Ldl {
         const float4 p3 = lds_f32x4(raw + 4u * (uint32_t)(3 * K + j0));
         const float4 zr = lds_f32x4(raw + 4u * (uint32_t)(4 * K));
         // 4 x 4 LDL^T of the pivot block (lower part of P; MUFU.RCP is good to 1 ulp)
-        const float d0 = p0.x, i0 = rcp_approx(d0);
+        const float d0 = p0.x + ridge, i0 = rcp_approx(d0);
         const float l10 = p0.y * i0, l20 = p0.z * i0, l30 = p0.w * i0;
-        const float d1 = fmaf(-l10, p0.y, p1.y), i1 = rcp_approx(d1);
+        const float d1 = fmaf(-l10, p0.y, p1.y + ridge), i1 = rcp_approx(d1);
         const float u21 = fmaf(-l20, p0.y, p1.z), u31 = fmaf(-l30, p0.y, p1.w);
         const float l21 = u21 * i1, l31 = u31 * i1;
-        const float d2 = fmaf(-l21, u21, fmaf(-l20, p0.z, p2.z)), i2 = rcp_approx(d2);
+        const float d2 = fmaf(-l21, u21, fmaf(-l20, p0.z, p2.z + ridge)), i2 = rcp_approx(d2);
         const float u32 = fmaf(-l31, u21, fmaf(-l30, p0.z, p2.w));
         const float l32 = u32 * i2;
-        const float d3 = fmaf(-l32, u32, fmaf(-l31, u31, fmaf(-l30, p0.w, p3.w))), i3 = rcp_approx(d3);
+        const float d3 = fmaf(-l32, u32, fmaf(-l31, u31, fmaf(-l30, p0.w, p3.w + ridge))), i3 = rcp_approx(d3);
         // own row: unscaled entries u_k = l_rk d_k and multipliers t_k = l_rk
         const float u0 = a[0], t0 = u0 * i0;
         const float u1 = fmaf(-t0, p0.y, a[1]), t1 = u1 * i1;
@@ -485,16 +485,19 @@ struct Ldl {
         const uint32_t xb = cbs + X_OFF;
         const int g = r >> 2, jj = r & 3;
         const uint32_t mycol = cbs + 4u * (uint32_t)(4 * g * K - 8 * g * (g - 1) + jj * (K - 4 * g) - 4 * g);
-        const float dinv = fast_rcp(lds_f32(mycol + 4u * r));
+        const float dinv = lds_f32(cbs + INV_OFF + 4u * r);       // 1/d_r as the factorisation used it
         float acc = lds_f32(zb + 4u * r);
         float x = 0.0f;
-#pragma unroll
+        // the block loop stays rolled (one copy of the RPW-step in-warp solve in the instruction cache: the
+        // solver warps of a CTA sit at different places of a ~35 KB loop body and instruction fetch was 20 % of
+        // their issue stalls)
+#pragma unroll 1
         for (int blk = NW - 1; blk >= 0; --blk) {
             if (q == blk) {
                 float lt[RPW];
 #pragma unroll
                 for (int i4 = 0; i4 < RPW; i4 += 4) {
-                    const float4 v = lds_f32x4(mycol + 4u * (blk * RPW + i4));
+                    const float4 v = lds_f32x4(mycol + 4u * (uint32_t)(blk * RPW + i4));
                     lt[i4] = v.x; lt[i4 + 1] = v.y; lt[i4 + 2] = v.z; lt[i4 + 3] = v.w;
                 }
 #pragma unroll
@@ -511,8 +514,8 @@ struct Ldl {
                 if (q < blk) {
 #pragma unroll
                     for (int i4 = 0; i4 < RPW; i4 += 4) {
-                        const float4 c4 = lds_f32x4(mycol + 4u * (blk * RPW + i4));
-                        const float4 x4 = lds_f32x4(xb + 4u * (blk * RPW + i4));
+                        const float4 c4 = lds_f32x4(mycol + 4u * (uint32_t)(blk * RPW + i4));
+                        const float4 x4 = lds_f32x4(xb + 4u * (uint32_t)(blk * RPW + i4));
                         acc = fmaf(-c4.x, x4.x, acc);
                         acc = fmaf(-c4.y, x4.y, acc);
                         acc = fmaf(-c4.z, x4.z, acc);
