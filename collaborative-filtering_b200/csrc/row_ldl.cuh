@@ -235,15 +235,22 @@ struct Ldl {
         const float4 p3 = lds_f32x4(raw + 4u * (uint32_t)(3 * K + j0));
         const float4 zr = lds_f32x4(raw + 4u * (uint32_t)(4 * K));
         // 4 x 4 LDL^T of the pivot block (lower part of P; MUFU.RCP is good to 1 ulp)
-        const float d0 = p0.x + ridge, i0 = rcp_approx(d0);
+        // Two levels of two reciprocals each instead of four in a row: for a 2 x 2 block [a b; b c],
+        // d0 = a, d1 = det / a with det = a c - b^2, so 1/d0 = rcp(a) and 1/d1 = a rcp(det) are independent MUFUs.
+        const float d0 = p0.x + ridge, c11 = p1.y + ridge;
+        const float det1 = fmaf(d0, c11, -p0.y * p0.y);
+        const float i0 = rcp_approx(d0), i1 = d0 * rcp_approx(det1);
+        const float d1 = det1 * i0;
         const float l10 = p0.y * i0, l20 = p0.z * i0, l30 = p0.w * i0;
-        const float d1 = fmaf(-l10, p0.y, p1.y + ridge), i1 = rcp_approx(d1);
         const float u21 = fmaf(-l20, p0.y, p1.z), u31 = fmaf(-l30, p0.y, p1.w);
         const float l21 = u21 * i1, l31 = u31 * i1;
-        const float d2 = fmaf(-l21, u21, fmaf(-l20, p0.z, p2.z + ridge)), i2 = rcp_approx(d2);
+        const float d2 = fmaf(-l21, u21, fmaf(-l20, p0.z, p2.z + ridge));
         const float u32 = fmaf(-l31, u21, fmaf(-l30, p0.z, p2.w));
+        const float s33 = fmaf(-l31, u31, fmaf(-l30, p0.w, p3.w + ridge));
+        const float det2 = fmaf(d2, s33, -u32 * u32);
+        const float i2 = rcp_approx(d2), i3 = d2 * rcp_approx(det2);
+        const float d3 = det2 * i2;
         const float l32 = u32 * i2;
-        const float d3 = fmaf(-l32, u32, fmaf(-l31, u31, fmaf(-l30, p0.w, p3.w + ridge))), i3 = rcp_approx(d3);
         // own row: unscaled entries u_k = l_rk d_k and multipliers t_k = l_rk
         const float u0 = a[0], t0 = u0 * i0;
         const float u1 = fmaf(-t0, p0.y, a[1]), t1 = u1 * i1;

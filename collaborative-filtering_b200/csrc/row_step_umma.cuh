@@ -548,8 +548,9 @@ __device__ __forceinline__ void umma_role_solver(const RowStepParams& p, const U
     const int col_bar = 1 + 3 * g, phase_bar = 2 + 3 * g, start_bar = 3 + 3 * g;
     const uint32_t tmem = *s.tmem_base;
     const uint32_t cbs = ptx::smem_u32(s.mats + (size_t)(g * C::RPB + h) * C::MAT_FLOATS);
-    float* red = s.red + (size_t)g * 4 * C::RPB * 4;
-    int32_t* bad = s.bad + g * C::RPB + h;
+    // explicit .shared addresses for the group's scratch words (a generic LD/ST takes the long-scoreboard path)
+    const uint32_t red_a = ptx::smem_u32(s.red + (size_t)g * 4 * C::RPB * 4);
+    const uint32_t bad_a = ptx::smem_u32(s.bad + g * C::RPB + h);
     double acc_d = 0.0, acc_d2 = 0.0;                  // fused residual statistics (thread r == 0 of each matrix)
     double acc_xx = 0.0, acc_bb = 0.0;                 // fused norms: sum |x|^2, sum bias^2 over the rows solved
 #ifdef B200ALS_TIMING
@@ -560,7 +561,7 @@ __device__ __forceinline__ void umma_role_solver(const RowStepParams& p, const U
 #endif
 
     uint32_t nfac = 0;                                 // factorisations so far (parity of the tensor-core update barrier)
-    int32_t* lastf = s.bad + 16 + g * C::RPB + h;      // split rows: "this group added the last piece"
+    const uint32_t lastf_a = ptx::smem_u32(s.bad + 16 + g * C::RPB + h);   // split rows: "this group added the last piece"
     constexpr int SLOT_LD = K + 4;                     // slot row: k matrix entries | c, s, -, -
 
     for (uint32_t pr = g;; pr += C::NG) {
@@ -596,7 +597,7 @@ __device__ __forceinline__ void umma_role_solver(const RowStepParams& p, const U
         const float ridge = p.reg_row ? p.reg_row[row] : p.reg;
         const float lam_bias = p.lam_bias_row ? p.lam_bias_row[row] : p.lam_bias;
         const float bias_old = p.bias_own[row];
-        if (q == 0 && seg == 0) { *bad = 0; *lastf = 0; }
+        if (q == 0 && seg == 0) { sts_s32(bad_a, 0); sts_s32(lastf_a, 0); }
 
         const uint32_t buf = pr % C::NBUF;
         ptx::mbar_wait(&s.acc_full[pr % C::ACCF], (pr / C::ACCF) & 1, 7, (int)pr);
@@ -635,10 +636,10 @@ __device__ __forceinline__ void umma_role_solver(const RowStepParams& p, const U
             named_bar_sync(phase_bar, 128);            // every thread's adds are fenced
             if (part && q == 0 && seg == 0) {
                 const int old = atomicAdd(p.slot_ctr + slot, 1);
-                if (old == npieces - 1) *lastf = 1;
+                if (old == npieces - 1) sts_s32(lastf_a, 1);
             }
             named_bar_sync(phase_bar, 128);
-            from_slot = part && (*reinterpret_cast<volatile int32_t*>(lastf) != 0);
+            from_slot = part && (lds_s32(lastf_a) != 0);
             if (from_slot) {
                 __threadfence();
                 c_r = __ldcg(gs + K);
@@ -703,7 +704,7 @@ __device__ __forceinline__ void umma_role_solver(const RowStepParams& p, const U
                                   tmem + buf * C::ACC_STRIDE + ((uint32_t)(16 * h) << 16), &s.upd[g * C::RPB + h],
                                   (uint32_t)L::MMA_PHASES * nfac, load_window);
         ++nfac;
-        if (!ok && valid) *bad = 1;
+        if (!ok && valid) sts_s32(bad_a, 1);
         TICK(3);
         const float x = L::backsolve(re, qe, sege, rev ? C::RPW - 1 : 0, cbs, phase_bar);   // barriers inside publish *bad too
 
@@ -716,20 +717,19 @@ __device__ __forceinline__ void umma_role_solver(const RowStepParams& p, const U
             v1 += __shfl_xor_sync(0xffffffffu, v1, o);
             v2 += __shfl_xor_sync(0xffffffffu, v2, o);
         }
-        if (seg == 0) {
-            float* rr = red + (q * C::RPB + h) * 4;
-            rr[0] = v0; rr[1] = v1; rr[2] = v2;
-        }
+        if (seg == 0)
+            sts_s32x4(red_a + 16u * (uint32_t)(q * C::RPB + h),
+                      make_int4(__float_as_int(v0), __float_as_int(v1), __float_as_int(v2), 0));
         named_bar_sync(phase_bar, 128);
-        const bool good = valid && (*bad == 0);
+        const bool good = valid && (lds_s32(bad_a) == 0);
         if (good) p.X[(size_t)row * p.ldx + r] = x;
         if (q == 0 && seg == 0) {
             if (good) {
                 float sx = 0.0f, cx = 0.0f, xx = 0.0f;
 #pragma unroll
                 for (int w = 0; w < 4; ++w) {
-                    const float* rr = red + (w * C::RPB + h) * 4;
-                    sx += rr[0]; cx += rr[1]; xx += rr[2];
+                    const int4 rr = lds_s32x4(red_a + 16u * (uint32_t)(w * C::RPB + h));
+                    sx += __int_as_float(rr.x); cx += __int_as_float(rr.y); xx += __int_as_float(rr.z);
                 }
                 const float cntf = (float)cnt;
                 const float beta = (tsum - sx) / (cntf + lam_bias);            // als.py:431-433 / 464-466
@@ -749,7 +749,8 @@ __device__ __forceinline__ void umma_role_solver(const RowStepParams& p, const U
                 if (atomicAdd(&p.status[0], 1) == 0) p.status[1] = (int32_t)row;
             }
         }
-        named_bar_sync(phase_bar, 128);                // red / xb / columns free for the next pair
+        // no barrier here: the next pair's descriptor barrier stands between these reads (red, bad, x, columns:
+        // everything after the barrier above) and the next writes to them
         TICK(5);
 #ifdef B200ALS_TIMING
         if (blockIdx.x == 0 && threadIdx.x == 96) tacc[6] += 1;
