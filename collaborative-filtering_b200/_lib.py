@@ -82,7 +82,7 @@ _SIGNATURES = {
                                vp, vp, vp, vp],
     "b200als_sumsq": [vp, C.c_int64, C.c_int64, C.c_int64, vp, vp],
     "b200als_finalize_iter": [vp, C.c_int64, vp, vp, vp],
-    "b200als_finalize_iter_fused": [vp, C.c_int64, vp, vp, vp],
+    "b200als_finalize_iter_fused": [vp, vp, C.c_int64, vp, vp, vp],
     "b200als_item_gram_f64": [C.c_int64, vp, vp, vp, C.c_int32, vp, C.c_int64, vp, vp, vp, vp, vp, vp],
     "b200als_wstep_system": [C.c_int64, C.c_int32, C.c_int32, vp, vp, vp, vp, C.c_int64,
                              C.c_double, vp, vp, vp],

@@ -473,6 +473,7 @@ class FitSession:
                 base[4] = self.b_u_d.index_select(0, ue).double().pow(2).sum()
                 base[5] = self.b_i_d.index_select(0, ie).double().pow(2).sum()
             self.acc_base = base
+            self.acc.copy_(base)        # every later iteration: b200als_finalize_iter_fused puts the base back
 
     # ---- small wrappers ---------------------------------------------------------
     def _stream(self):
@@ -555,9 +556,6 @@ class FitSession:
         self._mark("compose")
         if names:
             self._compose(self.Z_d)                                     # als.py:411
-        if fused:
-            self.acc.copy_(self.acc_base)
-            self.launches += 1
         # (1) users (als.py:414-433)
         self._mark("user")
         self._step(rt.indptr, rt.indices, rt.vals, m, self.u_list, self.Z_d, n, self.b_i_d, self.reg_user, None,
@@ -631,8 +629,12 @@ class FitSession:
             check(lib.b200als_sumsq(ptr(self.b_i_d), 1, n, n, acc.data_ptr() + 40, stream), "sumsq")
             self.launches += 4
         slot = it % self.hist.shape[0]
-        fin = lib.b200als_finalize_iter_fused if fused else lib.b200als_finalize_iter
-        check(fin(ptr(acc), rt.nnz, ptr(self.mu_d), self.hist.data_ptr() + 48 * slot, stream), "finalize_iter")
+        if fused:       # also resets the accumulators to their start values for the next iteration
+            check(lib.b200als_finalize_iter_fused(ptr(acc), ptr(self.acc_base), rt.nnz, ptr(self.mu_d),
+                                                  self.hist.data_ptr() + 48 * slot, stream), "finalize_iter")
+        else:
+            check(lib.b200als_finalize_iter(ptr(acc), rt.nnz, ptr(self.mu_d), self.hist.data_ptr() + 48 * slot,
+                                            stream), "finalize_iter")
         self.launches += 1
         self._mark("end")
 

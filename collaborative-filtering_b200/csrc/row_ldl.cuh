@@ -367,46 +367,43 @@ struct Ldl {
         }
     }
 
-    // RPW = 32: the window as two 16-column halves through ONE copy of the 16-column code (a fully unrolled 32-column
-    // substitution is 1400 instructions, and instruction fetch was a quarter of its stall samples): half 0, then
-    // the 16 x 16 rectangle a[16..31] -= t[0..15] . U, then the second half moves down into a[0..15] and the loop
-    // runs the same code on it.  Same operations as the flat form, in the same order per entry.
+    // The window goes through ONE copy of the half-width code as two halves (a flat 32-column substitution is 1400
+    // instructions, and instruction fetch was a quarter of its stall samples): half 0, then the rectangle
+    // a[H..2H) -= t[0..H) . U, then the second half moves down into a[0..H) and the loop runs the same code on it.
+    // Same operations as the flat form, in the same order per entry.
     static __device__ __forceinline__ void subst(float (&a)[RPW], float& rhs, const int r, const uint32_t cbs,
                                                  const int J0, const uint32_t tile_row, const uint32_t tile_lo,
                                                  const bool tile_on) {
-        if constexpr (RPW == 16) {
-            subst_tri<16>(a, rhs, r, cbs, J0, tile_row, tile_lo, tile_on);
-        } else {
-            static_assert(RPW == 16 || RPW == 32, "window halves");
+        constexpr int H = RPW / 2;
+        static_assert(H % 8 == 0, "a half must be whole 8-column core matrices of the panel");
 #pragma unroll 1
-            for (int hf = 0; hf < 2; ++hf) {
-                const int Jh = J0 + 16 * hf;
-                subst_tri<16>(a, rhs, r, cbs, Jh, tile_row + 256u * (uint32_t)hf, tile_lo, tile_on);   // 16 panel columns = 2 x 128 B
-                if (hf == 0) {
-                    const int g0 = Jh >> 2;
+        for (int hf = 0; hf < 2; ++hf) {
+            const int Jh = J0 + H * hf;
+            subst_tri<H>(a, rhs, r, cbs, Jh, tile_row + (uint32_t)(H / 8) * 128u * (uint32_t)hf, tile_lo, tile_on);
+            if (hf == 0) {
+                const int g0 = Jh >> 2;
 #pragma unroll
-                    for (int jb = 0; jb < 4; ++jb) {
-                        const uint32_t rowoff = 16u * (uint32_t)(g0 + 4 + jb);       // rows Jh + 16 + 4 jb .. + 3
+                for (int jb = 0; jb < H / 4; ++jb) {
+                    const uint32_t rowoff = 16u * (uint32_t)(g0 + H / 4 + jb);       // rows Jh + H + 4 jb .. + 3
 #pragma unroll
-                        for (int ib = 0; ib < 4; ++ib) {
-                            const int gi = g0 + ib;
-                            const uint32_t S4i = 4u * (uint32_t)(K - 4 * gi);
-                            const uint32_t ci = col_block(cbs, gi) + rowoff;
-                            const float4 v0 = lds_f32x4(ci);
-                            const float4 v1 = lds_f32x4(ci + S4i);
-                            const float4 v2 = lds_f32x4(ci + 2u * S4i);
-                            const float4 v3 = lds_f32x4(ci + 3u * S4i);
-                            const float t0 = a[4 * ib], t1 = a[4 * ib + 1], t2 = a[4 * ib + 2], t3 = a[4 * ib + 3];
-                            const int c = 16 + 4 * jb;
-                            a[c + 0] = fmaf(-t3, v3.x, fmaf(-t2, v2.x, fmaf(-t1, v1.x, fmaf(-t0, v0.x, a[c + 0]))));
-                            a[c + 1] = fmaf(-t3, v3.y, fmaf(-t2, v2.y, fmaf(-t1, v1.y, fmaf(-t0, v0.y, a[c + 1]))));
-                            a[c + 2] = fmaf(-t3, v3.z, fmaf(-t2, v2.z, fmaf(-t1, v1.z, fmaf(-t0, v0.z, a[c + 2]))));
-                            a[c + 3] = fmaf(-t3, v3.w, fmaf(-t2, v2.w, fmaf(-t1, v1.w, fmaf(-t0, v0.w, a[c + 3]))));
-                        }
+                    for (int ib = 0; ib < H / 4; ++ib) {
+                        const int gi = g0 + ib;
+                        const uint32_t S4i = 4u * (uint32_t)(K - 4 * gi);
+                        const uint32_t ci = col_block(cbs, gi) + rowoff;
+                        const float4 v0 = lds_f32x4(ci);
+                        const float4 v1 = lds_f32x4(ci + S4i);
+                        const float4 v2 = lds_f32x4(ci + 2u * S4i);
+                        const float4 v3 = lds_f32x4(ci + 3u * S4i);
+                        const float t0 = a[4 * ib], t1 = a[4 * ib + 1], t2 = a[4 * ib + 2], t3 = a[4 * ib + 3];
+                        const int c = H + 4 * jb;
+                        a[c + 0] = fmaf(-t3, v3.x, fmaf(-t2, v2.x, fmaf(-t1, v1.x, fmaf(-t0, v0.x, a[c + 0]))));
+                        a[c + 1] = fmaf(-t3, v3.y, fmaf(-t2, v2.y, fmaf(-t1, v1.y, fmaf(-t0, v0.y, a[c + 1]))));
+                        a[c + 2] = fmaf(-t3, v3.z, fmaf(-t2, v2.z, fmaf(-t1, v1.z, fmaf(-t0, v0.z, a[c + 2]))));
+                        a[c + 3] = fmaf(-t3, v3.w, fmaf(-t2, v2.w, fmaf(-t1, v1.w, fmaf(-t0, v0.w, a[c + 3]))));
                     }
-#pragma unroll
-                    for (int i = 0; i < 16; ++i) a[i] = a[16 + i];
                 }
+#pragma unroll
+                for (int i = 0; i < H; ++i) a[i] = a[H + i];
             }
         }
     }

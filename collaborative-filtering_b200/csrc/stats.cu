@@ -144,7 +144,8 @@ __global__ void finalize_iter_kernel(const double* __restrict__ acc, int64_t nnz
 }
 
 // acc[0..1] are sums of d' = d - mu_old (the item step ran with mu_old, als.py:447): shift back
-__global__ void finalize_iter_fused_kernel(const double* __restrict__ acc, int64_t nnz, float* mu_f32, double* hist) {
+__global__ void finalize_iter_fused_kernel(double* __restrict__ acc, const double* __restrict__ reset, int64_t nnz,
+                                           float* mu_f32, double* hist) {
     if (threadIdx.x == 0 && blockIdx.x == 0) {
         const double N = (double)nnz;
         const double delta = acc[0] / N;
@@ -158,6 +159,8 @@ __global__ void finalize_iter_fused_kernel(const double* __restrict__ acc, int64
         hist[4] = sqrt(acc[5]);
         hist[5] = mu;
         *mu_f32 = (float)mu;
+        if (reset)                                          // start values of the next iteration's accumulators
+            for (int i = 0; i < 6; ++i) acc[i] = reset[i];
     }
 }
 
@@ -369,10 +372,10 @@ int b200als_finalize_iter(const double* acc6, int64_t nnz_total, float* mu_f32, 
     return B200ALS_OK;
 }
 
-int b200als_finalize_iter_fused(const double* acc6, int64_t nnz_total, float* mu_f32, double* hist6,
+int b200als_finalize_iter_fused(double* acc6, const double* reset6, int64_t nnz_total, float* mu_f32, double* hist6,
                                 b200als_stream_t stream) {
     ALS_CHECK_ARG(acc6 && mu_f32 && hist6 && nnz_total > 0, "bad args");
-    finalize_iter_fused_kernel<<<1, 32, 0, as_stream(stream)>>>(acc6, nnz_total, mu_f32, hist6);
+    finalize_iter_fused_kernel<<<1, 32, 0, as_stream(stream)>>>(acc6, reset6, nnz_total, mu_f32, hist6);
     ALS_LAUNCH_CHECK();
     return B200ALS_OK;
 }

@@ -236,8 +236,10 @@ int b200als_finalize_iter(const double* acc6, int64_t nnz_total,
                           float* mu_f32, double* hist6, b200als_stream_t stream);
 /* Same, when acc6[0..1] came from b200als_step_args.stats_acc of the item step, i.e. are sums of
  * d'_e = d_e - mu_old (the step subtracts the mu it ran with):  mu = mu_old + acc[0]/nnz,
- * rmse^2 = acc[1]/nnz - (acc[0]/nnz)^2.  *mu_f32 is read (mu_old) and overwritten. */
-int b200als_finalize_iter_fused(const double* acc6, int64_t nnz_total,
+ * rmse^2 = acc[1]/nnz - (acc[0]/nnz)^2.  *mu_f32 is read (mu_old) and overwritten.
+ * reset6 (optional): acc6 <- reset6 afterwards, the start values of the next iteration's
+ * accumulators (zeros, plus the norm share of the rows no step solves). */
+int b200als_finalize_iter_fused(double* acc6, const double* reset6, int64_t nnz_total,
                                 float* mu_f32, double* hist6, b200als_stream_t stream);
 
 /* ------------------------------------------------------------------------
