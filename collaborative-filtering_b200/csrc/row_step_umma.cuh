@@ -541,7 +541,11 @@ __device__ __forceinline__ void umma_role_solver(const RowStepParams& p, const U
     // Odd groups eliminate in reverse order (the permuted system P A P^T, P = index reversal): the
     // thread-per-row factorisation loads the LAST rows most, so alternating the direction spreads
     // the heavy warps over quadrants 0 and 3 instead of piling them on one SM sub-partition.
-    const bool rev = (g & 1) != 0;
+    // k = 128: the last group stays forward whatever its parity — a reversed group's tensor-core update of phase NW-2
+    // reads (K - RPW)/8 row groups of garbage PAST its panel in the raw-row scratch at the end of the matrix buffer:
+    // 1.5 KB at k = 64 (stays inside the scratch words behind the matrices), 6 KB at k = 128, which leaves the CTA's
+    // shared memory when the LAST matrix buffer is a reversed group's (measured: illegal access with NG = 4)
+    const bool rev = (g & 1) != 0 && (K == 64 || g != C::NG - 1);
     const int qe = rev ? 3 - q : q;                    // elimination-order block / row / lane segment
     const int re = rev ? K - 1 - r : r;
     const int sege = rev ? C::RPW - 1 - seg : seg;
