@@ -15,6 +15,13 @@ import types
 
 import numpy as np
 
+
+def _dummy_attr(attr):
+    """Stand-in modules: any public attribute is a dummy class (nothing of them is ever called)."""
+    if attr.startswith("__"):
+        raise AttributeError(attr)
+    return type(attr, (), {})
+
 HERE = os.path.dirname(os.path.abspath(__file__))
 REPO = os.path.dirname(os.path.dirname(HERE))
 REF = os.environ.get("B200ALS_REFERENCE", "/root/reference")
@@ -27,7 +34,7 @@ for name in ("optuna", "optuna.samplers", "optuna.pruners", "optuna.visualizatio
             __import__(name)
         except Exception:
             mod = types.ModuleType(name)
-            mod.__getattr__ = lambda attr, _n=name: type(attr, (), {})     # any attribute: a dummy class
+            mod.__getattr__ = _dummy_attr
             sys.modules[name] = mod
 
 from scripts.als import ALS as RefALS                                                    # noqa: E402
