@@ -8,7 +8,7 @@ from .config import ALSConfig, BiasesConfig, CoreConfig, GraphConfig, GraphSimCo
 from .als import ALS, EPS, SCALE_FACTOR
 from .dist import Shard
 from . import _lib
-from . import evaluate
+from . import evaluate, hostrng
 
 __all__ = ["ALS", "ALSConfig", "CoreConfig", "BiasesConfig", "GraphConfig", "GraphSimConfig",
            "Shard", "EPS", "SCALE_FACTOR"]

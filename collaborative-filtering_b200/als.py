@@ -22,7 +22,7 @@ import logging
 import numpy as np
 import torch
 
-from . import _lib, graph as _graph
+from . import _lib, graph as _graph, hostrng as _hostrng
 from ._lib import StepArgs, check, ptr
 from .config import ALSConfig
 from .dist import Shard
@@ -372,11 +372,15 @@ class FitSession:
         W_d = self.W_d = [torch.zeros(features[nm].shape[1], ld, dtype=f32, device=dev) for nm in names]
         W64_d = self.W64_d = [torch.zeros(features[nm].shape[1] * k, dtype=f64, device=dev) for nm in names]
         if init is None:
-            rng = np.random.default_rng(model.random_state)             # als.py:329
-            U_d[:m, :k] = torch.from_numpy(rng.normal(scale=SCALE_FACTOR, size=(m, k)).astype(np.float32)).to(dev)
-            V_d[:n, :k] = torch.from_numpy(rng.normal(scale=SCALE_FACTOR, size=(n, k)).astype(np.float32)).to(dev)
+            # als.py:329, 367-376: default_rng(random_state).normal(scale=0.1, ...) — the same values, drawn on
+            # all host cores (hostrng.py)
+            draws = _hostrng.normal_stream(model.random_state, [(m, k), (n, k)] + [(features[nm].shape[1], k)
+                                                                                  for nm in names],
+                                           [np.float32, np.float32] + [np.float64] * len(names), SCALE_FACTOR)
+            U_d[:m, :k] = torch.from_numpy(draws[0]).to(dev)
+            V_d[:n, :k] = torch.from_numpy(draws[1]).to(dev)
             for f, nm in enumerate(names):
-                w0 = rng.normal(scale=SCALE_FACTOR, size=(features[nm].shape[1], k))
+                w0 = draws[2 + f]
                 W64_d[f].copy_(torch.from_numpy(w0.reshape(-1)).to(dev))
                 W_d[f][:, :k] = torch.from_numpy(w0.astype(np.float32)).to(dev)
         elif isinstance(init, str) and init == "device":

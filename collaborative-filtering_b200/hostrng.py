@@ -1,0 +1,75 @@
+"""The reference's factor-initialisation draw on all host cores, bit-identical to numpy.
+
+The reference (scripts/als.py:329, 367-376) seeds ONE `np.random.default_rng(random_state)` and draws
+`rng.normal(scale=0.1, size=(m, k))` for U, then V, then every W_f.  Seed parity needs exactly those values;
+numpy walks the stream on one core (half of the end-to-end fit time at the Netflix shape).
+`normal_stream` returns the same arrays from `libb200als_host.so` (include/b200als_host.h,
+csrc/host_rng.c: numpy's own ziggurat code over a random-access PCG64, chunks decoded speculatively in
+parallel and stitched).  If that library has not been built the draw falls back to numpy itself — the same
+values, one core — since this is host-side plumbing, not the CUDA path.
+"""
+from __future__ import annotations
+
+import ctypes as C
+import logging
+import os
+
+import numpy as np
+
+logger = logging.getLogger(__name__)
+
+_HERE = os.path.dirname(os.path.abspath(__file__))
+HOST_LIB_PATH = os.path.join(_HERE, "libb200als_host.so")
+_lib = None
+_M64 = (1 << 64) - 1
+
+
+def _load():
+    global _lib
+    if _lib is None:
+        if not os.path.exists(HOST_LIB_PATH):
+            _lib = False
+            logger.info("libb200als_host.so not built: drawing the initial factors with numpy on one core")
+        else:
+            lib = C.CDLL(HOST_LIB_PATH)
+            fn = lib.b200als_host_normal_fill
+            fn.restype = C.c_int
+            fn.argtypes = [C.c_uint64] * 4 + [C.c_int32, C.c_void_p, C.c_void_p, C.c_void_p, C.c_double, C.c_int32,
+                                              C.c_void_p]
+            _lib = lib
+    return _lib or None
+
+
+def host_threads() -> int:
+    env = os.environ.get("B200ALS_HOST_THREADS")
+    if env:
+        return max(1, int(env))
+    try:
+        n = len(os.sched_getaffinity(0))
+    except AttributeError:
+        n = os.cpu_count() or 1
+    return max(1, min(n, 32))
+
+
+def normal_stream(seed, shapes, dtypes, scale: float, n_threads: int | None = None, force_numpy: bool = False):
+    """[rng.normal(scale=scale, size=s).astype(d) for s, d in zip(shapes, dtypes)] with rng = default_rng(seed),
+    dtypes float32 / float64."""
+    dtypes = [np.dtype(d) for d in dtypes]
+    assert all(d in (np.dtype(np.float32), np.dtype(np.float64)) for d in dtypes)
+    lib = None if force_numpy else _load()
+    rng = np.random.default_rng(seed)
+    if lib is None:
+        return [rng.normal(scale=scale, size=s).astype(d, copy=False) for s, d in zip(shapes, dtypes)]
+    st = rng.bit_generator.state
+    assert st["bit_generator"] == "PCG64" and not st["has_uint32"], st
+    state, inc = int(st["state"]["state"]), int(st["state"]["inc"])
+    outs = [np.empty(s, dtype=d) for s, d in zip(shapes, dtypes)]
+    counts = np.array([o.size for o in outs], dtype=np.int64)
+    ptrs = np.array([o.ctypes.data for o in outs], dtype=np.uint64)
+    as_f32 = np.array([d == np.dtype(np.float32) for d in dtypes], dtype=np.int32)
+    rc = lib.b200als_host_normal_fill(state >> 64, state & _M64, inc >> 64, inc & _M64, len(outs), counts.ctypes.data,
+                                      ptrs.ctypes.data, as_f32.ctypes.data, float(scale),
+                                      int(n_threads or host_threads()), None)
+    if rc != 0:
+        raise MemoryError(f"b200als_host_normal_fill failed (code {rc})")
+    return outs
