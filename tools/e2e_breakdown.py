@@ -26,7 +26,10 @@ for rep in range(2):                       # second pass: warm allocator, the nu
     rt = stage("h2d_and_csr_csc_build", lambda: ratings_from_flat(flat_h, vals_h, (m, n), dev, sorted_input=True))
     rng = np.random.default_rng(42)
     t = time.perf_counter(); rng.normal(scale=0.1, size=(m, k)); rng.normal(scale=0.1, size=(n, k))
+    out["numpy_rng_alone"] = round(time.perf_counter() - t, 4)
+    t = time.perf_counter(); b200als.hostrng.normal_stream(42, [(m, k), (n, k)], [np.float32] * 2, 0.1)
     out["host_rng_alone"] = round(time.perf_counter() - t, 4)
+    out["host_threads"] = b200als.hostrng.host_threads()
     mu0 = float(rt.vals.sum(dtype=torch.float64).item() / nnz)
     ses = stage("session_init_incl_host_rng_and_upload", lambda: model.session(rt, mu0))
     stage("iterations", lambda: [ses.iteration(it) for it in range(K)])
