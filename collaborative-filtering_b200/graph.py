@@ -10,33 +10,82 @@ sweep (`als.py:453-461`, live V) run level-parallel with sequential semantics.
 """
 from __future__ import annotations
 
+from concurrent.futures import ThreadPoolExecutor
+
 import numpy as np
 
+from . import _hostlib
 
-def similarity_topk(X: np.ndarray, topk, eps: float) -> np.ndarray:
+_SMALL = 1 << 20          # below this many entries of S a thread team costs more than the pass
+
+
+def _threads(S: np.ndarray, n_threads) -> int:
+    return 1 if S.size < _SMALL else int(n_threads or _hostlib.host_threads())
+
+
+def _elem_ok(S: np.ndarray) -> bool:
+    return S.ndim == 2 and S.flags.c_contiguous and S.dtype in (np.dtype(np.float32), np.dtype(np.float64))
+
+
+def similarity_topk(X: np.ndarray, topk, eps: float, n_threads: int | None = None) -> np.ndarray:
     """Dense symmetric top-k cosine similarity, zero diagonal (als.py:220-240).
 
-    dtype follows X (float32 features → float32 S), as in the reference.
+    dtype follows X (float32 features → float32 S), as in the reference.  Which of the tied similarities
+    survive is decided by numpy's own `argpartition` (introselect), as in the reference's
+    `np.argpartition(S[i], -topk)`; along the last axis of a 2-D block numpy runs that same selection row by
+    row, so blocks of rows go through one call each on a thread pool (the GIL is released inside), and the
+    final `np.maximum(S, S.T)` is one in-place pass of libb200als_host.so over tile pairs.
+    tests/test_host_graph.py holds this against the row-by-row loop and the reference's fixtures.
     """
     row_norm = np.sqrt((X * X).sum(axis=1, keepdims=True)) + eps
     unit = X / row_norm
     S = unit @ unit.T
+    nth = _threads(S, n_threads)
     np.fill_diagonal(S, 0.0)
     n = S.shape[0]
     if topk is not None and topk < n:
-        for i in range(n):
-            weakest = np.argpartition(S[i], -topk)[:-topk]
-            S[i, weakest] = 0.0
-    return np.maximum(S, S.T)
+        rb = max(16, min(256, (1 << 19) // n))       # rows per call: long enough to amortise the call, short enough to balance
+
+        def prune(lo):
+            blk = S[lo:lo + rb]
+            order = np.argpartition(blk, -topk, axis=1)                 # row by row the reference's 1-D call
+            np.put_along_axis(blk, order[:, :-topk], 0.0, axis=1)       # S[i, weakest] = 0.0
+
+        if nth > 1:
+            with ThreadPoolExecutor(nth) as pool:
+                list(pool.map(prune, range(0, n, rb)))
+        else:
+            for lo in range(0, n, rb):
+                prune(lo)
+    lib = _hostlib.load()
+    if lib is None or not _elem_ok(S):
+        return np.maximum(S, S.T)
+    if lib.b200als_host_symmetrize_max(S.ctypes.data, n, S.dtype.itemsize, nth) != 0:
+        raise ValueError("b200als_host_symmetrize_max: bad arguments")
+    return S
 
 
-def to_csr(S: np.ndarray):
+def to_csr(S: np.ndarray, n_threads: int | None = None):
     """CSR of the nonzeros of S: (sptr int64, sidx int32, sval float32)."""
     n = S.shape[0]
-    r, c = np.nonzero(S)                       # row-major → ascending columns per row
+    lib = _hostlib.load()
+    if lib is None or not _elem_ok(S):
+        r, c = np.nonzero(S)                       # row-major → ascending columns per row
+        sptr = np.zeros(n + 1, dtype=np.int64)
+        np.cumsum(np.bincount(r, minlength=n), out=sptr[1:])
+        return sptr, c.astype(np.int32), S[r, c].astype(np.float32)
+    nth = _threads(S, n_threads)
+    cols, eb = S.shape[1], S.dtype.itemsize
     sptr = np.zeros(n + 1, dtype=np.int64)
-    np.cumsum(np.bincount(r, minlength=n), out=sptr[1:])
-    return sptr, c.astype(np.int32), S[r, c].astype(np.float32)
+    if lib.b200als_host_dense_row_nnz(S.ctypes.data, n, cols, eb, sptr[1:].ctypes.data, nth) != 0:
+        raise ValueError("b200als_host_dense_row_nnz: bad arguments")
+    np.cumsum(sptr[1:], out=sptr[1:])
+    sidx = np.empty(int(sptr[-1]), dtype=np.int32)
+    sval = np.empty(int(sptr[-1]), dtype=np.float32)
+    if lib.b200als_host_dense_to_csr(S.ctypes.data, n, cols, eb, sptr.ctypes.data, sidx.ctypes.data, sval.ctypes.data,
+                                     nth) != 0:
+        raise ValueError("b200als_host_dense_to_csr: bad arguments")
+    return sptr, sidx, sval
 
 
 def level_schedule(sptr: np.ndarray, sidx: np.ndarray, rated: np.ndarray):

@@ -10,45 +10,11 @@ values, one core — since this is host-side plumbing, not the CUDA path.
 """
 from __future__ import annotations
 
-import ctypes as C
-import logging
-import os
-
 import numpy as np
 
-logger = logging.getLogger(__name__)
+from ._hostlib import HOST_LIB_PATH, host_threads, load as _load   # noqa: F401  (re-exported)
 
-_HERE = os.path.dirname(os.path.abspath(__file__))
-HOST_LIB_PATH = os.path.join(_HERE, "libb200als_host.so")
-_lib = None
 _M64 = (1 << 64) - 1
-
-
-def _load():
-    global _lib
-    if _lib is None:
-        if not os.path.exists(HOST_LIB_PATH):
-            _lib = False
-            logger.info("libb200als_host.so not built: drawing the initial factors with numpy on one core")
-        else:
-            lib = C.CDLL(HOST_LIB_PATH)
-            fn = lib.b200als_host_normal_fill
-            fn.restype = C.c_int
-            fn.argtypes = [C.c_uint64] * 4 + [C.c_int32, C.c_void_p, C.c_void_p, C.c_void_p, C.c_double, C.c_int32,
-                                              C.c_void_p]
-            _lib = lib
-    return _lib or None
-
-
-def host_threads() -> int:
-    env = os.environ.get("B200ALS_HOST_THREADS")
-    if env:
-        return max(1, int(env))
-    try:
-        n = len(os.sched_getaffinity(0))
-    except AttributeError:
-        n = os.cpu_count() or 1
-    return max(1, min(n, 32))
 
 
 def normal_stream(seed, shapes, dtypes, scale: float, n_threads: int | None = None, force_numpy: bool = False):

@@ -1,0 +1,85 @@
+"""A4 / A8 host set-up (scripts/als.py:220-240): the threaded similarity build and the C passes of
+libb200als_host.so give exactly the arrays of the reference's row-by-row numpy sequence."""
+import numpy as np
+import pytest
+
+from b200als import _hostlib, graph
+
+
+def _reference_sequence(X, topk, eps):
+    """The reference's statements, one row at a time (scripts/als.py:220-240)."""
+    unit = X / (np.sqrt((X * X).sum(axis=1, keepdims=True)) + eps)
+    S = unit @ unit.T
+    np.fill_diagonal(S, 0.0)
+    n = S.shape[0]
+    if topk is not None and topk < n:
+        for i in range(n):
+            weakest = np.argpartition(S[i], -topk)[:-topk]
+            S[i, weakest] = 0.0
+    return np.maximum(S, S.T)
+
+
+def _numpy_csr(S):
+    n = S.shape[0]
+    r, c = np.nonzero(S)
+    sptr = np.zeros(n + 1, dtype=np.int64)
+    np.cumsum(np.bincount(r, minlength=n), out=sptr[1:])
+    return sptr, c.astype(np.int32), S[r, c].astype(np.float32)
+
+
+def _features(n, d, dtype, signed, seed):
+    rng = np.random.default_rng(seed)
+    X = (rng.random((n, d)) < 0.15).astype(dtype)          # binary genre-like rows: massive ties, some all-zero rows
+    if signed:
+        X = X * rng.standard_normal((n, d)).astype(dtype)
+    return X
+
+
+@pytest.mark.parametrize("n,d,dtype,signed", [
+    (1, 3, np.float32, False), (37, 5, np.float32, False), (131, 7, np.float64, True),
+    (700, 19, np.float32, False), (1100, 19, np.float32, False),      # 1100² > 2^20: thread pool + OpenMP passes
+    (1300, 12, np.float64, True),
+])
+@pytest.mark.parametrize("topk", [1, 5, 40, None])
+def test_similarity_and_csr_equal_the_row_by_row_sequence(n, d, dtype, signed, topk):
+    X = _features(n, d, dtype, signed, seed=n + (topk or 0))
+    want = _reference_sequence(X, topk, 1e-8)
+    for nth in (1, 3, 8):
+        S = graph.similarity_topk(X, topk, 1e-8, n_threads=nth)
+        assert S.dtype == want.dtype and np.array_equal(S, want), (n, topk, nth)
+        assert np.array_equal(S, S.T)
+        got, ref = graph.to_csr(S, n_threads=nth), _numpy_csr(want)
+        assert all(g.dtype == r.dtype and np.array_equal(g, r) for g, r in zip(got, ref))
+
+
+def test_threading_is_forced_for_large_inputs(monkeypatch):
+    """With the size threshold lowered every pass takes its threaded branch on a small case."""
+    monkeypatch.setattr(graph, "_SMALL", 1)
+    X = _features(257, 9, np.float32, False, seed=5)
+    want = _reference_sequence(X, 7, 1e-8)
+    S = graph.similarity_topk(X, 7, 1e-8, n_threads=4)
+    assert np.array_equal(S, want)
+    assert all(np.array_equal(g, r) for g, r in zip(graph.to_csr(S, n_threads=4), _numpy_csr(want)))
+
+
+def test_numpy_expressions_are_used_without_the_library(monkeypatch):
+    monkeypatch.setattr(_hostlib, "load", lambda: None)
+    X = _features(90, 6, np.float32, False, seed=2)
+    want = _reference_sequence(X, 5, 1e-8)
+    S = graph.similarity_topk(X, 5, 1e-8)
+    assert np.array_equal(S, want)
+    assert all(np.array_equal(g, r) for g, r in zip(graph.to_csr(S), _numpy_csr(want)))
+
+
+def test_symmetrize_propagates_nan_like_numpy():
+    lib = _hostlib.load()
+    assert lib is not None, "libb200als_host.so missing: run __graft_entry__.build()"
+    rng = np.random.default_rng(0)
+    for dt in (np.float32, np.float64):
+        A = rng.standard_normal((150, 150)).astype(dt)
+        A[rng.random(A.shape) < 0.05] = np.nan
+        want = np.maximum(A, A.T)
+        assert lib.b200als_host_symmetrize_max(A.ctypes.data, 150, A.dtype.itemsize, 4) == 0
+        assert np.array_equal(A, want, equal_nan=True)
+    assert lib.b200als_host_symmetrize_max(None, 5, 4, 1) == -1
+    assert lib.b200als_host_symmetrize_max(A.ctypes.data, 5, 2, 1) == -1
