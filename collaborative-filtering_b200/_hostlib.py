@@ -21,6 +21,7 @@ _SIGNATURES = {
     "b200als_host_symmetrize_max": [vp, i64, i32, i32],
     "b200als_host_dense_row_nnz": [vp, i64, i64, i32, vp, i32],
     "b200als_host_dense_to_csr": [vp, i64, i64, i32, vp, vp, vp, i32],
+    "b200als_host_graph_levels": [vp, vp, vp, i64, vp],
 }
 EXPORTED_SYMBOLS = tuple(_SIGNATURES)
 

@@ -82,3 +82,22 @@ int b200als_host_dense_to_csr(const void* S, int64_t rows, int64_t cols, int32_t
     }
     return 0;
 }
+
+// Level of every rated row in the lower-triangular dependency DAG of CSR(S) (graph.py: level_schedule): a rated
+// row runs one level after its deepest rated neighbour with a smaller index; unrated rows get -1.  Sequential by
+// nature (level[i] needs level[j < i]) and a few hundred thousand steps at most, so one thread.
+int b200als_host_graph_levels(const int64_t* sptr, const int32_t* sidx, const uint8_t* rated, int64_t n,
+                              int64_t* level) {
+    if (n < 0 || (n > 0 && (!sptr || !rated || !level)) || (n > 0 && sptr[n] > 0 && !sidx)) return -1;
+    for (int64_t i = 0; i < n; ++i) {
+        if (!rated[i]) { level[i] = -1; continue; }
+        int64_t lv = -1;
+        for (int64_t e = sptr[i]; e < sptr[i + 1]; ++e) {
+            const int64_t j = sidx[e];
+            if (j < 0 || j >= n) return -1;
+            if (j < i && level[j] > lv) lv = level[j];
+        }
+        level[i] = lv + 1;
+    }
+    return 0;
+}

@@ -102,13 +102,21 @@ def level_schedule(sptr: np.ndarray, sidx: np.ndarray, rated: np.ndarray):
     """
     n = sptr.size - 1
     level = np.full(n, -1, dtype=np.int64)
-    for i in range(n):
-        if not rated[i]:
-            continue
-        nb = sidx[sptr[i]:sptr[i + 1]]
-        nb = nb[nb < i]
-        lv = level[nb]
-        level[i] = (lv.max() + 1) if lv.size and lv.max() >= 0 else 0
+    lib = _hostlib.load()
+    if lib is not None:
+        sp = np.ascontiguousarray(sptr, dtype=np.int64)
+        si = np.ascontiguousarray(sidx, dtype=np.int32)
+        ra = np.ascontiguousarray(rated, dtype=np.uint8)
+        if lib.b200als_host_graph_levels(sp.ctypes.data, si.ctypes.data, ra.ctypes.data, n, level.ctypes.data) != 0:
+            raise ValueError("b200als_host_graph_levels: bad CSR")
+    else:
+        for i in range(n):
+            if not rated[i]:
+                continue
+            nb = sidx[sptr[i]:sptr[i + 1]]
+            nb = nb[nb < i]
+            lv = level[nb]
+            level[i] = (lv.max() + 1) if lv.size and lv.max() >= 0 else 0
     rows = np.flatnonzero(level >= 0)
     if rows.size == 0:
         return np.zeros(1, dtype=np.int64), np.zeros(0, dtype=np.int32)

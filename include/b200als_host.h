@@ -40,6 +40,12 @@ int b200als_host_dense_row_nnz(const void* S, int64_t rows, int64_t cols, int32_
 int b200als_host_dense_to_csr(const void* S, int64_t rows, int64_t cols, int32_t elem_bytes, const int64_t* sptr,
                               int32_t* sidx, float* sval, int32_t n_threads);
 
+/* level[i] of every rated row i in the dependency order of the Gauss-Seidel item sweep (scripts/als.py:453-461
+ * reads the freshly written V_j of neighbours j < i): 0 if no rated neighbour has a smaller index, else 1 + the
+ * deepest such neighbour's level; -1 for unrated rows (rated[i] == 0, skipped by scripts/als.py:440-441). */
+int b200als_host_graph_levels(const int64_t* sptr, const int32_t* sidx, const uint8_t* rated, int64_t n,
+                              int64_t* level);
+
 #ifdef __cplusplus
 }
 #endif

@@ -83,3 +83,25 @@ def test_symmetrize_propagates_nan_like_numpy():
         assert np.array_equal(A, want, equal_nan=True)
     assert lib.b200als_host_symmetrize_max(None, 5, 4, 1) == -1
     assert lib.b200als_host_symmetrize_max(A.ctypes.data, 5, 2, 1) == -1
+
+
+def test_level_schedule_equals_the_python_loop(monkeypatch):
+    rng = np.random.default_rng(4)
+    for n, topk, p_rated in ((1, 1, 1.0), (60, 3, 0.7), (900, 5, 0.9), (1200, 40, 0.5), (300, None, 1.0)):
+        X = _features(n, 8, np.float32, False, seed=n)
+        sptr, sidx, _ = graph.to_csr(graph.similarity_topk(X, topk, 1e-8))
+        rated = rng.random(n) < p_rated
+        got = graph.level_schedule(sptr, sidx, rated)
+        with monkeypatch.context() as mp:
+            mp.setattr(_hostlib, "load", lambda: None)
+            want = graph.level_schedule(sptr, sidx, rated)
+        assert all(g.dtype == w.dtype and np.array_equal(g, w) for g, w in zip(got, want)), n
+        # the schedule's defining property: every rated neighbour with a smaller index sits in an earlier level
+        level = np.full(n, -1)
+        for lv in range(got[0].size - 1):
+            level[got[1][got[0][lv]:got[0][lv + 1]]] = lv
+        assert np.array_equal(level >= 0, rated)
+        for i in np.flatnonzero(rated)[:200]:
+            nb = sidx[sptr[i]:sptr[i + 1]]
+            nb = nb[(nb < i) & rated[nb]]
+            assert (level[nb] < level[i]).all()
