@@ -44,6 +44,9 @@ def load():
 
 
 def host_threads() -> int:
+    """Threads for one host pass: the cores this process may run on (at most 32), shared evenly between the
+    ranks of a node under torchrun (LOCAL_WORLD_SIZE) — every rank makes the same draw at the same time, and an
+    oversubscribed OpenMP team spins at its barriers.  B200ALS_HOST_THREADS overrides."""
     env = os.environ.get("B200ALS_HOST_THREADS")
     if env:
         return max(1, int(env))
@@ -51,4 +54,8 @@ def host_threads() -> int:
         n = len(os.sched_getaffinity(0))
     except AttributeError:
         n = os.cpu_count() or 1
-    return max(1, min(n, 32))
+    try:
+        local_ranks = max(1, int(os.environ.get("LOCAL_WORLD_SIZE", "1")))
+    except ValueError:
+        local_ranks = 1
+    return max(1, min(n, 32) // local_ranks)

@@ -97,3 +97,14 @@ def test_tiny_chunks_exercise_the_stitch(tmp_path):
                 f32.ctypes.data, 1.0, 4, None)
         assert rc == 0
         assert _same_bits(out, np.random.default_rng(seed).standard_normal(out.size))
+
+
+def test_host_threads_are_shared_between_local_ranks(monkeypatch):
+    monkeypatch.delenv("B200ALS_HOST_THREADS", raising=False)
+    monkeypatch.delenv("LOCAL_WORLD_SIZE", raising=False)
+    alone = hostrng.host_threads()
+    assert 1 <= alone <= 32
+    monkeypatch.setenv("LOCAL_WORLD_SIZE", "8")
+    assert hostrng.host_threads() == max(1, alone // 8)
+    monkeypatch.setenv("B200ALS_HOST_THREADS", "5")
+    assert hostrng.host_threads() == 5
