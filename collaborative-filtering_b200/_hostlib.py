@@ -22,6 +22,7 @@ _SIGNATURES = {
     "b200als_host_dense_row_nnz": [vp, i64, i64, i32, vp, i32],
     "b200als_host_dense_to_csr": [vp, i64, i64, i32, vp, vp, vp, i32],
     "b200als_host_graph_levels": [vp, vp, vp, i64, vp],
+    "b200als_host_widen_f32": [vp, i64, vp, i64, i64, i32],
 }
 EXPORTED_SYMBOLS = tuple(_SIGNATURES)
 

@@ -22,7 +22,7 @@ import logging
 import numpy as np
 import torch
 
-from . import _lib, graph as _graph, hostrng as _hostrng
+from . import _lib, graph as _graph, hostrng as _hostrng, readback as _readback
 from ._lib import StepArgs, check, ptr
 from .config import ALSConfig
 from .dist import Shard
@@ -661,10 +661,10 @@ class FitSession:
         model._set_history(h)
         if done:
             model.mu = float(h[-1, 5])
-        model.U = self.U_d[:rt.m, :k].double().cpu().numpy()
-        model.V = self.V_d[:rt.n, :k].double().cpu().numpy()
-        model.b_u = self.b_u_d[:rt.m].double().cpu().numpy()
-        model.b_i = self.b_i_d[:rt.n].double().cpu().numpy()
+        model.U = _readback.f64_from_device(self.U_d[:rt.m, :k])
+        model.V = _readback.f64_from_device(self.V_d[:rt.n, :k])
+        model.b_u = _readback.f64_from_device(self.b_u_d[:rt.m])
+        model.b_i = _readback.f64_from_device(self.b_i_d[:rt.n])
         for f, nm in enumerate(self.names):
             model.W[nm] = self.W64_d[f].view(-1, k).cpu().numpy().copy()
         model.launches_per_iter = self.launches

@@ -101,3 +101,23 @@ int b200als_host_graph_levels(const int64_t* sptr, const int32_t* sidx, const ui
     }
     return 0;
 }
+
+// float32 [rows, cols] (row stride ld_src elements) -> contiguous float64 [rows, cols]: the public attributes are
+// float64 (scripts/als.py:404-407) while the device holds float32.  Exact; used by the chunked read-back (als.py).
+int b200als_host_widen_f32(const float* src, int64_t ld_src, double* dst, int64_t rows, int64_t cols,
+                           int32_t n_threads) {
+    if (rows < 0 || cols < 0 || ld_src < cols || (rows > 0 && cols > 0 && (!src || !dst))) return -1;
+    if (n_threads < 1) n_threads = 1;
+    const int64_t block = 4096 / (cols > 0 ? cols : 1) + 1;                     // rows per task: at least a page of output
+    const int64_t n_blocks = (rows + block - 1) / block;
+#pragma omp parallel for schedule(static) num_threads(n_threads)
+    for (int64_t b = 0; b < n_blocks; ++b) {
+        const int64_t r1 = (b + 1) * block < rows ? (b + 1) * block : rows;
+        for (int64_t r = b * block; r < r1; ++r) {
+            const float* s = src + r * ld_src;
+            double* d = dst + r * cols;
+            for (int64_t c = 0; c < cols; ++c) d[c] = (double)s[c];
+        }
+    }
+    return 0;
+}

@@ -46,6 +46,11 @@ int b200als_host_dense_to_csr(const void* S, int64_t rows, int64_t cols, int32_t
 int b200als_host_graph_levels(const int64_t* sptr, const int32_t* sidx, const uint8_t* rated, int64_t n,
                               int64_t* level);
 
+/* dst[r, c] = (double)src[r * ld_src + c]: the float64 public copies of the learned float32 arrays
+ * (scripts/als.py:404-407 leave U, V, b_u, b_i as float64).  dst is contiguous [rows, cols]. */
+int b200als_host_widen_f32(const float* src, int64_t ld_src, double* dst, int64_t rows, int64_t cols,
+                           int32_t n_threads);
+
 #ifdef __cplusplus
 }
 #endif

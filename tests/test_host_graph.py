@@ -105,3 +105,23 @@ def test_level_schedule_equals_the_python_loop(monkeypatch):
             nb = sidx[sptr[i]:sptr[i + 1]]
             nb = nb[(nb < i) & rated[nb]]
             assert (level[nb] < level[i]).all()
+
+
+def test_readback_float64_copies(monkeypatch):
+    """readback.f64_from_device == t.double().cpu().numpy() in both modes (CPU tensors stand in for the device)."""
+    import torch
+    from b200als import readback
+    monkeypatch.delenv("B200ALS_READBACK", raising=False)
+    monkeypatch.setattr(readback, "MIN_PIPELINED_ELEMS", 1)
+    g = torch.Generator().manual_seed(0)
+    base = torch.randn(1003, 72, generator=g)
+    for t in (base, base[:901, :64], base[:, 0].contiguous(), base[:5, :3], torch.randn(4096 * 3, generator=g)):
+        want = t.double().numpy()
+        assert np.array_equal(readback.f64_from_device(t), want)                 # default: direct
+        for chunk in (1 << 10, 4096 * 4, 1 << 16, 1 << 24):
+            got = readback.f64_from_device(t, mode="pipelined", chunk_bytes=chunk, n_threads=3)
+            assert got.dtype == np.float64 and got.shape == want.shape and np.array_equal(got, want), (t.shape, chunk)
+    with pytest.raises(ValueError):
+        readback.f64_from_device(base, mode="lazy")
+    monkeypatch.setenv("B200ALS_READBACK", "pipelined")
+    assert np.array_equal(readback.f64_from_device(base), base.double().numpy())
