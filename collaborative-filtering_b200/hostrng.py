@@ -24,10 +24,12 @@ def normal_stream(seed, shapes, dtypes, scale: float, n_threads: int | None = No
     assert all(d in (np.dtype(np.float32), np.dtype(np.float64)) for d in dtypes)
     lib = None if force_numpy else _load()
     rng = np.random.default_rng(seed)
-    if lib is None:
-        return [rng.normal(scale=scale, size=s).astype(d, copy=False) for s, d in zip(shapes, dtypes)]
     st = rng.bit_generator.state
-    assert st["bit_generator"] == "PCG64" and not st["has_uint32"], st
+    # a caller-owned Generator / BitGenerator must be left advanced exactly as numpy would leave it, and only PCG64
+    # has the walk below: both go through numpy itself
+    caller_owned = isinstance(seed, (np.random.Generator, np.random.BitGenerator))
+    if lib is None or caller_owned or st["bit_generator"] != "PCG64" or st["has_uint32"]:
+        return [rng.normal(scale=scale, size=s).astype(d, copy=False) for s, d in zip(shapes, dtypes)]
     state, inc = int(st["state"]["state"]), int(st["state"]["inc"])
     outs = [np.empty(s, dtype=d) for s, d in zip(shapes, dtypes)]
     counts = np.array([o.size for o in outs], dtype=np.int64)

@@ -59,9 +59,18 @@ def test_other_scales_and_all_float64():
 
 def test_generator_object_seed_and_numpy_fallback_agree():
     shapes, dtypes = [(50_000, 4), (30, 4)], [np.float32, np.float64]
-    a = hostrng.normal_stream(np.random.default_rng(11), shapes, dtypes, 0.1, n_threads=4)
+    a = hostrng.normal_stream(11, shapes, dtypes, 0.1, n_threads=4)
     b = hostrng.normal_stream(11, shapes, dtypes, 0.1, force_numpy=True)
     assert all(_same_bits(x, y) for x, y in zip(a, b))
+    # a caller-owned generator is drawn from by numpy itself and is left advanced as the reference leaves it
+    g1, g2 = np.random.default_rng(11), np.random.default_rng(11)
+    c = hostrng.normal_stream(g1, shapes, dtypes, 0.1, n_threads=4)
+    want = _numpy_draw(g2, shapes, dtypes, 0.1)
+    assert all(_same_bits(x, y) for x, y in zip(c, want)) and all(_same_bits(x, y) for x, y in zip(c, a))
+    assert g1.bit_generator.state == g2.bit_generator.state
+    # another bit generator: numpy's own walk
+    d = hostrng.normal_stream(np.random.MT19937(3), [(1000,)], [np.float64], 0.1)
+    assert _same_bits(d[0], np.random.Generator(np.random.MT19937(3)).normal(scale=0.1, size=(1000,)))
 
 
 def test_session_init_uses_the_stream(monkeypatch):
