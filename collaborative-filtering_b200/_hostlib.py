@@ -44,10 +44,11 @@ def load():
     return _lib or None
 
 
-def host_threads() -> int:
+def host_threads(shared: bool = True) -> int:
     """Threads for one host pass: the cores this process may run on (at most 32), shared evenly between the
-    ranks of a node under torchrun (LOCAL_WORLD_SIZE) — every rank makes the same draw at the same time, and an
-    oversubscribed OpenMP team spins at its barriers.  B200ALS_HOST_THREADS overrides."""
+    ranks of a node under torchrun (LOCAL_WORLD_SIZE) when every rank runs the same pass at the same time — an
+    oversubscribed OpenMP team spins at its barriers.  shared=False: the pass runs on one rank only while the
+    others wait for its result.  B200ALS_HOST_THREADS overrides."""
     env = os.environ.get("B200ALS_HOST_THREADS")
     if env:
         return max(1, int(env))
@@ -59,4 +60,4 @@ def host_threads() -> int:
         local_ranks = max(1, int(os.environ.get("LOCAL_WORLD_SIZE", "1")))
     except ValueError:
         local_ranks = 1
-    return max(1, min(n, 32) // local_ranks)
+    return max(1, min(n, 32) // (local_ranks if shared else 1))

@@ -373,16 +373,21 @@ class FitSession:
         W64_d = self.W64_d = [torch.zeros(features[nm].shape[1] * k, dtype=f64, device=dev) for nm in names]
         if init is None:
             # als.py:329, 367-376: default_rng(random_state).normal(scale=0.1, ...) — the same values, drawn on
-            # all host cores (hostrng.py)
-            draws = _hostrng.normal_stream(model.random_state, [(m, k), (n, k)] + [(features[nm].shape[1], k)
-                                                                                  for nm in names],
-                                           [np.float32, np.float32] + [np.float64] * len(names), SCALE_FACTOR)
-            U_d[:m, :k] = torch.from_numpy(draws[0]).to(dev)
-            V_d[:n, :k] = torch.from_numpy(draws[1]).to(dev)
-            for f, nm in enumerate(names):
-                w0 = draws[2 + f]
-                W64_d[f].copy_(torch.from_numpy(w0.reshape(-1)).to(dev))
-                W_d[f][:, :k] = torch.from_numpy(w0.astype(np.float32)).to(dev)
+            # all host cores (hostrng.py).  Sharded: one rank draws with every core and the device arrays are
+            # broadcast, instead of N ranks walking the same stream on 1/N of the cores each.
+            if shard.rank == 0 or not shard.active:
+                draws = _hostrng.normal_stream(model.random_state, [(m, k), (n, k)] + [(features[nm].shape[1], k)
+                                                                                      for nm in names],
+                                               [np.float32, np.float32] + [np.float64] * len(names), SCALE_FACTOR,
+                                               n_threads=_hostrng.host_threads(shared=False))
+                U_d[:m, :k] = torch.from_numpy(draws[0]).to(dev)
+                V_d[:n, :k] = torch.from_numpy(draws[1]).to(dev)
+                for f, nm in enumerate(names):
+                    w0 = draws[2 + f]
+                    W64_d[f].copy_(torch.from_numpy(w0.reshape(-1)).to(dev))
+                    W_d[f][:, :k] = torch.from_numpy(w0.astype(np.float32)).to(dev)
+            for t in [U_d, V_d] + W_d + W64_d:
+                shard.broadcast_from_first(t)
         elif isinstance(init, str) and init == "device":
             g = torch.Generator(device=dev)
             g.manual_seed(int(model.random_state))

@@ -96,6 +96,12 @@ class Shard:
             recv = torch.cat(parts, 0)
         full.index_copy_(0, plan.perm, recv)
 
+    def broadcast_from_first(self, t: torch.Tensor) -> None:
+        """Rank 0 of the group's copy of `t` lands in every replica (initial factors: one draw, not N)."""
+        if self.active:
+            src = 0 if self.group is None else td.get_global_rank(self.group, 0)
+            td.broadcast(t, src=src, group=self.group)
+
     def all_reduce_sum(self, t: torch.Tensor) -> None:
         if self.active:
             td.all_reduce(t, op=td.ReduceOp.SUM, group=self.group)

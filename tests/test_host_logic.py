@@ -203,6 +203,19 @@ for shape in ((s.padded_rows(m), ld), (s.padded_rows(m),)):
         v = rows.to(torch.float32) + 0.25 * r
         want[rows] = v[:, None] if len(shape) == 2 else v
     assert torch.equal(full, want), (full, want)
+# initial factors: rank 0 draws, everyone ends with its arrays (als.py FitSession init)
+import numpy as np
+from b200als import hostrng
+shapes, dts = [(300, 8), (50, 8), (3, 8)], [np.float32, np.float32, np.float64]
+bufs = [torch.zeros(sh, dtype=torch.float32 if d is np.float32 else torch.float64) for sh, d in zip(shapes, dts)]
+if s.rank == 0:
+    for b, a in zip(bufs, hostrng.normal_stream(42, shapes, dts, 0.1, n_threads=hostrng.host_threads(shared=False))):
+        b.copy_(torch.from_numpy(a))
+for b in bufs:
+    s.broadcast_from_first(b)
+rng = np.random.default_rng(42)
+for b, sh, d in zip(bufs, shapes, dts):
+    assert np.array_equal(b.numpy(), rng.normal(scale=0.1, size=sh).astype(d)), s.rank
 acc = torch.tensor([1.0 + s.rank, 10.0], dtype=torch.float64)
 s.all_reduce_sum(acc)
 assert acc.tolist() == [3.0, 20.0]
