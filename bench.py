@@ -17,6 +17,15 @@ dominant kernel's algorithmic bytes / its event-timed duration against the
 measured copy bandwidth; `cpu_baseline` = the oracle port of the reference's
 numpy loop timed on this box's host cores over a bounded row sample.
 `--impl reference` runs only that CPU arm and prints the same line shape.
+
+The default run (c4, one GPU) also carries `secondary`: the other configurations
+north_star states a target on, each a small record of its own — `c3` (k = 64, the
+50 %-of-roofline target), `c4k64`, `c3k96` on the tensor-core path next to
+`c3k96_ffma` (zero-padded tcgen05 against the scalar path), and `c2`: the
+reference's own workload (full model at the bundled shape), timed end to end as
+scripts/evaluate_models.py:245-255 times it, with the oracle port's whole fit on
+the same input beside it.  At N > 1 the line carries `sharded_vs_single`: three
+sharded iterations against three un-sharded ones on rank 0 from the same start.
 """
 from __future__ import annotations
 
@@ -38,18 +47,25 @@ WORKLOADS = {
     # name: (m, n, nnz, k)   — SURVEY.md §8 config shorthand
     "c1": (610, 4980, 100_000, 32),
     "c3": (138_493, 26_744, 20_000_000, 64),
+    "c3k96": (138_493, 26_744, 20_000_000, 96),
     "c4": (480_189, 17_770, 100_000_000, 128),
     "c4k64": (480_189, 17_770, 100_000_000, 64),
     "tiny": (3000, 2000, 200_000, 64),
 }
-# DRAM bytes (read + write) of one row_step launch, from `ncu --set full` on a single GPU; None = not captured.
-# Sources: profiles/r01_ncu_c3_umma_k64_v8.txt, profiles/r01_ncu_c4_umma_k128_v6.txt (at c3 the algorithmic bytes
-# are mostly served by the 126 MB L2; at c4 the item half-step's gathered matrix no longer fits).
-NCU_DRAM_BYTES = {("c3", "user"): 204.5e6, ("c3", "item"): 211.2e6, ("c4", "user"): 1.195e9, ("c4", "item"): 22.23e9}
-WORKLOAD_NAMES = {"c1": "c1_bundled_shape_uv_biases", "c3": "c3_movielens20m_shape",
-                  "c4": "c4_netflix_shape", "c4k64": "c4_netflix_shape_k64", "tiny": "tiny_debug"}
+WORKLOAD_NAMES = {"c1": "c1_bundled_shape_uv_biases", "c3": "c3_movielens20m_shape", "c3k96": "c3_movielens20m_shape_k96",
+                  "c4": "c4_netflix_shape", "c4k64": "c4_netflix_shape_k64", "tiny": "tiny_debug",
+                  "c2": "c2_bundled_shape_full_model", "c5": "c5_powerlaw_10Mx1M_2B"}
 HYPER = dict(lambda_u=5.0, lambda_v=5.0, lambda_bu=3.0, lambda_bi=3.0)
 DATA_SEED = 1234
+
+
+def workload_config(wl):
+    """The `config` object of the JSON line: the same for the B200 arm and the reference arm (what ran how —
+    sharding, Gram path, last train RMSE — goes under `run`)."""
+    m, n, nnz, k = WORKLOADS[wl]
+    return {"workload": WORKLOAD_NAMES[wl], "users": m, "items": n, "ratings": nnz, "k": k,
+            "model": "U/V + biases", "hyper": HYPER,
+            "l2_policy": "inputs larger than L2 (CSR+CSC %.1f GB of ratings walked once per iteration)" % (nnz * 16 / 1e9)}
 
 
 def algorithmic_bytes_half(nnz, rows, k):
@@ -208,41 +224,17 @@ def host_prefix_from_coo(rows, cols, vals, m, n, frac=0.05):
 # --------------------------------------------------------------------------------------
 # B200 arm
 # --------------------------------------------------------------------------------------
-def b200_arm(args):
+def make_cfg(b200als, k, n_iters):
+    return b200als.ALSConfig(core=b200als.CoreConfig(n_factors=k, n_iters=n_iters, lambda_u=HYPER["lambda_u"],
+                                                     lambda_v=HYPER["lambda_v"]),
+                             biases=b200als.BiasesConfig(HYPER["lambda_bu"], HYPER["lambda_bi"]))
+
+
+def timed_iterations(ses, shard, K, W, dev, sampler=None):
+    """W untimed + K timed iterations of a FitSession, bracketed by barrier + synchronize; CUDA events on the
+    launching stream, max over ranks.  Returns (ms total, phase means, launches per iteration, wall t0, t1)."""
     import torch
     import torch.distributed as td
-    import b200als
-    from b200als.sparse import ratings_from_flat
-    from b200als.synth import synth_ratings_torch
-
-    world = int(os.environ.get("WORLD_SIZE", "1"))
-    rank = int(os.environ.get("RANK", "0"))
-    local = int(os.environ.get("LOCAL_RANK", "0"))
-    if args.gpus != world and world > 1:
-        raise SystemExit(f"--gpus {args.gpus} but WORLD_SIZE={world}")
-    torch.cuda.set_device(local)
-    dev = torch.device("cuda", local)
-    if world > 1:
-        td.init_process_group("nccl", device_id=dev)
-    b200als._lib.require_device()
-    shard = b200als.Shard.from_env()
-    wl = args.workload
-    m, n, nnz, k = WORKLOADS[wl]
-    K, W = args.steps, args.warmup
-
-    rows, cols, vals = synth_ratings_torch(m, n, nnz, seed=DATA_SEED, device=dev)
-    flat = rows * n + cols
-    cfg = b200als.ALSConfig(core=b200als.CoreConfig(n_factors=k, n_iters=W + K, lambda_u=HYPER["lambda_u"],
-                                                    lambda_v=HYPER["lambda_v"]),
-                            biases=b200als.BiasesConfig(HYPER["lambda_bu"], HYPER["lambda_bi"]))
-
-    # ---- resident arm: ratings already in HBM ---------------------------------------
-    rt = ratings_from_flat(flat, vals, (m, n), dev, sorted_input=True)
-    model = b200als.ALS(cfg)
-    model.shard = shard
-    model.gram_path = {"auto": 0, "ffma": 1, "umma": 2}[args.path]
-    mu0 = float(vals.sum(dtype=torch.float64).item() / nnz)
-    ses = model.session(rt, mu0, init="device", profile=True)
     for it in range(W):
         ses.iteration(it)
     torch.cuda.synchronize()
@@ -250,8 +242,7 @@ def b200_arm(args):
     for p in ses.phase_ms:
         ses.phase_ms[p] = []
     shard.barrier()
-    sampler = ClockSampler(local)
-    if rank == 0:
+    if sampler is not None:
         sampler.start()
         time.sleep(0.25)
     e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
@@ -266,81 +257,273 @@ def b200_arm(args):
     shard.barrier()
     t1 = time.perf_counter()
     ms = e0.elapsed_time(e1)
-    clocks = sampler.stop(t0, t1) if rank == 0 else None
-    launches = ses.launches * K
     phases = {p: (float(np.mean(v)) if v else 0.0) for p, v in ses.collect_phase_times().items()}
-    hist = ses.read_history(W + K)
     tms = torch.tensor([ms], dtype=torch.float64, device=dev)
-    if world > 1:
+    if shard.active:
         td.all_reduce(tms, op=td.ReduceOp.MAX)
-    ms = float(tms.item())
-    ms_per_step = ms / K
-    value = nnz / (ms_per_step * 1e-3)
-    rmse_last = float(hist[-1, 0])
-    del ses
+    return float(tms.item()), phases, ses.launches, t0, t1
 
-    # ---- end-to-end arm: public fit_coo with pinned HOST buffers ----------------------
-    flat_h = flat.cpu().pin_memory()
-    vals_h = vals.cpu().pin_memory()
-    del rows, cols, flat, vals, rt
-    torch.cuda.empty_cache()
-    cfg_e = b200als.ALSConfig(core=b200als.CoreConfig(n_factors=k, n_iters=K, lambda_u=HYPER["lambda_u"],
-                                                      lambda_v=HYPER["lambda_v"]),
-                              biases=b200als.BiasesConfig(HYPER["lambda_bu"], HYPER["lambda_bi"]))
-    m2 = b200als.ALS(cfg_e)
-    m2.shard = shard
-    m2.gram_path = model.gram_path
-    shard.barrier()
-    torch.cuda.synchronize()
-    t0 = time.perf_counter()
-    m2.fit_coo(flat_h, vals_h, (m, n), tol=None, verbose=0, sorted_input=True)
-    torch.cuda.synchronize()
-    te = time.perf_counter() - t0
-    tet = torch.tensor([te], dtype=torch.float64, device=dev)
-    if world > 1:
-        td.all_reduce(tet, op=td.ReduceOp.MAX)
-    te = float(tet.item())
-    e2e_value = nnz * K / te
-    h2d = (nnz * 12 + (m + n) * k * 4) / K
-    d2h = ((m + n) * (k + 1) * 8 + K * 48) / K
 
-    if rank != 0:
-        if world > 1:
-            td.destroy_process_group()
-        return
+def roofline_of(wl_shape, world, phases, ms_per_step):
+    m, n, nnz, k = wl_shape
     peak, peak_kind = measured_peaks()
-    # dominant kernel = the slower of the two half-step launches (same kernel, two data sets)
     rows_u, rows_i = (m + world - 1) // world, (n + world - 1) // world
     cand = {"user": algorithmic_bytes_half(nnz / world, rows_u, k), "item": algorithmic_bytes_half(nnz / world, rows_i, k)}
     dom = max(("user", "item"), key=lambda p: phases[p])
     ach = cand[dom] / (phases[dom] * 1e-3) / 1e9 if phases[dom] > 0 else 0.0
     b_iter = cand["user"] + cand["item"]
-    # dram__bytes_read.sum + dram__bytes_write.sum of that launch from one `ncu --set full` capture (profiles/)
-    traffic = NCU_DRAM_BYTES.get((wl, dom)) if world == 1 and args.path == "auto" else None
+    return {"bound": "hbm", "kernel": f"row_step ({dom} half-step)", "achieved": ach, "peak": peak,
+            "unit": "GB/s", "frac": ach / peak,
+            # dram__bytes of the launch is an ncu quantity; this run did not measure it (see profiles/ for captures)
+            "traffic": None, "peak_source": peak_kind,
+            "algorithmic_bytes_per_launch": cand[dom],
+            "half_step_frac": {p: (cand[p] / (phases[p] * 1e-3) / 1e9 / peak if phases[p] > 0 else None)
+                               for p in ("user", "item")},
+            "iteration_frac": b_iter / (ms_per_step * 1e-3) / 1e9 / peak}
+
+
+def resident_run(b200als, wl_shape, K, W, shard, path, dev, sampler=None, keep=False):
+    """Synthetic ratings of the shape generated on the device, CSR/CSC built, K timed iterations."""
+    import torch
+    from b200als.sparse import ratings_from_flat
+    from b200als.synth import synth_ratings_torch
+    m, n, nnz, k = wl_shape
+    rows, cols, vals = synth_ratings_torch(m, n, nnz, seed=DATA_SEED, device=dev)
+    flat = rows * n + cols
+    del rows, cols
+    rt = ratings_from_flat(flat, vals, (m, n), dev, sorted_input=True)
+    model = b200als.ALS(make_cfg(b200als, k, W + K))
+    model.shard = shard
+    model.gram_path = path
+    mu0 = float(vals.sum(dtype=torch.float64).item() / nnz)
+    ses = model.session(rt, mu0, init="device", profile=True)
+    ms, phases, launches, t0, t1 = timed_iterations(ses, shard, K, W, dev, sampler)
+    hist = ses.read_history(W + K)
+    paths = dict(model.last_paths)
+    out = dict(ms=ms, ms_per_step=ms / K, phases=phases, launches=launches, t0=t0, t1=t1,
+               rmse_last=float(hist[-1, 0]), paths=paths, fused_exchange=bool(getattr(ses, "peers", None)))
+    if keep:
+        out.update(flat=flat, vals=vals, rt=rt, mu0=mu0)
+    del ses
+    return out
+
+
+def sharded_vs_single(b200als, rt, mu0, k, shard, path, dev, iters=3):
+    """Parity of the sharded fit: `iters` sharded iterations on all ranks next to `iters` un-sharded ones on rank 0,
+    same start.  Max relative difference (Frobenius) of U, V, b_u, b_i and the largest |d train RMSE|."""
+    import torch
+
+    def run(sh):
+        model = b200als.ALS(make_cfg(b200als, k, iters))
+        model.shard = sh
+        model.gram_path = path
+        ses = model.session(rt, mu0, init="device")
+        for it in range(iters):
+            ses.iteration(it)
+        torch.cuda.synchronize()
+        return ses, ses.read_history(iters)
+
+    ses_s, hist_s = run(shard)
+    shard.barrier()
+    out = None
+    if shard.rank == 0:
+        ses_1, hist_1 = run(b200als.Shard())
+        m, n = rt.m, rt.n
+
+        def rel(a, b):
+            return float((a.double() - b.double()).norm() / b.double().norm().clamp_min(1e-300))
+        out = {"iterations": iters,
+               "U": rel(ses_s.U_d[:m], ses_1.U_d[:m]), "V": rel(ses_s.V_d[:n], ses_1.V_d[:n]),
+               "b_u": rel(ses_s.b_u_d[:m], ses_1.b_u_d[:m]), "b_i": rel(ses_s.b_i_d[:n], ses_1.b_i_d[:n]),
+               "train_rmse_abs": float(np.abs(hist_s[:, 0] - hist_1[:, 0]).max()),
+               "train_rmse_sharded": [float(x) for x in hist_s[:, 0]],
+               "train_rmse_single": [float(x) for x in hist_1[:, 0]]}
+        del ses_1
+    shard.barrier()
+    del ses_s
+    return out
+
+
+def e2e_run(b200als, wl_shape, flat_h, vals_h, K, shard, path, dev):
+    """The public call on pinned HOST buffers: H2D, CSR/CSC build, host RNG init, K iterations, and (rank 0) the
+    float64 D2H of U, V, b_u, b_i — all inside the timed region.  Max over ranks."""
+    import torch
+    import torch.distributed as td
+    m, n, nnz, k = wl_shape
+    m2 = b200als.ALS(make_cfg(b200als, k, K))
+    m2.shard = shard
+    m2.gram_path = path
+    shard.barrier()
+    torch.cuda.synchronize()
+    t0 = time.perf_counter()
+    m2.fit_coo(flat_h, vals_h, (m, n), tol=None, verbose=0, sorted_input=True)
+    if shard.rank == 0:
+        got = (m2.U, m2.V, m2.b_u, m2.b_i)           # the model is read back once, on rank 0 (every rank holds a replica)
+        assert got[0].shape == (m, k) and got[0].dtype == np.float64
+    torch.cuda.synchronize()
+    te = time.perf_counter() - t0
+    tet = torch.tensor([te], dtype=torch.float64, device=dev)
+    if shard.active:
+        td.all_reduce(tet, op=td.ReduceOp.MAX)
+    te = float(tet.item())
+    return {"value": nnz * K / te, "unit": "ratings/s",
+            "h2d_bytes_per_step": (nnz * 12 + (m + n) * k * 4) / K,
+            "d2h_bytes_per_step": ((m + n) * (k + 1) * 4 + K * 48) / K,
+            "seconds_total": te, "iterations": K,
+            "what": "ALS.fit_coo(pinned host flat_idx+vals) incl. H2D, CSR/CSC build, host RNG init, K iterations, "
+                    "float32 D2H of U,V,b_u,b_i widened to the public float64 attributes (rank 0)"}
+
+
+def c2_run(b200als, dev, n_iters, with_cpu=True):
+    """C2: the reference's own workload — full model (biases + genres/years W_f + inverse_sqrt popularity + genres
+    Laplacian, hyper-parameters of scripts/als.py:48-67) at the bundled shape, timed end to end exactly as
+    scripts/evaluate_models.py:245-255 does: construct + fit(dense R) + dense predict."""
+    import torch
+    sys.path.insert(0, os.path.join(REPO, "tests"))
+    from _util import bundled_features, load_case
+    c = load_case("c2_full")
+    feats = bundled_features()
+    R = np.full(c.m * c.n, np.nan)
+    R[c.flat] = c.vals
+    R = R.reshape(c.m, c.n)
+    cfgd = dict(c.cfgd, core=dict(c.cfgd["core"], n_iters=n_iters))
+
+    def mk(mod):
+        sim = mod.GraphSimConfig(**cfgd["sim"])
+        return mod.ALSConfig(core=mod.CoreConfig(**cfgd["core"]), biases=mod.BiasesConfig(**cfgd["biases"]),
+                             graph=mod.GraphConfig(alpha=cfgd["alpha"], sim=sim))
+
+    def one():
+        torch.cuda.synchronize()
+        t0 = time.perf_counter()
+        model = b200als.ALS(config=mk(b200als), lambda_w=c.lambda_w)
+        model.fit(R, features=feats, tol=None, verbose=0)
+        pred = model.predict(feats)
+        dt = time.perf_counter() - t0
+        return dt, model, pred
+
+    one()                                            # warm-up (context, module load)
+    times = []
+    for _ in range(3):
+        dt, model, pred = one()
+        times.append(dt)
+    # per-phase device times of the same fit
+    from b200als.sparse import ratings_from_dense
+    rt = ratings_from_dense(R, dev)
+    m2 = b200als.ALS(config=mk(b200als), lambda_w=c.lambda_w)
+    ts = time.perf_counter()
+    ses = m2.session(rt, float(np.nanmean(R)), feats, None, profile=True)
+    setup_s = time.perf_counter() - ts
+    for it in range(n_iters):
+        ses.iteration(it)
+    torch.cuda.synchronize()
+    ph = {p: (float(np.sum(v)) if v else 0.0) for p, v in ses.collect_phase_times().items()}
+    nnz = int(c.flat.size)
+    t = float(np.median(times))
+    out = {"workload": WORKLOAD_NAMES["c2"], "users": c.m, "items": c.n, "ratings": nnz, "k": cfgd["core"]["n_factors"],
+           "iterations": n_iters, "model": "biases + W_f(genres, years) + inverse_sqrt + genres Laplacian (alpha 0.5, topk 50)",
+           "seconds_fit_predict": t, "seconds_all": times, "value": nnz * n_iters / t, "unit": "ratings/s",
+           "timed_like": "scripts/evaluate_models.py:245-255 (construct + fit(dense R, features) + dense predict)",
+           "phase_ms_total": ph, "session_setup_s": setup_s, "timings": dict(m2.timings),
+           "graph_levels": int(ses.level_ptr.size - 1) if ses.use_graph else 0,
+           "launches_per_iteration": int(ses.launches), "train_rmse_last": float(model.history["train_rmse"][-1])}
+    del ses
+    if with_cpu:
+        sys.path.insert(0, os.path.join(REPO, "oracle"))
+        import als_oracle
+        t0 = time.perf_counter()
+        o = als_oracle.SparseALSOracle(mk(b200als), c.lambda_w)
+        o.fit(R, feats, tol=None)
+        po = o.predict(feats)
+        tc = time.perf_counter() - t0
+        cores = len(os.sched_getaffinity(0)) if hasattr(os, "sched_getaffinity") else (os.cpu_count() or 1)
+        out["cpu_baseline"] = {"value": nnz * n_iters / tc, "unit": "ratings/s", "seconds_fit_predict": tc, "cores": cores,
+                               "kind": "port", "sample": "the whole fit + predict on the same input (no sampling)"}
+        out["max_abs_pred_diff_vs_port"] = float(np.abs(pred - po).max())
+        out["train_rmse_last_port"] = float(o.history["train_rmse"][-1])
+    return out
+
+
+def b200_arm(args):
+    import torch
+    import torch.distributed as td
+    import b200als
+
+    world = int(os.environ.get("WORLD_SIZE", "1"))
+    rank = int(os.environ.get("RANK", "0"))
+    local = int(os.environ.get("LOCAL_RANK", "0"))
+    if args.gpus != world and world > 1:
+        raise SystemExit(f"--gpus {args.gpus} but WORLD_SIZE={world}")
+    torch.cuda.set_device(local)
+    dev = torch.device("cuda", local)
+    if world > 1:
+        td.init_process_group("nccl", device_id=dev)
+    b200als._lib.require_device()
+    shard = b200als.Shard.from_env()
+    wl = args.workload
+    shape = WORKLOADS[wl]
+    m, n, nnz, k = shape
+    K, W = args.steps, args.warmup
+    path = {"auto": 0, "ffma": 1, "umma": 2}[args.path]
+
+    # ---- resident arm: ratings already in HBM ---------------------------------------
+    sampler = ClockSampler(local) if rank == 0 else None
+    res = resident_run(b200als, shape, K, W, shard, path, dev, sampler, keep=True)
+    clocks = sampler.stop(res["t0"], res["t1"]) if rank == 0 else None
+    ms_per_step = res["ms_per_step"]
+    value = nnz / (ms_per_step * 1e-3)
+
+    svs = None
+    if world > 1 and not args.no_parity:
+        svs = sharded_vs_single(b200als, res["rt"], res["mu0"], k, shard, path, dev)
+
+    # ---- end-to-end arm: public fit_coo with pinned HOST buffers ----------------------
+    flat_h = res.pop("flat").cpu().pin_memory()
+    vals_h = res.pop("vals").cpu().pin_memory()
+    res.pop("rt")
+    torch.cuda.empty_cache()
+    e2e = e2e_run(b200als, shape, flat_h, vals_h, K, shard, path, dev)
+    del flat_h, vals_h
+
+    if rank != 0:
+        if world > 1:
+            td.destroy_process_group()
+        return
     out = {
         "metric": "ALS ratings/sec/iter (= nnz x ALS iterations/sec)", "value": value, "unit": "ratings/s",
         "iterations_per_sec": 1e3 / ms_per_step,
         "n_gpus": world, "steps": K, "warmup": W, "ms_per_step": ms_per_step, "higher_is_better": True,
         "scaling": "strong", "vs_baseline": None, "dtype": "f32", "data": "synthetic",
-        "config": {"workload": WORKLOAD_NAMES[wl], "users": m, "items": n, "ratings": nnz, "k": k,
-                   "model": "U/V + biases", "hyper": HYPER, "sharding": f"rows/{world}",
-                   "l2_policy": "inputs larger than L2 (CSR+CSC %.1f GB)" % (nnz * 16 / 1e9),
-                   "gram_path": args.path, "train_rmse_last": rmse_last},
+        "config": workload_config(wl),
+        "run": {"sharding": f"rows/{world}", "gram_path": args.path, "paths_taken": res["paths"],
+                "exchange": ("fused peer stores" if res["fused_exchange"] else ("all-gather" if world > 1 else "none")),
+                "train_rmse_last": res["rmse_last"]},
         "clocks": clocks,
-        "e2e": {"value": e2e_value, "unit": "ratings/s", "h2d_bytes_per_step": h2d, "d2h_bytes_per_step": d2h,
-                "seconds_total": te, "iterations": K,
-                "what": "ALS.fit_coo(pinned host flat_idx+vals) incl. H2D, CSR/CSC build, host RNG init, "
-                        "K iterations, D2H of U,V,b_u,b_i"},
-        "gpu_launches": int(launches),
-        "roofline": {"bound": "hbm", "kernel": f"row_step ({dom} half-step)", "achieved": ach, "peak": peak,
-                     "unit": "GB/s", "frac": ach / peak, "traffic": traffic, "peak_source": peak_kind,
-                     "algorithmic_bytes_per_launch": cand[dom],
-                     "iteration_frac": b_iter / (ms_per_step * 1e-3) / 1e9 / peak},
-        "phase_ms": phases,
+        "e2e": e2e,
+        "gpu_launches": int(res["launches"] * K),
+        "roofline": roofline_of(shape, world, res["phases"], ms_per_step),
+        "phase_ms": res["phases"],
     }
+    if svs is not None:
+        out["sharded_vs_single"] = svs
     if world == 1 and not args.no_cpu:
         v, t, info = cpu_reference_arm(wl, steps=2, warmup=1, budget_s=args.cpu_budget)
         out["cpu_baseline"] = dict(value=v, **info)
+    if world == 1 and wl == "c4" and not args.no_secondary:
+        # the other configurations north_star states a target on, each as its own small record
+        sec = {}
+        torch.cuda.empty_cache()
+        for name, p2 in (("c3", path), ("c4k64", path), ("c3k96", path), ("c3k96_ffma", 1)):
+            shp = WORKLOADS[name.split("_")[0]]
+            r2 = resident_run(b200als, shp, K, W, shard, p2, dev)
+            sec[name] = {"workload": WORKLOAD_NAMES[name.split("_")[0]], "users": shp[0], "items": shp[1], "ratings": shp[2],
+                         "k": shp[3], "ms_per_step": r2["ms_per_step"], "value": shp[2] / (r2["ms_per_step"] * 1e-3),
+                         "unit": "ratings/s", "phase_ms": r2["phases"], "paths_taken": r2["paths"],
+                         "roofline": roofline_of(shp, 1, r2["phases"], r2["ms_per_step"]),
+                         "train_rmse_last": r2["rmse_last"]}
+            torch.cuda.empty_cache()
+        sec["c2"] = c2_run(b200als, dev, args.c2_iters, with_cpu=not args.no_cpu)
+        out["secondary"] = sec
     print(json.dumps(out), flush=True)
     if world > 1:
         td.destroy_process_group()
@@ -360,8 +543,8 @@ def reference_arm(args):
         "n_gpus": int(os.environ.get("WORLD_SIZE", "1")), "steps": args.steps, "warmup": args.warmup,
         "ms_per_step": t * 1e3, "higher_is_better": True, "scaling": "strong", "vs_baseline": None,
         "dtype": "f64", "data": "synthetic",
-        "config": {"workload": WORKLOAD_NAMES[wl], "users": m, "items": n, "ratings": nnz, "k": k,
-                   "model": "U/V + biases", "hyper": HYPER},
+        "config": workload_config(wl),
+        "ms_per_full_iteration_extrapolated": nnz / v * 1e3,
         "cpu_baseline": dict(value=v, **info),
         "e2e": {"value": v, "unit": "ratings/s", "h2d_bytes_per_step": 0, "d2h_bytes_per_step": 0},
         "gpu_launches": 0,
@@ -377,7 +560,10 @@ def main():
     ap.add_argument("--impl", default="b200", choices=["b200", "reference"])
     ap.add_argument("--workload", default="c4", choices=sorted(WORKLOADS))
     ap.add_argument("--path", default="auto", choices=["auto", "ffma", "umma"])
-    ap.add_argument("--no-cpu", action="store_true", help="skip the cpu_baseline leg")
+    ap.add_argument("--no-cpu", action="store_true", help="skip the cpu_baseline legs")
+    ap.add_argument("--no-secondary", action="store_true", help="skip the c3 / c4k64 / c3k96 / c2 records of the default run")
+    ap.add_argument("--no-parity", action="store_true", help="N > 1: skip the sharded_vs_single check")
+    ap.add_argument("--c2-iters", type=int, default=20, help="iterations of the c2 record (scripts/als.py:52 uses 20)")
     ap.add_argument("--cpu-budget", type=float, default=15.0)
     ap.add_argument("--ref-budget", type=float, default=90.0)
     args = ap.parse_args()

@@ -10,10 +10,11 @@ import os
 
 _HERE = os.path.dirname(os.path.abspath(__file__))
 LIB_PATH = os.path.join(_HERE, "libb200als.so")
-ABI_VERSION = 7
+ABI_VERSION = 8
 MAX_K = 160
 MAX_FEATURES = 8
 STATUS_WORDS = 4
+MAX_PEERS = 7
 
 STEP_SOLVE, STEP_FACTOR = 0, 1
 PATH_AUTO, PATH_FFMA, PATH_UMMA = 0, 1, 2
@@ -52,6 +53,8 @@ class StepArgs(C.Structure):
         ("status", vp), ("stats_acc", vp), ("norm_acc", vp),
         ("split", vp),
         ("workspace", vp), ("workspace_bytes", C.c_size_t),
+        ("row_ids", vp), ("n_peers", C.c_int32), ("reserved0", C.c_int32),
+        ("peer_X", vp * MAX_PEERS), ("peer_bias", vp * MAX_PEERS),
     ]
 
 
@@ -60,12 +63,14 @@ _SIGNATURES = {
     "b200als_abi_version": [],
     "b200als_last_error": [],
     "b200als_device_ok": [],
+    "b200als_peer_enable": [C.c_int32],
     "b200als_last_launch_count": [],
+    "b200als_last_path": [],
     "b200als_dense_indptr": [vp, C.c_int64, C.c_int64, vp, vp, vp],
     "b200als_dense_fill": [vp, C.c_int64, C.c_int64, vp, vp, vp, vp, vp, vp, vp, vp],
     "b200als_coo_workspace_bytes": [C.c_int64, C.c_int64, C.c_int64, C.POINTER(C.c_size_t)],
     "b200als_coo_to_csr_csc": [vp, vp, C.c_int64, C.c_int64, C.c_int64, C.c_int,
-                               vp, vp, vp, vp, vp, vp, vp, vp, C.c_size_t, vp],
+                               vp, vp, vp, vp, vp, vp, vp, vp, C.c_size_t, vp, vp],
     "b200als_row_order_workspace_bytes": [C.c_int64, C.POINTER(C.c_size_t)],
     "b200als_row_order": [vp, C.c_int64, vp, vp, vp, C.c_size_t, vp],
     "b200als_compose_z": [vp, C.c_int64, C.c_int64, C.c_int32, C.c_int32,

@@ -18,6 +18,8 @@ from __future__ import annotations
 
 import ctypes as C
 import logging
+import os
+import time
 
 import numpy as np
 import torch
@@ -36,6 +38,26 @@ logger = logging.getLogger(__name__)
 
 def _round4(k: int) -> int:
     return (k + 3) & ~3
+
+
+def factor_ld(k: int, gram_path: int) -> int:
+    """Row stride (floats) of the device factor matrices.  The tcgen05 half-step exists for widths 64 and 128
+    and covers every k in (32, 128] by zero padding (include/b200als.h): rows are then exactly 64 / 128 floats
+    with zeros behind column k.  Other k (<= 32: a 64-wide tensor-core tile would be mostly padding; 129..160)
+    take the FFMA path with 16-byte aligned rows."""
+    if gram_path != _lib.PATH_FFMA:
+        if 32 < k <= 64 or (gram_path == _lib.PATH_UMMA and k <= 64):
+            return 64
+        if 64 < k <= 128:
+            return 128
+    return _round4(k)
+
+
+def _env_int(name: str, default: int) -> int:
+    try:
+        return int(os.environ.get(name, default))
+    except ValueError:
+        return default
 
 
 class ALS:
@@ -64,10 +86,10 @@ class ALS:
         self.S_topk = sim.topk if sim is not None else None
         self.S_eps = sim.eps if sim is not None else EPS
 
-        self.U: np.ndarray | None = None
-        self.V: np.ndarray | None = None
-        self.b_u: np.ndarray | None = None
-        self.b_i: np.ndarray | None = None
+        # U, V, b_u, b_i (als.py:176-179) are properties: float64 numpy arrays like the reference's, copied from
+        # the device on first read after a fit (see `_host` / `_dev_model` below)
+        self._host: dict[str, np.ndarray | None] = {"U": None, "V": None, "b_u": None, "b_i": None}
+        self._dev_model: dict | None = None    # device-resident float32 model of the last fit
         self.mu: float = 0.0
         self.S: np.ndarray | None = None
         self.history: dict[str, list[float]] = {
@@ -76,11 +98,46 @@ class ALS:
         # build-side knobs (not part of the reference surface)
         self.device = None                 # torch device; default: current CUDA device
         self.gram_path = _lib.PATH_AUTO    # PATH_FFMA / PATH_UMMA force one Gram path
-        self.split_rows = 0                # tcgen05 path: cut rows longer than this into pieces (0: default, <0: never)
-        self.split_piece = 0               # ratings per piece (0: split_rows / 2)
+        # tcgen05 path: rows longer than split_rows are cut into pieces of split_piece ratings (0: the library's
+        # absolute defaults, include/b200als.h; < 0: never)
+        self.split_rows = _env_int("B200ALS_SPLIT_ROWS", 0)
+        self.split_piece = _env_int("B200ALS_SPLIT_PIECE", 0)
         self.shard: Shard | None = None    # row sharding across ranks (dist.Shard)
         self.timings: dict[str, float] = {}
         self.launches_per_iter: int = 0
+        self.last_paths: dict[str, int] = {}   # Gram path the last iteration's half-steps took (PATH_FFMA / PATH_UMMA)
+
+    # ---- learned parameters: float64 numpy on the host, fetched lazily -------------------------------
+    # The fit leaves the model in HBM.  predict / predict_pairs / sse_on_flat read it there, and the float64
+    # host copies the reference exposes (als.py:404-407) are made when an attribute is first read: a driver that
+    # only calls predict() after fit() (tune_params.py:376-392, evaluate_models.py:246-265) never pays for them.
+    # Once an attribute has been read (the caller may edit the array in place) or assigned, the host arrays are
+    # authoritative again and predictions upload them, as before.
+    def _get_param(self, name: str):
+        v = self._host[name]
+        if v is None and self._dev_model is not None:
+            d = self._dev_model
+            t = {"U": d["U"][:d["m"], :d["k"]], "V": d["V"][:d["n"], :d["k"]],
+                 "b_u": d["b_u"][:d["m"]], "b_i": d["b_i"][:d["n"]]}[name]
+            with torch.cuda.device(t.device):
+                v = _readback.f64_from_device(t)
+            self._host[name] = v
+            d["host_touched"] = True
+        return v
+
+    def _set_param(self, name: str, value) -> None:
+        self._host[name] = value
+        if self._dev_model is not None:
+            self._dev_model["host_touched"] = True
+
+    U = property(lambda self: self._get_param("U"), lambda self, v: self._set_param("U", v))
+    V = property(lambda self: self._get_param("V"), lambda self, v: self._set_param("V", v))
+    b_u = property(lambda self: self._get_param("b_u"), lambda self, v: self._set_param("b_u", v))
+    b_i = property(lambda self: self._get_param("b_i"), lambda self, v: self._set_param("b_i", v))
+
+    @property
+    def fitted(self) -> bool:
+        return self._dev_model is not None or (self._host["U"] is not None and self._host["V"] is not None)
 
     # ------------------------------------------------------------------ helpers
     def _item_reg(self, counts: np.ndarray) -> np.ndarray:
@@ -107,6 +164,11 @@ class ALS:
                                  f"Expected number of rows: {n}.")
             if not np.isfinite(X).all():
                 raise ValueError(f"Feature '{name}' contains infinite values.")
+
+    def _n_items(self) -> int:
+        if self._host["V"] is not None:
+            return int(self._host["V"].shape[0])
+        return int(self._dev_model["n"])
 
     def _dev(self):
         if self.device is not None:
@@ -165,6 +227,9 @@ class ALS:
     def _fit_ratings(self, rt: Ratings, mu0, features, tol, min_iters, verbose, init) -> "ALS":
         if verbose == 0:
             logging.disable(logging.CRITICAL)          # als.py:325-326 (global, as in the reference)
+        # history is created once per object and every fit() appends to it (als.py:185-191, 510-517): a second fit
+        # on the same object continues the lists, and _converged() looks at the combined list
+        self._hist_prefix = {key: list(v) for key, v in self.history.items()}
         ses = FitSession(self, rt, mu0, features, init, False)
         n_iters = int(self.n_iters)
         if verbose > 0:
@@ -192,24 +257,43 @@ class ALS:
 
     def _set_history(self, h: np.ndarray) -> None:
         keys = ("train_rmse", "U_norm", "V_norm", "bu_norm", "bi_norm")
+        prefix = getattr(self, "_hist_prefix", None) or {}
         for j, key in enumerate(keys):
-            self.history[key] = [float(x) for x in h[:, j]]
+            self.history[key] = list(prefix.get(key, [])) + [float(x) for x in h[:, j]]
 
     # ------------------------------------------------------------------ predict
+    def _resident_model(self, dev):
+        """The device-resident model of the last fit, if it still is what the public attributes say."""
+        d = self._dev_model
+        if d is None or d.get("host_touched") or d["U"].device != dev:
+            return None
+        if float(self.mu) != d["mu_value"] or set(self.W) != set(d["W"]):
+            return None
+        if any(self.W[nm] is not d["W_host"][nm] for nm in d["W"]):
+            return None
+        return d
+
     def _upload_model(self, features, dev):
-        """Public attributes (float64 numpy, possibly edited by the caller) → device float32."""
+        """Device float32 model for predict / predict_pairs / sse_on_flat: the arrays the fit left in HBM, or —
+        when the caller has read or assigned U, V, b_u, b_i, mu, W since — an upload of the public attributes."""
         lib = _lib.load()
-        m, k = self.U.shape
-        n = self.V.shape[0]
-        ld = _round4(k)
         f32 = torch.float32
-        U_d = torch.zeros(m, ld, dtype=f32, device=dev)
-        V_d = torch.zeros(n, ld, dtype=f32, device=dev)
-        U_d[:, :k] = torch.from_numpy(np.asarray(self.U, dtype=np.float32)).to(dev)
-        V_d[:, :k] = torch.from_numpy(np.asarray(self.V, dtype=np.float32)).to(dev)
-        b_u_d = torch.from_numpy(np.asarray(self.b_u, dtype=np.float32)).to(dev)
-        b_i_d = torch.from_numpy(np.asarray(self.b_i, dtype=np.float32)).to(dev)
-        mu_d = torch.full((1,), float(self.mu), dtype=f32, device=dev)
+        res = self._resident_model(dev)
+        if res is not None:
+            m, n, k, ld = res["m"], res["n"], res["k"], res["ld"]
+            U_d, V_d, b_u_d, b_i_d, mu_d = res["U"], res["V"], res["b_u"], res["b_i"], res["mu"]
+        else:
+            U, V = self.U, self.V
+            m, k = U.shape
+            n = V.shape[0]
+            ld = _round4(k)
+            U_d = torch.zeros(m, ld, dtype=f32, device=dev)
+            V_d = torch.zeros(n, ld, dtype=f32, device=dev)
+            U_d[:, :k] = torch.from_numpy(np.asarray(U, dtype=np.float32)).to(dev)
+            V_d[:, :k] = torch.from_numpy(np.asarray(V, dtype=np.float32)).to(dev)
+            b_u_d = torch.from_numpy(np.asarray(self.b_u, dtype=np.float32)).to(dev)
+            b_i_d = torch.from_numpy(np.asarray(self.b_i, dtype=np.float32)).to(dev)
+            mu_d = torch.full((1,), float(self.mu), dtype=f32, device=dev)
         used = [(nm, X) for nm, X in features.items() if self.W.get(nm) is not None]   # als.py:569-572
         if len(used) > _lib.MAX_FEATURES:
             raise ValueError(f"at most {_lib.MAX_FEATURES} feature matrices are supported")
@@ -217,13 +301,16 @@ class ALS:
             X_d = [torch.from_numpy(np.ascontiguousarray(X, dtype=np.float32)).to(dev) for _, X in used]
             W_d = []
             for nm, X in used:
+                if res is not None:
+                    W_d.append(res["W"][nm])
+                    continue
                 w = torch.zeros(X.shape[1], ld, dtype=f32, device=dev)
                 w[:, :k] = torch.from_numpy(np.asarray(self.W[nm], dtype=np.float32)).to(dev)
                 W_d.append(w)
             xptr = (C.c_void_p * len(used))(*[x.data_ptr() for x in X_d])
             wptr = (C.c_void_p * len(used))(*[w.data_ptr() for w in W_d])
             dims = (C.c_int32 * len(used))(*[int(x.shape[1]) for x in X_d])
-            Z_d = torch.empty(n, ld, dtype=f32, device=dev)
+            Z_d = torch.empty(V_d.shape[0], ld, dtype=f32, device=dev)
             check(lib.b200als_compose_z(ptr(V_d), ld, n, k, len(used), xptr, dims, wptr, ld, -1, ptr(Z_d), ld,
                                         torch.cuda.current_stream().cuda_stream), "compose_z")
             torch.cuda.current_stream().synchronize()
@@ -233,10 +320,10 @@ class ALS:
 
     def predict(self, features: dict[str, np.ndarray] | None = None) -> np.ndarray:
         """Completed (m, n) float64 matrix  U Zᵀ + μ + b_u + b_i  (als.py:532-574)."""
-        if self.U is None or self.V is None:
+        if not self.fitted:
             raise RuntimeError("Model must be fitted before prediction.")
         features = features or {}
-        self._check_features(features, self.V.shape[0], "predict")      # als.py:558-565
+        self._check_features(features, self._n_items(), "predict")      # als.py:558-565
         lib = _lib.load()
         _lib.require_device()
         dev = self._dev()
@@ -251,10 +338,10 @@ class ALS:
     def predict_pairs(self, rows, cols, features: dict[str, np.ndarray] | None = None) -> np.ndarray:
         """Entries of `predict(features)` at (rows, cols) — `R_pred.ravel()[u*n+i]` of
         tune_params.py:165-167 without the dense matrix.  Returns float64."""
-        if self.U is None or self.V is None:
+        if not self.fitted:
             raise RuntimeError("Model must be fitted before prediction.")
         features = features or {}
-        self._check_features(features, self.V.shape[0], "predict")
+        self._check_features(features, self._n_items(), "predict")
         lib = _lib.load()
         _lib.require_device()
         dev = self._dev()
@@ -274,10 +361,10 @@ class ALS:
         """Squared-error sums and counts over flat indices u*n+i, split by `item_bin[i]` when given, computed on
         the device without the dense (m, n) prediction (b200als_sse_on_flat).  `flat_idx` / `y_true` may be numpy
         arrays or tensors already on the device.  Returns (sse float64[n_bins], cnt int64[n_bins]) as numpy."""
-        if self.U is None or self.V is None:
+        if not self.fitted:
             raise RuntimeError("Model must be fitted before prediction.")
         features = features or {}
-        self._check_features(features, self.V.shape[0], "predict")
+        self._check_features(features, self._n_items(), "predict")
         if not (1 <= int(n_bins) <= 32):
             raise ValueError("n_bins must be in [1, 32]")
         lib = _lib.load()
@@ -348,7 +435,9 @@ class FitSession:
         if len(features) > _lib.MAX_FEATURES:
             raise ValueError(f"at most {_lib.MAX_FEATURES} feature matrices are supported")
         names = self.names = list(features.keys())
-        ld = self.ld = _round4(k)
+        ld = self.ld = factor_ld(k, model.gram_path)
+        model._dev_model = None                    # a new fit replaces the resident model
+        model._host = {"U": None, "V": None, "b_u": None, "b_i": None}
         f32, f64 = torch.float32, torch.float64
 
         # ---- graph (host build for argpartition tie parity, als.py:354-357) ----
@@ -361,7 +450,9 @@ class FitSession:
                 logger.warning(f"GraphSim feature '{fname}' not found in features dict. "
                                f"Graph regularization disabled.")
             else:
+                t0 = time.perf_counter()
                 model.S = _graph.similarity_topk(Xg, model.S_topk, model.S_eps)
+                model.timings["S_build_s"] = time.perf_counter() - t0
         use_graph = self.use_graph = model.S is not None
         D = model.S.sum(axis=1) if use_graph else None                  # als.py:357 (S's dtype)
 
@@ -436,6 +527,14 @@ class FitSession:
         if use_graph:
             self.i_list = i_order[:i_nonempty]      # the Gauss–Seidel sweep is not sharded (§8e)
 
+        # fused exchange: the other ranks' replicas mapped here; the half-steps store solved rows into all of them
+        self.peers = None
+        if shard.active and not use_graph:
+            shared = shard.share_replicas(dict(U=U_d, V=V_d, b_u=self.b_u_d, b_i=self.b_i_d))
+            if shared is not None:
+                self.peers = {nm: [t.data_ptr() for t in ts] for nm, ts in shared.items()}
+                self._peer_tensors = shared             # keeps the mappings alive
+                self._token = torch.zeros(1, dtype=torch.float32, device=dev)
         self.u_split = self._split_plan(rt.indptr, self.u_list)
         self.i_split = None if use_graph else self._split_plan(rt.cindptr, self.i_list)
 
@@ -448,8 +547,10 @@ class FitSession:
         self.hist = torch.zeros(max(self.n_iters, 1), 6, dtype=f64, device=dev)
 
         if use_graph:
+            t0 = time.perf_counter()
             sptr, sidx, sval = _graph.to_csr(model.S)
             self.level_ptr, level_rows = _graph.level_schedule(sptr, sidx, item_counts > 0)
+            model.timings["S_csr_levels_s"] = time.perf_counter() - t0
             self.sptr_d = torch.from_numpy(sptr).to(dev)
             self.sidx_d = torch.from_numpy(sidx).to(dev)
             self.sval_d = torch.from_numpy(sval).to(dev)
@@ -498,7 +599,9 @@ class FitSession:
         """Long rows of a schedule cut into pieces for the tcgen05 path (b200als_split_plan_build); None if
         the path is not in use or no row can exceed the threshold."""
         model, lib = self.model, self.lib
-        if model.gram_path == _lib.PATH_FFMA or self.k not in (64, 128) or model.split_rows < 0 or rows.numel() == 0:
+        if model.gram_path == _lib.PATH_FFMA or self.ld not in (64, 128) or model.split_rows < 0 or rows.numel() == 0:
+            return None
+        if model.gram_path == _lib.PATH_AUTO and 2 * self.k <= self.ld:
             return None
         r64 = rows.to(torch.int64)
         nnz_list = int((indptr[r64 + 1] - indptr[r64]).sum().item())
@@ -516,7 +619,7 @@ class FitSession:
         return plan
 
     def _step(self, indptr, indices, vals, n_rows, rows, F, n_f_rows, bias_other, reg, reg_row, lamb, X, bias_own,
-              mode, stats=None, split=None, norms=None):
+              mode, stats=None, split=None, norms=None, peers=None):
         a = StepArgs()
         a.struct_bytes = C.sizeof(StepArgs)
         a.k, a.mode, a.path = self.k, mode, self.model.gram_path
@@ -536,8 +639,13 @@ class FitSession:
         a.norm_acc = norms
         a.split = C.addressof(split) if split is not None else None
         a.workspace, a.workspace_bytes = ptr(self.ws), self.ws.numel()
+        if peers is not None:
+            a.n_peers = len(peers[0])
+            for j, (px, pb) in enumerate(zip(*peers)):
+                a.peer_X[j], a.peer_bias[j] = px, pb
         check(self.lib.b200als_row_step(C.byref(a), self._stream()), "row_step")
         self.launches += self.lib.b200als_last_launch_count() + 1      # + the cursor memset
+        return self.lib.b200als_last_path()
 
     def _mark(self, phase):
         """Profile mode: CUDA events on the launching stream around each phase."""
@@ -567,17 +675,24 @@ class FitSession:
             self._compose(self.Z_d)                                     # als.py:411
         # (1) users (als.py:414-433)
         self._mark("user")
-        self._step(rt.indptr, rt.indices, rt.vals, m, self.u_list, self.Z_d, n, self.b_i_d, self.reg_user, None,
-                   self.lam_bu, self.U_d, self.b_u_d, _lib.STEP_SOLVE, split=self.u_split,
-                   norms=(self.acc.data_ptr() + 16) if fused else None)
+        peers = self.peers
+        model.last_paths["user"] = self._step(
+            rt.indptr, rt.indices, rt.vals, m, self.u_list, self.Z_d, n, self.b_i_d, self.reg_user, None,
+            self.lam_bu, self.U_d, self.b_u_d, _lib.STEP_SOLVE, split=self.u_split,
+            norms=(self.acc.data_ptr() + 16) if fused else None,
+            peers=(peers["U"], peers["b_u"]) if peers else None)
         if shard.active:
-            shard.exchange_rows(self.U_d, self.u_plan)
-            shard.exchange_rows(self.b_u_d, self.u_plan)
+            if peers:
+                shard.order_ranks(self._token)      # every rank's rows of U, b_u have landed in every replica
+            else:
+                shard.exchange_rows(self.U_d, self.u_plan)
+                shard.exchange_rows(self.b_u_d, self.u_plan)
         # (2) items (als.py:436-466); the item step ignores the feature term
         self._mark("item")
         if self.use_graph:
-            self._step(rt.cindptr, rt.cindices, rt.cvals, n, self.i_list, self.U_d, m, self.b_u_d, 0.0,
-                       self.reg_item_d, self.lam_bi, self.V_d, self.b_i_d, _lib.STEP_FACTOR)
+            model.last_paths["item"] = self._step(
+                rt.cindptr, rt.cindices, rt.cvals, n, self.i_list, self.U_d, m, self.b_u_d, 0.0,
+                self.reg_item_d, self.lam_bi, self.V_d, self.b_i_d, _lib.STEP_FACTOR)
             lp = self.level_ptr
             for lv in range(lp.size - 1):
                 lo, hi = int(lp[lv]), int(lp[lv + 1])
@@ -589,13 +704,19 @@ class FitSession:
         else:
             # A10 fused: with Z == V and no sweep after it, the item step sees every residual of
             # the iteration's final state, so it accumulates sum d / sum d^2 itself
-            self._step(rt.cindptr, rt.cindices, rt.cvals, n, self.i_list, self.U_d, m, self.b_u_d, 0.0,
-                       self.reg_item_d, self.lam_bi, self.V_d, self.b_i_d, _lib.STEP_SOLVE,
-                       stats=self.acc if fused else None, split=self.i_split,
-                       norms=(self.acc.data_ptr() + 24) if fused else None)
-            if shard.active:
+            model.last_paths["item"] = self._step(
+                rt.cindptr, rt.cindices, rt.cvals, n, self.i_list, self.U_d, m, self.b_u_d, 0.0,
+                self.reg_item_d, self.lam_bi, self.V_d, self.b_i_d, _lib.STEP_SOLVE,
+                stats=self.acc if fused else None, split=self.i_split,
+                norms=(self.acc.data_ptr() + 24) if fused else None,
+                peers=(peers["V"], peers["b_i"]) if peers else None)
+            if shard.active and not peers:
                 shard.exchange_rows(self.V_d, self.i_plan)
                 shard.exchange_rows(self.b_i_d, self.i_plan)
+            # (fused exchange: the residual all-reduce below orders the ranks after the item step; without fused
+            # statistics an explicit token does)
+            if shard.active and peers and not fused:
+                shard.order_ranks(self._token)
         # (3) W_f (als.py:468-501)
         self._mark("wstep")
         if names and ((it % model.update_w_every == 0) or (it == self.n_iters - 1)):
@@ -666,10 +787,14 @@ class FitSession:
         model._set_history(h)
         if done:
             model.mu = float(h[-1, 5])
-        model.U = _readback.f64_from_device(self.U_d[:rt.m, :k])
-        model.V = _readback.f64_from_device(self.V_d[:rt.n, :k])
-        model.b_u = _readback.f64_from_device(self.b_u_d[:rt.m])
-        model.b_i = _readback.f64_from_device(self.b_i_d[:rt.n])
         for f, nm in enumerate(self.names):
             model.W[nm] = self.W64_d[f].view(-1, k).cpu().numpy().copy()
+        # U, V, b_u, b_i stay in HBM; the float64 host copies are made when the attributes are read (ALS._get_param)
+        model._host = {"U": None, "V": None, "b_u": None, "b_i": None}
+        model._dev_model = dict(U=self.U_d, V=self.V_d, b_u=self.b_u_d, b_i=self.b_i_d, mu=self.mu_d,
+                                mu_value=float(model.mu), W={nm: self.W_d[f] for f, nm in enumerate(self.names)},
+                                W_host={nm: model.W[nm] for nm in self.names}, ld=self.ld, m=rt.m, n=rt.n, k=k,
+                                host_touched=False)
+        if os.environ.get("B200ALS_EAGER_READBACK"):
+            model.U, model.V, model.b_u, model.b_i     # noqa: B018 — reads materialise the host copies
         model.launches_per_iter = self.launches

@@ -47,4 +47,31 @@ int b200als_device_ok(void) {
     return 1;
 }
 
+int b200als_peer_enable(int32_t peer_device) {
+    int dev = 0;
+    if (cudaGetDevice(&dev) != cudaSuccess) {
+        cudaGetLastError();
+        b200als::set_error("no CUDA device is current");
+        return B200ALS_E_CUDA;
+    }
+    if (peer_device == dev) return B200ALS_OK;
+    int can = 0;
+    if (cudaDeviceCanAccessPeer(&can, dev, peer_device) != cudaSuccess || !can) {
+        cudaGetLastError();
+        b200als::set_error("device %d cannot access device %d's memory", dev, peer_device);
+        return B200ALS_E_UNSUPPORTED;
+    }
+    cudaError_t e = cudaDeviceEnablePeerAccess(peer_device, 0);
+    if (e == cudaErrorPeerAccessAlreadyEnabled) {
+        cudaGetLastError();
+        return B200ALS_OK;
+    }
+    if (e != cudaSuccess) {
+        cudaGetLastError();
+        b200als::set_error("cudaDeviceEnablePeerAccess(%d) failed: %s", peer_device, cudaGetErrorString(e));
+        return B200ALS_E_CUDA;
+    }
+    return B200ALS_OK;
+}
+
 }  // extern "C"

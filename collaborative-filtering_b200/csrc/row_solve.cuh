@@ -301,6 +301,9 @@ struct RowEpilogueArgs {
     float qq;                     // sum q^2 of the row (fused residual statistics)
     double* stats_d; double* stats_d2;   // thread-0 accumulators, may be null
     double* stats_xx; double* stats_bb;  // thread-0 accumulators of |x|^2 and bias^2
+    int n_peers;                         // fused exchange: replicas of the other ranks (row_step_ffma.cuh)
+    float* peer_X[B200ALS_MAX_PEERS];
+    float* peer_bias[B200ALS_MAX_PEERS];
 };
 
 // Preconditions: the lower-triangle tiles of F^T F are in S.Gt (tile rows 0..kt-1), c_s = F^T q
@@ -364,20 +367,27 @@ __device__ __forceinline__ void row_epilogue_tiles(const SolveSmem& S, const flo
             const float fc = (float)cnt;
             const float beta = (t_sum - part) / (fc + a.lam_bias);
             a.bias_own[r] = beta;
+            for (int j = 0; j < a.n_peers; ++j) a.peer_bias[j][r] = beta;
             *a.stats_xx += (double)xx;
             *a.stats_bb += (double)beta * (double)beta;
             if (a.stats_d) {
                 // d_e = q_e - beta - f_e.x over the row, from the quantities already at hand:
                 //   sum d^2 = qq - 2 beta t + cnt beta^2 - 2 (c.x - beta s.x) + x^T G x,
                 //   x^T G x = x.(c - beta_old s) - ridge x.x
-                *a.stats_d += (double)(t_sum - fc * beta - part);
-                *a.stats_d2 += (double)(a.qq - 2.0f * beta * t_sum + fc * beta * beta - cx +
-                                        (2.0f * beta - bias_old) * part - a.reg * xx);
+                // The terms are O(cnt) and cancel to ~0.4 cnt: combined in float64 (once per row, one thread).
+                const double bd = (double)beta, td = (double)t_sum, cd = (double)cnt, pd = (double)part;
+                *a.stats_d += td - cd * bd - pd;
+                *a.stats_d2 += (double)a.qq - 2.0 * bd * td + cd * bd * bd - (double)cx +
+                               (2.0 * bd - (double)bias_old) * pd - (double)a.reg * (double)xx;
             }
         }
     }
     float* xo = a.X + (size_t)r * a.ldx;
     for (int i = tid; i < k; i += nthr) xo[i] = x[i];
+    for (int j = 0; j < a.n_peers; ++j) {
+        float* xp = a.peer_X[j] + (size_t)r * a.ldx;
+        for (int i = tid; i < k; i += nthr) xp[i] = x[i];
+    }
 }
 
 }  // namespace b200als

@@ -7,11 +7,17 @@
 
 namespace b200als {
 
+static thread_local int g_last_path = 0;   // Gram path the last b200als_row_step on this thread took
+
 template <int KP, int T>
 static int launch_ffma(const RowStepParams& p, cudaStream_t s) {
     using C = FfmaCfg<KP, T>;
     auto kern = row_step_ffma_kernel<KP, T>;
-    static thread_local int blocks_per_sm = 0;   // per (KP,T) instantiation
+    // per (KP,T) instantiation and per device (function attributes belong to the device's context)
+    static thread_local int blocks_per_dev[64] = {0};
+    int dev = 0;
+    ALS_CUDA(cudaGetDevice(&dev));
+    int& blocks_per_sm = blocks_per_dev[dev & 63];
     if (blocks_per_sm == 0) {
         ALS_CUDA(cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)C::smem_bytes));
         int b = 0;
@@ -109,15 +115,18 @@ int b200als_step_workspace_bytes(int32_t k, int32_t path, int64_t n_f_rows, size
     ALS_CHECK_ARG(bytes_host, "null");
     ALS_CHECK_ARG(k >= 1 && k <= B200ALS_MAX_K, "k out of range");
     ALS_CHECK_ARG(n_f_rows >= 0, "negative row count");
-    *bytes_host = (path == B200ALS_PATH_FFMA) ? 256 : umma_workspace_bytes(k, n_f_rows);
+    *bytes_host = (path == B200ALS_PATH_FFMA) ? 256 : umma_workspace_bytes(umma_padded_k(k), n_f_rows);
     return B200ALS_OK;
 }
+
+int b200als_last_path(void) { return g_last_path; }
 
 int b200als_split_plan_bytes(int32_t k, int64_t n_list, int64_t nnz, int32_t split_rows, int32_t split_piece,
                              size_t* bytes_host) {
     ALS_CHECK_ARG(bytes_host, "null");
-    ALS_CHECK_ARG(k >= 1 && k <= B200ALS_MAX_K, "k out of range");
+    ALS_CHECK_ARG(k >= 1 && k <= 128, "k out of range (the tcgen05 path covers k <= 128)");
     ALS_CHECK_ARG(n_list >= 0 && n_list < (1ll << 31) && nnz >= 0, "count out of range");
+    k = umma_padded_k(k);
     SplitLayout L;
     split_layout(k, n_list, nnz, split_rows, split_piece, 256, L);
     *bytes_host = L.total;
@@ -128,8 +137,9 @@ int b200als_split_plan_build(const int64_t* indptr, const int32_t* rows, int64_t
                              int32_t split_rows, int32_t split_piece, void* plan_mem, size_t plan_bytes,
                              b200als_split_plan* plan_host, b200als_stream_t stream) {
     ALS_CHECK_ARG(indptr && plan_host, "null");
-    ALS_CHECK_ARG(k >= 1 && k <= B200ALS_MAX_K, "k out of range");
+    ALS_CHECK_ARG(k >= 1 && k <= 128, "k out of range (the tcgen05 path covers k <= 128)");
     ALS_CHECK_ARG(n_list >= 0 && n_list < (1ll << 31) && nnz >= 0, "count out of range");
+    k = umma_padded_k(k);
     memset(plan_host, 0, sizeof(*plan_host));
     plan_host->n_list = n_list;
     SplitLayout L;
@@ -159,12 +169,15 @@ int b200als_row_step(const b200als_step_args* a, b200als_stream_t stream) {
     int path = a->path;
     // FACTOR mode (graph sweep) stores the Cholesky factor from the tile solver: FFMA path only
     if (path == B200ALS_PATH_AUTO || a->mode == B200ALS_STEP_FACTOR)
-        path = (a->mode == B200ALS_STEP_SOLVE && umma_supported(a->k, a->ldf)) ? B200ALS_PATH_UMMA : B200ALS_PATH_FFMA;
+        path = (a->mode == B200ALS_STEP_SOLVE && umma_preferred(a->k, a->ldf)) ? B200ALS_PATH_UMMA : B200ALS_PATH_FFMA;
+    g_last_path = path;
     size_t need = 256;
     if (path == B200ALS_PATH_UMMA) {
         ALS_CHECK_ARG(a->n_f_rows > 0, "n_f_rows must be set for the tcgen05 path");
-        need = umma_workspace_bytes(a->k, a->n_f_rows);
+        need = umma_workspace_bytes((int)a->ldf, a->n_f_rows);
     }
+    ALS_CHECK_ARG(a->n_peers >= 0 && a->n_peers <= B200ALS_MAX_PEERS, "n_peers out of range");
+    ALS_CHECK_ARG(a->n_peers == 0 || a->mode == B200ALS_STEP_SOLVE, "peer replicas only in SOLVE mode");
     if (!a->workspace || a->workspace_bytes < need) {
         set_error("b200als_row_step: workspace %zu < required %zu", a->workspace_bytes, need);
         return B200ALS_E_WORKSPACE;
@@ -182,12 +195,19 @@ int b200als_row_step(const b200als_step_args* a, b200als_stream_t stream) {
     p.norms = (a->mode == B200ALS_STEP_SOLVE) ? a->norm_acc : nullptr;
     p.cursor = reinterpret_cast<unsigned long long*>(a->workspace);
     p.items = nullptr; p.split_hdr = nullptr; p.slot_np = nullptr; p.slot_ctr = nullptr; p.slot_acc = nullptr;
+    p.row_ids = a->row_ids;
+    p.n_peers = a->n_peers;
+    for (int j = 0; j < B200ALS_MAX_PEERS; ++j) {
+        p.peer_X[j] = j < a->n_peers ? a->peer_X[j] : nullptr;
+        p.peer_bias[j] = j < a->n_peers ? a->peer_bias[j] : nullptr;
+        ALS_CHECK_ARG(j >= a->n_peers || (p.peer_X[j] && p.peer_bias[j]), "null peer replica");
+    }
     ALS_CUDA(cudaMemsetAsync(a->workspace, 0, 256, s));
 
     if (path == B200ALS_PATH_UMMA) {
-        if (!umma_supported(a->k, a->ldf)) {
-            set_error("b200als_row_step: tcgen05 path needs k in {64,128} and ldf == k (got k=%d ldf=%lld)", a->k,
-                      (long long)a->ldf);
+        if (!umma_supported(a->k, a->ldf) || a->ldx < a->ldf) {
+            set_error("b200als_row_step: tcgen05 path needs ldf in {64,128}, k <= ldf, zero padding in F and ldx >= ldf "
+                      "(got k=%d ldf=%lld ldx=%lld)", a->k, (long long)a->ldf, (long long)a->ldx);
             return B200ALS_E_UNSUPPORTED;
         }
         return launch_umma(p, a->n_f_rows, a->split, static_cast<char*>(a->workspace), a->workspace_bytes, s);

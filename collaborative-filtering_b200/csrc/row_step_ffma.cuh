@@ -43,7 +43,25 @@ struct RowStepParams {
     const int32_t* slot_np;       // pieces of split row `slot`
     int32_t* slot_ctr;            // pieces of the slot accumulated so far (zeroed)
     float* slot_acc;              // per slot: k rows x (k + 4) [normal matrix | c, s, -, -] | t, qq, -, -  (zeroed)
+    // slab storage: indptr / rows[] are local to this rank's slab, row_ids[r] is the row's id in X / bias_own / reg_row
+    const int32_t* row_ids;
+    // fused exchange: the solved row and its bias are also stored into the replicas of the other ranks (peer-mapped
+    // device memory, NVLink) — the half-step's all-gather without a separate collective
+    int n_peers;
+    float* peer_X[B200ALS_MAX_PEERS];
+    float* peer_bias[B200ALS_MAX_PEERS];
 };
+
+// x and bias of a solved row go to every replica (thread-level: the caller's lanes hold consecutive entries, so the
+// peer stores are 128-byte coalesced NVLink writes)
+__device__ __forceinline__ void store_x_all(const RowStepParams& p, size_t off, float x) {
+    p.X[off] = x;
+    for (int j = 0; j < p.n_peers; ++j) p.peer_X[j][off] = x;
+}
+__device__ __forceinline__ void store_bias_all(const RowStepParams& p, int64_t row, float b) {
+    p.bias_own[row] = b;
+    for (int j = 0; j < p.n_peers; ++j) p.peer_bias[j][row] = b;
+}
 
 template <int KP, int T>
 struct FfmaCfg {
@@ -106,6 +124,7 @@ __global__ void __launch_bounds__(FfmaCfg<KP, T>::THREADS) row_step_ffma_kernel(
         const int64_t slot = misc_s[2];
         if (slot < 0) break;
         const int64_t r = p.rows ? (int64_t)p.rows[slot] : slot;
+        const int64_t gr = p.row_ids ? (int64_t)p.row_ids[r] : r;        // the row's id in X / bias_own / reg_row
         const int64_t beg = p.indptr[r], end = p.indptr[r + 1];
         const int64_t cnt = end - beg;
         if (cnt <= 0) continue;
@@ -251,15 +270,17 @@ __global__ void __launch_bounds__(FfmaCfg<KP, T>::THREADS) row_step_ffma_kernel(
         __syncthreads();
         RowEpilogueArgs ea;
         ea.k = k; ea.mode = p.mode;
-        ea.reg = p.reg_row ? p.reg_row[r] : p.reg;
-        ea.lam_bias = p.lam_bias_row ? p.lam_bias_row[r] : p.lam_bias;
+        ea.reg = p.reg_row ? p.reg_row[gr] : p.reg;
+        ea.lam_bias = p.lam_bias_row ? p.lam_bias_row[gr] : p.lam_bias;
         ea.X = p.X; ea.ldx = p.ldx; ea.bias_own = p.bias_own;
+        ea.n_peers = p.n_peers;
+        for (int j = 0; j < B200ALS_MAX_PEERS; ++j) { ea.peer_X[j] = p.peer_X[j]; ea.peer_bias[j] = p.peer_bias[j]; }
         ea.chol_out = p.chol_out; ea.aux_out = p.aux_out; ea.status = p.status;
         ea.stats_d = &stat_d; ea.stats_d2 = &stat_d2;
         ea.stats_xx = &stat_xx; ea.stats_bb = &stat_bb;
         const float t_sum = red_s[31];
         ea.qq = red_s[30];
-        row_epilogue_tiles(S, c_s, s_s, t_sum, cnt, r, ea, tid, NTHR, 1);
+        row_epilogue_tiles(S, c_s, s_s, t_sum, cnt, gr, ea, tid, NTHR, 1);
     }
     if (p.stats && tid == 0) {
         atomicAdd(&p.stats[0], stat_d);

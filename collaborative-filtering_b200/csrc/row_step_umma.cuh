@@ -598,9 +598,10 @@ __device__ __forceinline__ void umma_role_solver(const RowStepParams& p, const U
             row = p.items[-2 - d0v.x].x;
         }
         const bool any_part = __any_sync(0xffffffffu, part);   // both halves sit in every warp: group-uniform
-        const float ridge = p.reg_row ? p.reg_row[row] : p.reg;
-        const float lam_bias = p.lam_bias_row ? p.lam_bias_row[row] : p.lam_bias;
-        const float bias_old = p.bias_own[row];
+        const int64_t grow = p.row_ids ? (int64_t)p.row_ids[row] : row;   // the row's id in X / bias_own / reg_row
+        const float ridge = p.reg_row ? p.reg_row[grow] : p.reg;
+        const float lam_bias = p.lam_bias_row ? p.lam_bias_row[grow] : p.lam_bias;
+        const float bias_old = p.bias_own[grow];
         if (q == 0 && seg == 0) { sts_s32(bad_a, 0); sts_s32(lastf_a, 0); }
 
         const uint32_t buf = pr % C::NBUF;
@@ -726,7 +727,7 @@ __device__ __forceinline__ void umma_role_solver(const RowStepParams& p, const U
                       make_int4(__float_as_int(v0), __float_as_int(v1), __float_as_int(v2), 0));
         named_bar_sync(phase_bar, 128);
         const bool good = valid && (lds_s32(bad_a) == 0);
-        if (good) p.X[(size_t)row * p.ldx + r] = x;
+        if (good) store_x_all(p, (size_t)grow * p.ldx + r, x);
         if (q == 0 && seg == 0) {
             if (good) {
                 float sx = 0.0f, cx = 0.0f, xx = 0.0f;
@@ -737,20 +738,20 @@ __device__ __forceinline__ void umma_role_solver(const RowStepParams& p, const U
                 }
                 const float cntf = (float)cnt;
                 const float beta = (tsum - sx) / (cntf + lam_bias);            // als.py:431-433 / 464-466
-                p.bias_own[row] = beta;
+                store_bias_all(p, grow, beta);
                 // residuals of the row with the fresh x, beta:  d_e = q_e - beta - f_e.x
                 //   sum d   = t - cnt beta - s.x
                 //   sum d^2 = qq - 2 beta t + cnt beta^2 - 2 (c.x - beta s.x) + x^T G x,
                 //   x^T G x = x.(c - beta_old s) - ridge x.x      (x solves (G + ridge I) x = c - beta_old s)
-                const float sd = tsum - cntf * beta - sx;
-                const float sd2 = qq - 2.0f * beta * tsum + cntf * beta * beta - cx +
-                                  (2.0f * beta - bias_old) * sx - ridge * xx;
-                acc_d += (double)sd;
-                acc_d2 += (double)sd2;
+                // (terms of O(cnt) cancelling to ~0.4 cnt: combined in float64, once per row on one thread)
+                const double bd = (double)beta, td = (double)tsum, cd = (double)cnt, sxd = (double)sx;
+                acc_d += td - cd * bd - sxd;
+                acc_d2 += (double)qq - 2.0 * bd * td + cd * bd * bd - (double)cx +
+                          (2.0 * bd - (double)bias_old) * sxd - (double)ridge * (double)xx;
                 acc_xx += (double)xx;
                 acc_bb += (double)beta * (double)beta;
             } else if (valid && p.status) {
-                if (atomicAdd(&p.status[0], 1) == 0) p.status[1] = (int32_t)row;
+                if (atomicAdd(&p.status[0], 1) == 0) p.status[1] = (int32_t)grow;
             }
         }
         // no barrier here: the next pair's descriptor barrier stands between these reads (red, bad, x, columns:
@@ -832,12 +833,19 @@ __global__ void __launch_bounds__(UmmaCfg<K>::THREADS, 1) row_step_umma_kernel(c
     }
 }
 
-static inline bool umma_supported(int k, int64_t ldf) { return (k == 64 || k == 128) && ldf == k; }
+// The kernel is instantiated for K = 64 and K = 128.  Any k <= K runs on it through zero padding: the caller
+// keeps the factor rows with a row stride of exactly K floats and zeros in columns [k, K) (b200als.h), so the
+// padded block of the normal matrix is ridge * I with a zero right-hand side, decoupled from the rest — the
+// k leading entries of the solution are unchanged and the padded ones come out as exact zeros.
+static inline int umma_padded_k(int k) { return k <= 64 ? 64 : (k <= 128 ? 128 : 0); }
+static inline bool umma_supported(int k, int64_t ldf) { return (ldf == 64 || ldf == 128) && k >= 1 && k <= ldf; }
+// AUTO takes the tensor-core path when more than half of the padded width is real work
+static inline bool umma_preferred(int k, int64_t ldf) { return umma_supported(k, ldf) && 2 * k > ldf; }
 
-// workspace: [256 B cursor] [bf16 copy of F]
-static inline size_t umma_workspace_bytes(int k, int64_t n_f_rows) {
-    if (k != 64 && k != 128) return 256;
-    return 256 + align_up((size_t)(n_f_rows > 0 ? n_f_rows : 0) * 4 * k, 256);
+// workspace: [256 B cursor] [bf16 copy of F]   (kp: padded width, 64 or 128)
+static inline size_t umma_workspace_bytes(int kp, int64_t n_f_rows) {
+    if (kp != 64 && kp != 128) return 256;
+    return 256 + align_up((size_t)(n_f_rows > 0 ? n_f_rows : 0) * 4 * kp, 256);
 }
 
 template <int K>
@@ -873,11 +881,8 @@ static int launch_umma_k(RowStepParams& p, int64_t n_f_rows, const b200als_split
         p.slot_acc = plan->slot_acc;
     }
     auto kern = row_step_umma_kernel<K>;
-    static thread_local bool configured = false;
-    if (!configured) {
-        ALS_CUDA(cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)C::smem_bytes));
-        configured = true;
-    }
+    // function attributes are per device: set on every launch (cheap), not cached per thread
+    ALS_CUDA(cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)C::smem_bytes));
     int64_t grid = p.n_list < kNumSMs ? p.n_list : kNumSMs;
     if (split) grid = kNumSMs;                         // pieces: the item count is only known on the device
     kern<<<(unsigned)grid, C::THREADS, C::smem_bytes, st>>>(p, reinterpret_cast<const unsigned char*>(H));
@@ -887,7 +892,7 @@ static int launch_umma_k(RowStepParams& p, int64_t n_f_rows, const b200als_split
 
 static inline int launch_umma(RowStepParams& p, int64_t n_f_rows, const b200als_split_plan* plan, char* ws,
                               size_t ws_bytes, cudaStream_t s) {
-    if (p.k == 64) return launch_umma_k<64>(p, n_f_rows, plan, ws, ws_bytes, s);
+    if (p.ldf == 64) return launch_umma_k<64>(p, n_f_rows, plan, ws, ws_bytes, s);
     return launch_umma_k<128>(p, n_f_rows, plan, ws, ws_bytes, s);
 }
 

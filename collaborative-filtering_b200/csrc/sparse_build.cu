@@ -234,17 +234,45 @@ __global__ void dense_fill_csc_kernel(const double* __restrict__ R, int64_t m, i
 
 // ---- COO input --------------------------------------------------------------
 // sorted flat index → (row32, col32); indptr by boundary detection.
+// Input check before anything is built: indices inside [0, m*n), strictly increasing (on the sorted sequence:
+// duplicates; on a `sorted` input also disorder), ratings finite.  status[0..2] count the violations.
+__global__ void coo_validate_kernel(const int64_t* __restrict__ flat, const float* __restrict__ vals, int64_t nnz,
+                                    int64_t total, unsigned long long* __restrict__ status) {
+    const int64_t stride = (int64_t)gridDim.x * blockDim.x;
+    unsigned oob = 0, dis = 0, nonf = 0;
+    for (int64_t e = (int64_t)blockIdx.x * blockDim.x + threadIdx.x; e < nnz; e += stride) {
+        const int64_t f = flat[e];
+        oob += (f < 0 || f >= total);
+        if (e > 0) dis += (flat[e - 1] >= f);
+        const float v = vals[e];
+        nonf += !(fabsf(v) <= 3.402823466e38f);
+    }
+    oob = __reduce_add_sync(0xffffffffu, oob);
+    dis = __reduce_add_sync(0xffffffffu, dis);
+    nonf = __reduce_add_sync(0xffffffffu, nonf);
+    if ((threadIdx.x & 31) == 0) {
+        if (oob) atomicAdd(&status[0], (unsigned long long)oob);
+        if (dis) atomicAdd(&status[1], (unsigned long long)dis);
+        if (nonf) atomicAdd(&status[2], (unsigned long long)nonf);
+    }
+}
+
+__device__ __forceinline__ int64_t clamp_flat(int64_t f, int64_t total) { return f < 0 ? 0 : (f >= total ? total - 1 : f); }
+
 __global__ void coo_split_kernel(const int64_t* __restrict__ flat, int64_t nnz, int64_t m, int64_t n,
                                  int32_t* __restrict__ rows32, int32_t* __restrict__ cols32,
                                  int64_t* __restrict__ indptr) {
     const int64_t stride = (int64_t)gridDim.x * blockDim.x;
+    const int64_t total = m * n;
     for (int64_t e = (int64_t)blockIdx.x * blockDim.x + threadIdx.x; e < nnz; e += stride) {
-        int64_t f = flat[e];
+        // out-of-range entries are clamped (and reported by coo_validate_kernel): nothing is written outside
+        // indptr[0..m] / the nnz-long arrays whatever the input holds
+        int64_t f = clamp_flat(flat[e], total);
         int64_t r = f / n;
         int32_t c = (int32_t)(f - r * n);
         rows32[e] = (int32_t)r;
         cols32[e] = c;
-        int64_t rprev = (e == 0) ? -1 : flat[e - 1] / n;
+        int64_t rprev = (e == 0) ? -1 : clamp_flat(flat[e - 1], total) / n;
         for (int64_t q = rprev + 1; q <= r; ++q) indptr[q] = e;   // rows rprev+1..r start at e
         if (e == nnz - 1)
             for (int64_t q = r + 1; q <= m; ++q) indptr[q] = nnz;
@@ -384,12 +412,13 @@ int b200als_coo_workspace_bytes(int64_t nnz, int64_t m, int64_t n, size_t* bytes
 int b200als_coo_to_csr_csc(const int64_t* flat_idx, const float* vals_in, int64_t nnz, int64_t m, int64_t n,
                            int sorted, int64_t* indptr, int32_t* indices, float* vals, int64_t* cindptr,
                            int32_t* cindices, float* cvals, int64_t* perm, void* workspace, size_t workspace_bytes,
-                           b200als_stream_t stream) {
+                           int64_t* status3, b200als_stream_t stream) {
     ALS_CHECK_ARG(m > 0 && n > 0 && nnz >= 0, "bad shape");
     ALS_CHECK_ARG(n < (1ll << 31) && m < (1ll << 31), "m and n must fit int32");
     ALS_CHECK_ARG(nnz < (1ll << 32), "nnz per call must be < 2^32 (shard larger jobs by rows)");
     ALS_CHECK_ARG(indptr && cindptr, "null indptr");
     cudaStream_t s = as_stream(stream);
+    if (status3) ALS_CUDA(cudaMemsetAsync(status3, 0, 3 * sizeof(int64_t), s));
     if (nnz == 0) {
         fill_empty_indptr_kernel<<<grid_for(m + 1, 256), 256, 0, s>>>(indptr, m + 1);
         ALS_LAUNCH_CHECK();
@@ -426,6 +455,11 @@ int b200als_coo_to_csr_csc(const int64_t* flat_idx, const float* vals_in, int64_
         flat_use = flat_sorted;
     } else {
         ALS_CUDA(cudaMemcpyAsync(vals, vals_in, sizeof(float) * nnz, cudaMemcpyDeviceToDevice, s));
+    }
+    if (status3) {
+        coo_validate_kernel<<<grid_for(nnz, 256), 256, 0, s>>>(flat_use, vals, nnz, m * n,
+                                                               reinterpret_cast<unsigned long long*>(status3));
+        ALS_LAUNCH_CHECK();
     }
     coo_split_kernel<<<grid_for(nnz, 256), 256, 0, s>>>(flat_use, nnz, m, n, rows32, indices, indptr);
     ALS_LAUNCH_CHECK();

@@ -20,6 +20,13 @@
 
 namespace b200als {
 
+#ifndef B200ALS_SPLIT_ROWS_DEFAULT
+#define B200ALS_SPLIT_ROWS_DEFAULT 12288
+#endif
+#ifndef B200ALS_SPLIT_PIECE_DEFAULT
+#define B200ALS_SPLIT_PIECE_DEFAULT 8192
+#endif
+
 struct SplitLayout {                 // byte offsets inside the step workspace (after the bf16 copy)
     size_t counts, scanned, cub_tmp, cub_bytes, items, slot_np, slot_ctr, slot_acc, total;
     int64_t max_items, max_slots;
@@ -33,12 +40,15 @@ static inline bool split_layout(int k, int64_t n_list, int64_t nnz, int32_t spli
     L = SplitLayout{};
     L.total = base;
     if (split_rows < 0 || nnz <= 0 || n_list <= 0) return false;
-    // default: a row may hold at most a quarter of one SM's share of the ratings
-    int64_t auto_t = nnz / ((int64_t)kNumSMs * 4);
-    auto_t = auto_t < 8192 ? 8192 : (auto_t > (1 << 20) ? (1 << 20) : auto_t);
-    L.thresh = split_rows == 0 ? (int)auto_t : split_rows;
+    // default: an ABSOLUTE piece length, not a share of the launch's ratings.  The tensor core adds into its
+    // float32 accumulator with truncation, so a chain of n accumulation steps (16 ratings each) biases the sums
+    // low by ~n 2^-25 relative; with pieces keyed on the launch size the result drifted with the number of
+    // ranks sharing the rows (round-1 SCALE record: train RMSE moved 4.4e-5 between 1 and 8 GPUs).  A fixed
+    // piece bounds the chain (B200ALS_SPLIT_PIECE_DEFAULT / 16 steps), makes the summation tree a function of the
+    // row alone, and still leaves pieces far below one SM's share at every named shape.
+    L.thresh = split_rows == 0 ? B200ALS_SPLIT_ROWS_DEFAULT : split_rows;
     if (L.thresh < 32) L.thresh = 32;
-    int piece = split_piece > 0 ? split_piece : L.thresh / 2;
+    int piece = split_piece > 0 ? split_piece : (split_rows == 0 ? B200ALS_SPLIT_PIECE_DEFAULT : L.thresh / 2);
     piece = ((piece + 31) / 32) * 32;
     if (piece < 32) piece = 32;
     L.piece = piece;

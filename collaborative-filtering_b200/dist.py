@@ -15,6 +15,15 @@ data.  The solved rows travel packed: index_select -> all_gather_into_tensor ->
 index_copy_ through a precomputed permutation; the padding slots of the last
 round point at one dummy row appended to each replica.
 
+Fused exchange (the default on a GPU box): every rank maps the other ranks'
+replicas into its address space (CUDA IPC handles, exchanged once per fit through
+the process group) and the half-step kernel itself stores each solved row and bias
+into all replicas — coalesced 128-byte NVLink writes from the solver's epilogue,
+overlapped with the rows still being solved — so no separate collective moves the
+factors; one small all-reduce per half-step orders the ranks (a kernel's peer
+stores are visible once it has completed).  The packed all-gather stays as the
+fallback (no peer access, CPU `gloo` groups, B200ALS_EXCHANGE=allgather).
+
 Residual sums are combined with one float64 all-reduce per iteration.
 
 `torch.distributed` is plumbing only; with a `gloo` group on CPU tensors the
@@ -101,6 +110,54 @@ class Shard:
         if self.active:
             src = 0 if self.group is None else td.get_global_rank(self.group, 0)
             td.broadcast(t, src=src, group=self.group)
+
+    # ---- fused exchange: peer-mapped replicas ------------------------------------
+    def share_replicas(self, tensors: dict) -> dict | None:
+        """Map every other rank's copy of each named CUDA tensor into this process.
+
+        Returns {name: [peer tensors, one per other rank]} (aliases of the peers' memory, usable as store targets
+        of a kernel on this device), or None when any rank could not set it up — the decision is collective, so
+        all ranks fall back to the packed all-gather together."""
+        import os
+        if not self.active or os.environ.get("B200ALS_EXCHANGE", "peer") != "peer":
+            return None
+        ok, out, err = 1, {}, ""
+        try:
+            first = next(iter(tensors.values()))
+            if not first.is_cuda or self.world - 1 > 7:
+                raise RuntimeError("peer exchange needs CUDA tensors and at most 8 ranks")
+            from torch.multiprocessing.reductions import reduce_tensor
+            from . import _lib
+            mine = {nm: reduce_tensor(t) for nm, t in tensors.items()}
+            box = [None] * self.world
+            td.all_gather_object(box, mine, group=self.group)
+            lib = _lib.load()
+            for r, entry in enumerate(box):
+                if r == self.rank:
+                    continue
+                for nm, (rebuild, args) in entry.items():
+                    t = rebuild(*args)
+                    if lib.b200als_peer_enable(int(t.device.index)) != 0:
+                        raise RuntimeError(_lib.last_error())
+                    if tuple(t.shape) != tuple(tensors[nm].shape) or t.stride() != tensors[nm].stride():
+                        raise RuntimeError(f"replica '{nm}' differs in shape between ranks")
+                    out.setdefault(nm, []).append(t)
+        except Exception as e:   # noqa: BLE001 — any failure means: use the collective instead
+            ok, err = 0, f"{type(e).__name__}: {e}"
+        flag = torch.tensor([ok], dtype=torch.int32, device=next(iter(tensors.values())).device)
+        td.all_reduce(flag, op=td.ReduceOp.MIN, group=self.group)
+        if int(flag.item()) == 0:
+            if err:
+                import logging
+                logging.getLogger(__name__).warning("peer-mapped exchange unavailable (%s): using all-gather", err)
+            return None
+        return out
+
+    def order_ranks(self, token: torch.Tensor) -> None:
+        """Every rank's work enqueued so far (peer stores included) is complete before anything enqueued after
+        this call starts on any rank: a one-element all-reduce on the stream."""
+        if self.active:
+            td.all_reduce(token, op=td.ReduceOp.SUM, group=self.group)
 
     def all_reduce_sum(self, t: torch.Tensor) -> None:
         if self.active:

@@ -1,14 +1,19 @@
 """float64 host copies of the learned float32 device arrays (scripts/als.py:404-407: U, V, b_u, b_i are float64).
 
-`direct` (the default, the path every measured number of round 1 used): widen on the device, one pageable D2H.
-`pipelined` (B200ALS_READBACK=pipelined; written at the end of round 1 after the GPU budget was spent, so NOT yet
-run on a GPU and therefore not the default): float32 D2H in chunks through two small pinned buffers, each chunk
-widened into the float64 result by libb200als_host.so on the host threads while the next chunk's copy is in
-flight.  Half the bytes cross PCIe, the copies are pinned, and the first-touch page faults of the result are
-spread over the cores.  The host part is covered on CPU tensors by tests/test_host_graph.py.
+Called when a public attribute of a fitted model is first read (ALS._get_param).  Two ways to the same array:
+
+`direct`    widen on the device, one pageable D2H of the float64 array.
+`pipelined` (default for arrays of >= 4 Mi elements) float32 D2H in chunks through two small pinned buffers, each
+            chunk widened into the float64 result by libb200als_host.so on the host threads while the next chunk's
+            copy is in flight.  Half the bytes cross PCIe and the copies are pinned.
+
+Either way the result array is advised MADV_HUGEPAGE before its first touch: at the Netflix shape the 492 MB result
+is 120 k first-touch page faults with 4 KB pages (they, not PCIe, were the 0.23 s of round 1's read-back) and 240
+with 2 MB pages.  B200ALS_READBACK=direct|pipelined overrides the choice; B200ALS_HUGEPAGE=0 skips the advice.
 """
 from __future__ import annotations
 
+import ctypes as C
 import os
 
 import numpy as np
@@ -18,6 +23,30 @@ from . import _hostlib
 
 CHUNK_BYTES = 16 << 20
 MIN_PIPELINED_ELEMS = 1 << 22
+_HUGE = 2 << 20
+_MADV_HUGEPAGE = 14
+_libc = None
+
+
+def empty_f64(shape) -> np.ndarray:
+    """np.empty(shape, float64) whose interior is advised to be backed by 2 MB pages (Linux THP in `madvise` mode)."""
+    global _libc
+    out = np.empty(shape, dtype=np.float64)
+    if out.nbytes < 2 * _HUGE or os.environ.get("B200ALS_HUGEPAGE", "1") == "0":
+        return out
+    try:
+        if _libc is None:
+            _libc = C.CDLL(None, use_errno=True)
+            _libc.madvise.argtypes = [C.c_void_p, C.c_size_t, C.c_int]
+            _libc.madvise.restype = C.c_int
+        a = out.ctypes.data
+        lo = (a + _HUGE - 1) & ~(_HUGE - 1)
+        hi = (a + out.nbytes) & ~(_HUGE - 1)
+        if hi > lo:
+            _libc.madvise(C.c_void_p(lo), C.c_size_t(hi - lo), _MADV_HUGEPAGE)      # advisory: failure changes nothing
+    except Exception:   # noqa: BLE001 — no libc / not Linux: plain pages
+        pass
+    return out
 
 
 def _widen_into(src: np.ndarray, dst: np.ndarray, nth: int) -> None:
@@ -33,21 +62,26 @@ def _widen_into(src: np.ndarray, dst: np.ndarray, nth: int) -> None:
 def f64_from_device(t: torch.Tensor, mode: str | None = None, chunk_bytes: int = CHUNK_BYTES,
                     n_threads: int | None = None) -> np.ndarray:
     """`t.double().cpu().numpy()` for a float32 vector or matrix (row-strided views allowed)."""
-    mode = mode or os.environ.get("B200ALS_READBACK", "direct")
-    if mode not in ("direct", "pipelined"):
-        raise ValueError(f"B200ALS_READBACK={mode!r}: expected 'direct' or 'pipelined'")
-    if mode == "direct" or t.dtype != torch.float32 or t.dim() not in (1, 2) or t.numel() < MIN_PIPELINED_ELEMS:
-        return t.double().cpu().numpy()
+    mode = mode or os.environ.get("B200ALS_READBACK", "auto")
+    if mode not in ("auto", "direct", "pipelined"):
+        raise ValueError(f"B200ALS_READBACK={mode!r}: expected 'auto', 'direct' or 'pipelined'")
+    small = t.numel() < MIN_PIPELINED_ELEMS
+    if mode == "direct" or t.dtype != torch.float32 or t.dim() not in (1, 2) or (small and mode == "auto") or t.numel() == 0:
+        out = empty_f64(tuple(t.shape))
+        if t.numel():
+            torch.from_numpy(out).copy_(t.double() if t.is_cuda else t)      # device-side widening, one D2H into `out`
+        return out
     t2 = t.reshape(1, -1) if t.dim() == 1 else t
-    if t2.dim() == 2 and t2.shape[0] == 1 and t2.shape[1] * 4 > chunk_bytes:      # a long vector: chunk along it
+    if t2.shape[0] == 1 and t2.shape[1] * 4 > chunk_bytes:      # a long vector: chunk along it
         width = chunk_bytes // 4
-        pad = (-t2.shape[1]) % width
-        if pad:
-            return t.double().cpu().numpy()                                      # ragged: not worth a third path
+        if t2.shape[1] % width:
+            out = empty_f64(tuple(t.shape))
+            torch.from_numpy(out).copy_(t.double() if t.is_cuda else t)      # ragged: not worth a third path
+            return out
         t2 = t2.reshape(-1, width)
     rows, cols = t2.shape
     nth = int(n_threads or _hostlib.host_threads())
-    out = np.empty((rows, cols), dtype=np.float64)
+    out = empty_f64((rows, cols))
     chunk_rows = max(1, chunk_bytes // (4 * cols))
     on_gpu = t2.is_cuda
     bufs = [torch.empty((chunk_rows, cols), dtype=torch.float32, pin_memory=on_gpu) for _ in range(2)]

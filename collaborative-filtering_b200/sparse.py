@@ -75,6 +75,10 @@ def ratings_from_flat(flat_idx, vals, shape, device, sorted_input: bool = False,
 
     `flat_idx` / `vals` may be numpy arrays (copied H2D here) or torch tensors
     already on `device` (int64 / float32).
+
+    The arrays are checked on the device before anything is built from them: an index outside the matrix raises
+    IndexError (as the reference's matrix_from_indices does), duplicates (which the reference's scatter would
+    resolve last-wins), a `sorted_input` promise that does not hold, or a non-finite rating raise ValueError.
     """
     lib = _lib.load()
     _lib.require_device()
@@ -101,10 +105,20 @@ def ratings_from_flat(flat_idx, vals, shape, device, sorted_input: bool = False,
     cindices = torch.empty(z, dtype=torch.int32, device=device)
     cvals = torch.empty(z, dtype=torch.float32, device=device)
     perm = torch.empty(z, dtype=torch.int64, device=device) if want_perm else None
+    status = torch.zeros(3, dtype=torch.int64, device=device)
     check(lib.b200als_coo_to_csr_csc(ptr(fd), ptr(vd), nnz, m, n, 1 if sorted_input else 0,
                                      ptr(indptr), ptr(indices), ptr(ovals), ptr(cindptr), ptr(cindices),
-                                     ptr(cvals), ptr(perm), ptr(ws), ws.numel(), _stream()), "coo_to_csr_csc")
-    torch.cuda.current_stream().synchronize()   # workspace `ws` is released on return
+                                     ptr(cvals), ptr(perm), ptr(ws), ws.numel(), ptr(status), _stream()),
+          "coo_to_csr_csc")
+    st = status.cpu().numpy()                   # also the synchronisation after which `ws` may be released
+    if st[0]:
+        # matrix_from_indices (create_folds.py:169-174) raises IndexError on these
+        raise IndexError(f"{int(st[0])} flat indices lie outside the ({m}, {n}) matrix")
+    if st[1]:
+        what = "is not strictly ascending (sorted_input=True was promised)" if sorted_input else "holds duplicates"
+        raise ValueError(f"flat_idx {what}: {int(st[1])} adjacent pairs out of order")
+    if st[2]:
+        raise ValueError(f"{int(st[2])} ratings are not finite (a list of observed entries has no 'missing' marker)")
     return Ratings(m, n, nnz, indptr, indices[:nnz], ovals[:nnz], cindptr, cindices[:nnz], cvals[:nnz],
                    perm[:nnz] if perm is not None else None)
 

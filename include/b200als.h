@@ -31,7 +31,7 @@
 extern "C" {
 #endif
 
-#define B200ALS_ABI_VERSION 7
+#define B200ALS_ABI_VERSION 8
 
 #define B200ALS_OK            0
 #define B200ALS_E_INVALID    -1   /* bad argument */
@@ -42,6 +42,7 @@ extern "C" {
 #define B200ALS_MAX_K        160  /* tune_params.py:99 N_FACTORS_MAX = 150 */
 #define B200ALS_MAX_FEATURES 8
 #define B200ALS_STATUS_WORDS 4    /* [0]=#non-SPD rows, [1]=first bad row, [2]=phase, [3]=reserved */
+#define B200ALS_MAX_PEERS    7    /* other ranks of an 8-GPU box whose replicas a half-step stores into */
 
 typedef void* b200als_stream_t;   /* cudaStream_t */
 
@@ -49,6 +50,9 @@ int         b200als_abi_version(void);
 const char* b200als_last_error(void);
 /* 1 if a usable sm_100 device is current, 0 otherwise (sync; never throws). */
 int         b200als_device_ok(void);
+/* Let kernels on the current device store into memory of `peer_device` (NVLink peer access; idempotent).  Needed
+ * before b200als_step_args.peer_X / peer_bias point at another GPU's replicas. */
+int         b200als_peer_enable(int32_t peer_device);
 
 /* ------------------------------------------------------------------------
  * A1 — CSR / CSC construction (als.py:335-340), index-bit-exact:
@@ -73,7 +77,14 @@ int b200als_dense_fill(const double* R, int64_t m, int64_t n,
 /* COO input: flat_idx[e] = u*n + i (create_folds.py:73-84 convention), unique,
  * any order unless `sorted` != 0 (then ascending, as np.flatnonzero and
  * np.setdiff1d give it, create_folds.py:200).  Replaces the dense
- * matrix_from_indices round trip (create_folds.py:152-174 + als.py:335-340). */
+ * matrix_from_indices round trip (create_folds.py:152-174 + als.py:335-340).
+ * The input is validated on the device before anything is built from it (one pass): *status3 (device, 3
+ * int64, may be NULL) receives [0] the number of indices outside [0, m*n) — the reference's
+ * matrix_from_indices raises IndexError on those (create_folds.py:169-174) —, [1] the number of adjacent
+ * pairs of the (sorted) sequence that are not strictly increasing, i.e. duplicates, or a `sorted` input that
+ * is not, [2] the number of non-finite ratings (NaN means "missing" in the reference's dense form and has no
+ * meaning in a list of observed entries).  Out-of-range indices are clamped while building, so nothing is
+ * written outside the outputs; the caller reads the status and rejects the arrays if any count is non-zero. */
 int b200als_coo_workspace_bytes(int64_t nnz, int64_t m, int64_t n, size_t* bytes_host);
 int b200als_coo_to_csr_csc(const int64_t* flat_idx, const float* vals_in,
                            int64_t nnz, int64_t m, int64_t n, int sorted,
@@ -81,6 +92,7 @@ int b200als_coo_to_csr_csc(const int64_t* flat_idx, const float* vals_in,
                            int64_t* cindptr, int32_t* cindices, float* cvals,
                            int64_t* perm,
                            void* workspace, size_t workspace_bytes,
+                           int64_t* status3,
                            b200als_stream_t stream);
 
 /* Row schedule: order[] = row ids sorted by descending rating count (longest
@@ -131,7 +143,7 @@ int b200als_compose_z(const float* V, int64_t ldv, int64_t n, int32_t k,
 #define B200ALS_STEP_SOLVE  0
 #define B200ALS_STEP_FACTOR 1
 
-#define B200ALS_PATH_AUTO   0   /* tcgen05 when k in {64,128}, else FFMA */
+#define B200ALS_PATH_AUTO   0   /* tcgen05 when ldf in {64,128} and ldf/2 < k <= ldf (zero-padded rows), else FFMA */
 #define B200ALS_PATH_FFMA   1
 #define B200ALS_PATH_UMMA   2
 
@@ -195,6 +207,15 @@ typedef struct b200als_step_args {
     const struct b200als_split_plan* split;   /* host pointer, optional (tcgen05 path, SOLVE mode): the plan built by
                                     b200als_split_plan_build for exactly this (indptr, rows, n_list) */
     void*  workspace; size_t workspace_bytes;   /* see b200als_step_workspace_bytes */
+    const int32_t* row_ids;      /* optional (slab storage): indptr / rows[] are local to the caller's slab of rows and
+                                    row_ids[r] is local row r's id in X, bias_own, reg_row and lam_bias_row */
+    int32_t n_peers;             /* fused exchange (multi-GPU, SOLVE mode): the solved row and its bias are ALSO stored
+                                    into peer_X[j] / peer_bias[j], j < n_peers — the replicas of the other ranks, mapped
+                                    into this process (CUDA IPC) — so the half-step's all-gather rides on the solver's
+                                    own stores over NVLink instead of a separate collective.  Same layout as X/bias_own. */
+    int32_t reserved0;
+    float* peer_X[B200ALS_MAX_PEERS];
+    float* peer_bias[B200ALS_MAX_PEERS];
 } b200als_step_args;
 
 /* workspace for one b200als_row_step call gathering from an F of n_f_rows rows */
@@ -202,6 +223,15 @@ int b200als_step_workspace_bytes(int32_t k, int32_t path, int64_t n_f_rows, size
 int b200als_row_step(const b200als_step_args* args_host, b200als_stream_t stream);
 /* Number of kernel launches the last b200als_row_step on this thread issued. */
 int b200als_last_launch_count(void);
+/* Gram path (B200ALS_PATH_FFMA / B200ALS_PATH_UMMA) the last b200als_row_step on this thread took. */
+int b200als_last_path(void);
+
+/* tcgen05 path and k: the kernel exists for K = 64 and K = 128 and covers every k <= K by zero padding — the
+ * caller keeps F (and X) with a row stride of exactly K floats and zeros in columns [k, K).  The padded block of
+ * the normal matrix is reg * I with a zero right-hand side and decouples: the k leading entries of the solution
+ * are those of the k x k system (als.py:426-428), the padded entries come out as exact zeros (and are written).
+ * k in 129..160 (tune_params.py:98-99 samples up to 150) stays on the FFMA path: a K = 160 accumulator needs
+ * 176 TMEM columns (2 matrices in flight instead of 3) and an 80 KB column store per matrix. */
 
 /* A8 — one level of the Gauss–Seidel Laplacian sweep (als.py:453-461).
  * For every item i in level_rows[0..n_level):

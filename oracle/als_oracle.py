@@ -155,7 +155,7 @@ class SparseALSOracle:
         """als.py:300-529 over the dict returned by csr_csc_from_*.
 
         on_iter(it, self) is called after each iteration's history append.
-        init: optional dict(U=, V=, W={}) to skip RNG draws (big shapes).
+        init: optional dict(U=, V=, W={}[, b_u=, b_i=]) to skip RNG draws (big shapes).
         max_rows: (CPU-baseline sampling only) int or (users, items): process only
         the first so-many user rows and item rows per sweep and skip the W / mu
         steps; `self.sampled_ratings` reports the ratings touched.  Never used
@@ -198,6 +198,11 @@ class SparseALSOracle:
             self.U = np.array(init["U"], dtype=float)
             self.V = np.array(init["V"], dtype=float)
             self.W = {kk: np.array(vv, dtype=float) for kk, vv in init.get("W", {}).items()}
+            # (tests at full size restart a half-step from a given state: biases are then given too)
+            if init.get("b_u") is not None:
+                self.b_u = np.array(init["b_u"], dtype=float)
+            if init.get("b_i") is not None:
+                self.b_i = np.array(init["b_i"], dtype=float)
 
         item_counts = np.diff(cindptr).astype(float)                   # als.py:379
         lambda_v_i = item_reg(item_counts, self.lambda_v, self.pop_reg_mode).astype(float)

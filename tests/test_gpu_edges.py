@@ -1,0 +1,253 @@
+"""GPU: the edges of the reference's own hyper-parameter range on the float32 device path, the
+exception surface of the solve, and the reference drivers' dense call sequence on the real CUDA class.
+
+  * lambda_u = lambda_v over the tuner's log-uniform range [1e-4, 1e4] (scripts/tune_params.py:102-103) with rows
+    that hold FEWER ratings than factors (the Gram is rank deficient and only the ridge keeps it SPD), at
+    k = 32 (FFMA path), 64 and 128 (tcgen05 path);
+  * the `lambda_w = 0` ablation form (scripts/evaluate_models.py:413-426): features passed, W_f regularised by EPS alone;
+  * a system that is not positive definite raises numpy.linalg.LinAlgError like scripts/helpers.py:19;
+  * k = 50 at the bundled shape; a graph + features model at k = 64 (FACTOR mode keeps the item step on FFMA);
+  * every k in (32, 128] takes the tcgen05 kernel through zero padding;
+  * `fit(R_train) -> predict() -> .ravel()[idx]`, the sequence of scripts/tune_params.py:376-392 and
+    scripts/evaluate_models.py:246-265, restated line for line and run on this class, against the reference's own
+    numbers (tests/golden/eval_folds.npz);
+  * input validation of fit_coo (out-of-range, duplicate, unsorted-but-promised-sorted, non-finite);
+  * refit on the same object appends to history (scripts/als.py:185-191).
+"""
+import os
+
+import numpy as np
+import pytest
+
+from _util import GOLDEN, bundled_features, load_case, make_cfg, rel_err
+
+pytestmark = pytest.mark.gpu
+
+FACTOR_TOL = 1e-3
+RMSE_TOL = 1e-4
+
+
+def _oracle(cfg, flat, vals, m, n, features=None, lambda_w=None):
+    import als_oracle
+    return als_oracle.SparseALSOracle(cfg, lambda_w).fit_sparse(als_oracle.csr_csc_from_flat(flat, vals, m, n), m, n,
+                                                                 features, tol=None)
+
+
+def _short_row_problem(seed, m=400, n=250, per_row=20):
+    """Every user holds ~per_row ratings and most items fewer than 64: cnt < k on both sides for k >= 64."""
+    from b200als.synth import synth_ratings
+    return synth_ratings(m, n, m * per_row, seed=seed) + (m, n)
+
+
+@pytest.mark.parametrize("k", [32, 64, 128])
+@pytest.mark.parametrize("lam", [1e-2, 1.0, 1e4])
+def test_lambda_range_short_rows_vs_oracle(cuda_device, k, lam):
+    import b200als
+    flat, vals, m, n = _short_row_problem(seed=100 + k)
+    cfg = b200als.ALSConfig(core=b200als.CoreConfig(n_factors=k, n_iters=3, lambda_u=lam, lambda_v=lam),
+                            biases=b200als.BiasesConfig(lambda_bu=2.0, lambda_bi=2.5))
+    o = _oracle(cfg, flat, vals, m, n)
+    model = b200als.ALS(cfg).fit_coo(flat, vals, (m, n), tol=None, verbose=0, sorted_input=True)
+    errs = {a: rel_err(getattr(model, a), getattr(o, a)) for a in ("U", "V", "b_u", "b_i")}
+    d = float(np.abs(np.asarray(model.history["train_rmse"]) - np.asarray(o.history["train_rmse"])).max())
+    print(f"k={k} lambda={lam:g}: {errs} dRMSE={d:.2e}")
+    assert max(errs.values()) < FACTOR_TOL, errs
+    assert d < RMSE_TOL
+
+
+@pytest.mark.parametrize("k", [32, 64, 128])
+def test_smallest_lambda_short_rows(cuda_device, k):
+    """lambda = 1e-4 with cnt < k: the normal matrices have condition numbers of 1e5..1e6 — beyond what a float32
+    Gram can resolve to 1e-3 in the FACTORS (the ridge is the size of the float32 rounding of the Gram itself), so
+    what is held here is what the model is used for: the fit runs, stays finite, and its train-RMSE curve and its
+    predictions on the observed entries follow the float64 reference's.  (The measured factor error is printed.)"""
+    import b200als
+    flat, vals, m, n = _short_row_problem(seed=200 + k)
+    cfg = b200als.ALSConfig(core=b200als.CoreConfig(n_factors=k, n_iters=3, lambda_u=1e-4, lambda_v=1e-4),
+                            biases=b200als.BiasesConfig(lambda_bu=2.0, lambda_bi=2.5))
+    o = _oracle(cfg, flat, vals, m, n)
+    model = b200als.ALS(cfg).fit_coo(flat, vals, (m, n), tol=None, verbose=0, sorted_input=True)
+    errs = {a: rel_err(getattr(model, a), getattr(o, a)) for a in ("U", "V", "b_u", "b_i")}
+    hist = np.asarray(model.history["train_rmse"])
+    d = float(np.abs(hist - np.asarray(o.history["train_rmse"])).max())
+    print(f"k={k} lambda=1e-4: {errs} dRMSE={d:.2e}")
+    assert np.isfinite(hist).all() and all(np.isfinite(getattr(model, a)).all() for a in ("U", "V", "b_u", "b_i"))
+    assert d < 5e-3
+    pp = model.predict_pairs(flat // n, flat % n)
+    assert abs(np.sqrt(np.mean((pp - vals) ** 2)) - np.sqrt(np.mean((o.predict_pairs(flat // n, flat % n) - vals) ** 2))) < 5e-3
+
+
+def test_lambda_w_zero_ablation_form(cuda_device):
+    """evaluate_models.py:413-426: the `no_features`-style variants pass the features with lambda_w = 0."""
+    import b200als
+    c = load_case("small_feat2")
+    lw = {fn: 0.0 for fn in c.feature_names}
+    cfg = make_cfg(c.cfgd)
+    o = _oracle(cfg, c.flat, c.vals, c.m, c.n, c.features, lw)
+    model = b200als.ALS(config=cfg, lambda_w=lw).fit_coo(c.flat, c.vals, (c.m, c.n), features=c.features, tol=None,
+                                                         verbose=0)
+    for a in ("U", "V", "b_u", "b_i"):
+        assert rel_err(getattr(model, a), getattr(o, a)) < FACTOR_TOL, a
+    for fn in c.feature_names:
+        assert rel_err(model.W[fn], o.W[fn]) < FACTOR_TOL, fn
+    assert np.abs(np.asarray(model.history["train_rmse"]) - np.asarray(o.history["train_rmse"])).max() < RMSE_TOL
+
+
+@pytest.mark.parametrize("k", [8, 64, 100])
+def test_not_positive_definite_raises_linalgerror(cuda_device, k):
+    """A negative ridge larger than the Gram's smallest eigenvalue: scipy's cho_factor raises LinAlgError
+    (scripts/helpers.py:19); so does this class, on both Gram paths."""
+    import b200als
+    from b200als.synth import synth_ratings
+    m, n, nnz = 200, 150, 4000
+    flat, vals = synth_ratings(m, n, nnz, seed=9)
+    cfg = b200als.ALSConfig(core=b200als.CoreConfig(n_factors=k, n_iters=2, lambda_u=-50.0, lambda_v=3.0),
+                            biases=b200als.BiasesConfig(lambda_bu=2.0, lambda_bi=2.0))
+    with pytest.raises(np.linalg.LinAlgError):
+        _oracle(cfg, flat, vals, m, n)
+    with pytest.raises(np.linalg.LinAlgError):
+        b200als.ALS(cfg).fit_coo(flat, vals, (m, n), tol=None, verbose=0, sorted_input=True)
+
+
+def test_bundled_shape_k50_vs_oracle(cuda_device):
+    """C1 at k = 50 (scripts/als_config.py:24's example value): tcgen05 path through zero padding to 64."""
+    import b200als
+    c = load_case("c1_k32")
+    cfgd = dict(c.cfgd, core=dict(c.cfgd["core"], n_factors=50, n_iters=3))
+    cfg = make_cfg(cfgd)
+    o = _oracle(cfg, c.flat, c.vals, c.m, c.n)
+    model = b200als.ALS(cfg).fit_coo(c.flat, c.vals, (c.m, c.n), tol=None, verbose=0)
+    assert model.last_paths == {"user": b200als._lib.PATH_UMMA, "item": b200als._lib.PATH_UMMA}
+    for a in ("U", "V", "b_u", "b_i"):
+        assert rel_err(getattr(model, a), getattr(o, a)) < FACTOR_TOL, a
+    assert model.U.shape == (c.m, 50) and model.V.shape == (c.n, 50)
+    assert np.abs(np.asarray(model.history["train_rmse"]) - np.asarray(o.history["train_rmse"])).max() < RMSE_TOL
+
+
+def test_graph_and_features_at_k64(cuda_device):
+    """The full model at k = 64: the user step takes the tcgen05 kernel, the Gauss-Seidel item step needs the stored
+    Cholesky factors (FACTOR mode) and stays on FFMA."""
+    import b200als
+    c = load_case("small_full")
+    cfgd = dict(c.cfgd, core=dict(c.cfgd["core"], n_factors=64, n_iters=3))
+    cfg = make_cfg(cfgd)
+    o = _oracle(cfg, c.flat, c.vals, c.m, c.n, c.features, c.lambda_w)
+    model = b200als.ALS(config=cfg, lambda_w=c.lambda_w).fit_coo(c.flat, c.vals, (c.m, c.n), features=c.features,
+                                                                 tol=None, verbose=0)
+    assert model.last_paths["user"] == b200als._lib.PATH_UMMA
+    assert model.last_paths["item"] == b200als._lib.PATH_FFMA
+    for a in ("U", "V", "b_u", "b_i"):
+        assert rel_err(getattr(model, a), getattr(o, a)) < FACTOR_TOL, a
+    for fn in c.feature_names:
+        assert rel_err(model.W[fn], o.W[fn]) < FACTOR_TOL, fn
+    assert np.abs(np.asarray(model.history["train_rmse"]) - np.asarray(o.history["train_rmse"])).max() < RMSE_TOL
+
+
+@pytest.mark.parametrize("k", [33, 40, 50, 72, 96, 100, 127, 129, 150])
+def test_every_k_above_32_on_the_tensor_core(cuda_device, k):
+    """PATH_AUTO: k in (32, 128] runs the tcgen05 kernel (rows zero-padded to 64 / 128), k > 128 stays on FFMA; both
+    match the oracle.  (scripts/tune_params.py:98-99 samples n_factors uniformly in [1, 150].)"""
+    import b200als
+    from b200als.synth import synth_ratings
+    m, n, nnz = 300, 200, 9000
+    flat, vals = synth_ratings(m, n, nnz, seed=k)
+    cfg = b200als.ALSConfig(core=b200als.CoreConfig(n_factors=k, n_iters=3, lambda_u=4.0, lambda_v=3.0),
+                            biases=b200als.BiasesConfig(lambda_bu=2.0, lambda_bi=2.5))
+    o = _oracle(cfg, flat, vals, m, n)
+    model = b200als.ALS(cfg)
+    model.split_rows, model.split_piece = 96, 64            # a few rows go through the split-row slots as well
+    model.fit_coo(flat, vals, (m, n), tol=None, verbose=0, sorted_input=True)
+    want = b200als._lib.PATH_UMMA if k <= 128 else b200als._lib.PATH_FFMA
+    assert model.last_paths == {"user": want, "item": want}
+    assert model.U.shape == (m, k) and model.V.shape == (n, k)
+    for a in ("U", "V", "b_u", "b_i"):
+        assert rel_err(getattr(model, a), getattr(o, a)) < FACTOR_TOL, a
+    assert np.abs(np.asarray(model.history["train_rmse"]) - np.asarray(o.history["train_rmse"])).max() < RMSE_TOL
+    for key, arr in (("U_norm", o.U), ("V_norm", o.V)):
+        assert abs(model.history[key][-1] - np.linalg.norm(arr)) < 1e-3 * np.linalg.norm(arr)
+
+
+def test_reference_driver_sequence_on_the_cuda_class(cuda_device):
+    """tune_params.py:376-392 / evaluate_models.py:246-274 restated: dense NaN-filled train matrix -> fit -> dense
+    predict -> .ravel()[val_idx] -> masked RMSE (tune_params.py:147-167), overall and per popularity bin, on THIS
+    class (nothing substituted), against the numbers the reference's own drivers produced on the same folds."""
+    import b200als
+    z = np.load(os.path.join(GOLDEN, "eval_folds.npz"))
+    m, n, n_bins = int(z["m"]), int(z["n"]), int(z["n_bins"])
+    R = np.full(m * n, np.nan)
+    R[z["flat_idx"]] = z["vals"].astype(np.float64) / 2.0
+    R = R.reshape(m, n)
+    k, iters, lu, lv, seed = z["cfg_core"]
+    item_bin = z["bin_quantile"]
+
+    def rmse_on_indices(R_true, R_pred, idx):                      # tune_params.py:147-167
+        if len(idx) == 0:
+            return float("nan")
+        y_true, y_pred = R_true.ravel()[idx], R_pred.ravel()[idx]
+        mask = ~np.isnan(y_true)
+        return float(np.sqrt(np.mean((y_true[mask] - y_pred[mask]) ** 2)))
+
+    for fold in range(4):
+        val_idx = z[f"val_idx_{fold}"]
+        R_train = R.copy()                                         # create_folds.py:200-206
+        R_train.ravel()[val_idx] = np.nan
+        R_valid = np.full_like(R, np.nan)
+        R_valid.ravel()[val_idx] = R.ravel()[val_idx]
+        model = b200als.ALS(b200als.ALSConfig(
+            core=b200als.CoreConfig(n_factors=int(k), n_iters=int(iters), lambda_u=float(lu), lambda_v=float(lv),
+                                    random_state=int(seed)),
+            biases=b200als.BiasesConfig(lambda_bu=1.5, lambda_bi=1.5)))
+        model.fit(R_train, features=None, tol=None, min_iters=0, verbose=0)
+        R_pred = model.predict(None)
+        assert R_pred.shape == (m, n) and R_pred.dtype == np.float64
+        assert abs(rmse_on_indices(R_valid, R_pred, val_idx) - float(z[f"rmse_{fold}"])) < RMSE_TOL
+        cols = val_idx % n                                         # evaluate_models.py:173-191
+        got = np.asarray([rmse_on_indices(R_valid, R_pred, val_idx[item_bin[cols] == b]) for b in range(n_bins)])
+        want = z[f"bin_rmse_{fold}"]
+        assert np.array_equal(np.isnan(got), np.isnan(want))
+        assert np.nanmax(np.abs(got - want)) < RMSE_TOL
+        assert len(model.history.get("train_rmse", [])) == len(z[f"train_rmse_{fold}"])
+        assert np.abs(np.asarray(model.history["train_rmse"]) - z[f"train_rmse_{fold}"]).max() < RMSE_TOL
+        # the resident model and the public float64 attributes describe the same model: reading the attributes
+        # (which makes them authoritative) must not change the prediction beyond float32 rounding
+        _ = model.U, model.V, model.b_u, model.b_i
+        assert np.abs(model.predict(None) - R_pred).max() < 1e-5
+
+
+def test_fit_coo_input_validation(cuda_device):
+    import b200als
+    from b200als.synth import synth_ratings
+    m, n, nnz = 60, 40, 500
+    flat, vals = synth_ratings(m, n, nnz, seed=1)
+    cfg = b200als.ALSConfig(core=b200als.CoreConfig(n_factors=4, n_iters=1, lambda_u=1.0, lambda_v=1.0))
+
+    def fit(f, v, **kw):
+        return b200als.ALS(cfg).fit_coo(f, v, (m, n), tol=None, verbose=0, **kw)
+    fit(flat, vals, sorted_input=True)
+    bad = flat.copy(); bad[7] = m * n                           # past the end: matrix_from_indices raises IndexError
+    with pytest.raises(IndexError):
+        fit(bad, vals)
+    bad = flat.copy(); bad[0] = -1
+    with pytest.raises(IndexError):
+        fit(bad, vals)
+    with pytest.raises(ValueError, match="duplicates"):
+        fit(np.concatenate([flat, flat[:3]]), np.concatenate([vals, vals[:3]]))
+    with pytest.raises(ValueError, match="ascending"):
+        fit(flat[::-1].copy(), vals[::-1].copy(), sorted_input=True)
+    v = vals.copy(); v[5] = np.nan
+    with pytest.raises(ValueError, match="finite"):
+        fit(flat, v)
+
+
+def test_refit_appends_history(cuda_device):
+    """history is created in __init__ and every fit appends (scripts/als.py:185-191, 510-517)."""
+    import b200als
+    c = load_case("small_biases")
+    model = b200als.ALS(config=make_cfg(c.cfgd))
+    model.fit_coo(c.flat, c.vals, (c.m, c.n), tol=None, verbose=0)
+    first = list(model.history["train_rmse"])
+    model.fit_coo(c.flat, c.vals, (c.m, c.n), tol=None, verbose=0)
+    assert len(model.history["train_rmse"]) == 2 * len(first)
+    assert model.history["train_rmse"][:len(first)] == first
+    assert np.allclose(model.history["train_rmse"][len(first):], first, atol=1e-6)     # same seed, same fit
+    assert len(model.history["U_norm"]) == 2 * len(first)

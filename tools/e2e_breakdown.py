@@ -33,9 +33,19 @@ for rep in range(2):                       # second pass: warm allocator, the nu
     mu0 = float(rt.vals.sum(dtype=torch.float64).item() / nnz)
     ses = stage("session_init_incl_host_rng_and_upload", lambda: model.session(rt, mu0))
     stage("iterations", lambda: [ses.iteration(it) for it in range(K)])
-    stage("finish_d2h_float64", lambda: ses.finish(K))
+    stage("finish_history_only", lambda: ses.finish(K))
+    from b200als import readback
+    for mode in ("direct", "pipelined"):
+        for hp in ("0", "1"):
+            os.environ["B200ALS_HUGEPAGE"] = hp
+            stage(f"readback_{mode}_hugepage{hp}", lambda: [readback.f64_from_device(t, mode=mode) for t in
+                                                            (ses.U_d[:m, :k], ses.V_d[:n, :k], ses.b_u_d[:m], ses.b_i_d[:n])])
+    os.environ["B200ALS_HUGEPAGE"] = "1"
+    stage("read_attributes_default", lambda: (model.U, model.V, model.b_u, model.b_i))
 t = time.perf_counter()
 m2 = b200als.ALS(cfg); m2.fit_coo(flat_h, vals_h, (m, n), tol=None, verbose=0, sorted_input=True)
 out["fit_coo_total"] = round(time.perf_counter() - t, 4)
+_ = m2.U, m2.V, m2.b_u, m2.b_i
+out["fit_coo_plus_attribute_reads"] = round(time.perf_counter() - t, 4)
 out.update(workload=wl, n_iterations=K)
 print(json.dumps(out))
