@@ -17,7 +17,7 @@ STATUS_WORDS = 4
 MAX_PEERS = 7
 
 STEP_SOLVE, STEP_FACTOR = 0, 1
-PATH_AUTO, PATH_FFMA, PATH_UMMA = 0, 1, 2
+PATH_AUTO, PATH_FFMA, PATH_UMMA, PATH_F64 = 0, 1, 2, 3
 
 c_i64p = C.c_void_p   # device pointers travel as integers
 vp = C.c_void_p
@@ -77,9 +77,11 @@ _SIGNATURES = {
                           C.POINTER(vp), C.POINTER(C.c_int32), C.POINTER(vp),
                           C.c_int64, C.c_int32, vp, C.c_int64, vp],
     "b200als_step_workspace_bytes": [C.c_int32, C.c_int32, C.c_int64, C.POINTER(C.c_size_t)],
-    "b200als_split_plan_bytes": [C.c_int32, C.c_int64, C.c_int64, C.c_int32, C.c_int32, C.POINTER(C.c_size_t)],
-    "b200als_split_plan_build": [vp, vp, C.c_int64, C.c_int64, C.c_int32, C.c_int32, C.c_int32, vp, C.c_size_t,
-                                 C.POINTER(SplitPlan), vp],
+    "b200als_split_default": [C.c_int32],
+    "b200als_split_plan_bytes": [C.c_int32, C.c_int64, C.c_int64, C.c_int32, C.c_int32, C.c_int64,
+                                 C.POINTER(C.c_size_t)],
+    "b200als_split_plan_build": [vp, vp, C.c_int64, C.c_int64, C.c_int32, C.c_int32, C.c_int32, C.c_int64, vp,
+                                 C.c_size_t, C.POINTER(SplitPlan), vp],
     "b200als_row_step": [C.POINTER(StepArgs), vp],
     "b200als_graph_level_solve": [C.c_int32, vp, C.c_int64, vp, vp, vp, vp, vp,
                                   C.c_float, C.c_float, vp, vp, C.c_int64, vp, vp],

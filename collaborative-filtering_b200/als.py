@@ -53,6 +53,15 @@ def factor_ld(k: int, gram_path: int) -> int:
     return _round4(k)
 
 
+# Ridge below which a row with fewer than PRECISE_COUNT_FACTOR * k ratings goes to the float64 half-step, per Gram
+# path.  Measured on B200 against the float64 oracle on rows of ~20 ratings (tests/test_gpu_edges.py): the relative
+# factor error grows like lambda^-1.5 from 1.3e-6 (FFMA) / 2e-5 (tcgen05, bf16 hi/lo operands) at lambda = 1 and
+# crosses the 1e-3 bar near 0.03 / 0.1; rows with many more ratings than factors have a full-rank Gram whose smallest
+# eigenvalue, not the ridge, bounds the condition number, and stay on the fast paths whatever lambda is.
+PRECISE_RIDGE = {_lib.PATH_FFMA: 0.1, _lib.PATH_UMMA: 0.3}
+PRECISE_COUNT_FACTOR = 4
+
+
 def _env_int(name: str, default: int) -> int:
     try:
         return int(os.environ.get(name, default))
@@ -102,6 +111,9 @@ class ALS:
         # absolute defaults, include/b200als.h; < 0: never)
         self.split_rows = _env_int("B200ALS_SPLIT_ROWS", 0)
         self.split_piece = _env_int("B200ALS_SPLIT_PIECE", 0)
+        # "auto": rows whose ridge is too small for float32 (few ratings AND small lambda, see PRECISE_RIDGE) take
+        # the float64 half-step, the rest the fast paths; "f32": never; "f64": every row (the reference's arithmetic)
+        self.precision = os.environ.get("B200ALS_PRECISION", "auto")
         self.shard: Shard | None = None    # row sharding across ranks (dist.Shard)
         self.timings: dict[str, float] = {}
         self.launches_per_iter: int = 0
@@ -218,6 +230,15 @@ class ALS:
         with torch.cuda.device(ratings.vals.device):
             mu0 = float(ratings.vals.sum(dtype=torch.float64).item() / max(ratings.nnz, 1))
             return self._fit_ratings(ratings, mu0, features, tol, min_iters, verbose, init)
+
+    def fit_slabs(self, slabs, tol=1e-3, min_iters=5, verbose=1, init=None) -> "ALS":
+        """Sharded fit on slab-only storage (`slab.RatingSlabs`: this rank's CSR rows and CSC columns, nothing else;
+        U/V + biases model).  Every rank of the job calls it with its own slabs and `model.shard` set."""
+        _lib.load()
+        _lib.require_device()
+        with torch.cuda.device(slabs.vals.device):
+            mu0 = float(slabs.vals_sum / max(slabs.nnz, 1))                 # als.py:360 over ALL ratings
+            return self._fit_ratings(slabs, mu0, None, tol, min_iters, verbose, init)
 
     # ------------------------------------------------------------------ core loop
     def session(self, rt: Ratings, mu0: float, features=None, init=None, profile: bool = False) -> "FitSession":
@@ -502,7 +523,20 @@ class FitSession:
         self.Z_d = torch.zeros(n_pad, ld, dtype=f32, device=dev) if names else V_d
 
         # ---- regularisers (als.py:379-384, 426, 450-454), folded in float64 ------
-        item_counts = (rt.cindptr[1:] - rt.cindptr[:-1]).cpu().numpy().astype(float)
+        slab = self.slab = hasattr(rt, "row_ids_u")       # slab.RatingSlabs: local row pointers, global ids
+        if slab:
+            if not shard.active and rt.world != 1:
+                raise ValueError("RatingSlabs of a multi-rank job need model.shard to be the job's Shard")
+            if (rt.rank, rt.world) != (shard.rank, shard.world):
+                raise ValueError(f"slabs were built for rank {rt.rank}/{rt.world}, the fit runs as {shard.rank}/{shard.world}")
+            if names or use_graph:
+                raise ValueError("slab storage covers the U/V + biases model (the W step and the graph sweep are not sharded)")
+            cnt_d = torch.zeros(n, dtype=torch.int64, device=dev)
+            cnt_d[rt.row_ids_i.long()] = rt.cindptr[1:] - rt.cindptr[:-1]
+            shard.all_reduce_sum(cnt_d)
+            item_counts = cnt_d.cpu().numpy().astype(float)
+        else:
+            item_counts = (rt.cindptr[1:] - rt.cindptr[:-1]).cpu().numpy().astype(float)
         lambda_v_i = model._item_reg(item_counts).astype(float)
         reg_item = lambda_v_i + EPS
         if use_graph:
@@ -517,7 +551,15 @@ class FitSession:
         i_order, i_nonempty = row_schedule(rt.cindptr)
         self.ulo, self.uhi = shard.my_range(m)          # contiguous split, residual reduction only
         self.ilo, self.ihi = shard.my_range(n)
-        if shard.active:
+        self.u_ids = rt.row_ids_u if slab else None     # local row -> id in U / b_u (slab storage)
+        self.i_ids = rt.row_ids_i if slab else None
+        if slab:
+            # the slab IS this rank's share: its non-empty rows, longest first (local ids)
+            self.u_list, self.i_list = u_order[:u_nonempty], i_order[:i_nonempty]
+            if shard.active:
+                self.u_plan = shard.plan_exchange_ids(rt.row_ids_u.long()[self.u_list.long()], m)
+                self.i_plan = shard.plan_exchange_ids(rt.row_ids_i.long()[self.i_list.long()], n)
+        elif shard.active:
             uo, io = u_order[:u_nonempty], i_order[:i_nonempty]
             self.u_list, self.i_list = shard.deal(uo), shard.deal(io)
             self.u_plan = shard.plan_exchange(uo, m)    # row m / n of the replicas is the dummy row
@@ -535,6 +577,10 @@ class FitSession:
                 self.peers = {nm: [t.data_ptr() for t in ts] for nm, ts in shared.items()}
                 self._peer_tensors = shared             # keeps the mappings alive
                 self._token = torch.zeros(1, dtype=torch.float32, device=dev)
+        # rows that need float64 (small ridge, few ratings) leave the fast lists
+        self.u_list, self.u_f64 = self._precision_split(rt.indptr, self.u_list, self.reg_user, None, self.u_ids, False)
+        self.i_list, self.i_f64 = self._precision_split(rt.cindptr, self.i_list, None, self.reg_item_d, self.i_ids,
+                                                        use_graph)
         self.u_split = self._split_plan(rt.indptr, self.u_list)
         self.i_split = None if use_graph else self._split_plan(rt.cindptr, self.i_list)
 
@@ -576,8 +622,13 @@ class FitSession:
         self.fused_stats = (not names) and (not use_graph)
         if self.fused_stats:
             base = torch.zeros(6, dtype=f64, device=dev)
-            if shard.rank == 0 or not shard.active:
+            if slab:
+                # every rank adds the share of the rows IT owns and nobody rated
+                ue = rt.row_ids_u.long()[u_order[u_nonempty:].long()]
+                ie = rt.row_ids_i.long()[i_order[i_nonempty:].long()]
+            else:
                 ue, ie = u_order[u_nonempty:].long(), i_order[i_nonempty:].long()
+            if slab or shard.rank == 0 or not shard.active:
                 base[2] = U_d.index_select(0, ue).double().pow(2).sum()
                 base[3] = V_d.index_select(0, ie).double().pow(2).sum()
                 base[4] = self.b_u_d.index_select(0, ue).double().pow(2).sum()
@@ -595,6 +646,36 @@ class FitSession:
               "compose_z")
         self.launches += 1
 
+    def _fast_path(self, factor_mode: bool) -> int:
+        """Gram path the library's AUTO rule / the caller's choice gives the fast list (include/b200als.h)."""
+        gp = self.model.gram_path
+        if factor_mode or gp == _lib.PATH_FFMA or self.ld not in (64, 128):
+            return _lib.PATH_FFMA
+        return _lib.PATH_UMMA if (gp == _lib.PATH_UMMA or 2 * self.k > self.ld) else _lib.PATH_FFMA
+
+    def _precision_split(self, indptr, rows, reg, reg_row, ids, factor_mode):
+        """(fast list, float64 list or None) of a half-step's schedule — see PRECISE_RIDGE."""
+        prec = self.model.precision
+        if prec not in ("auto", "f32", "f64"):
+            raise ValueError(f"precision={prec!r}: expected 'auto', 'f32' or 'f64'")
+        if prec == "f32" or rows.numel() == 0:
+            return rows, None
+        if prec == "f64":
+            return rows[:0].contiguous(), rows
+        thr = PRECISE_RIDGE[self._fast_path(factor_mode)]
+        r64 = rows.to(torch.int64)
+        few = (indptr[r64 + 1] - indptr[r64]) < PRECISE_COUNT_FACTOR * self.k
+        if reg_row is None:
+            if not reg < thr:
+                return rows, None
+            mask = few
+        else:
+            g = ids.to(torch.int64)[r64] if ids is not None else r64
+            mask = few & (reg_row[g] < thr)
+        if not bool(mask.any()):
+            return rows, None
+        return rows[~mask].contiguous(), rows[mask].contiguous()
+
     def _split_plan(self, indptr, rows):
         """Long rows of a schedule cut into pieces for the tcgen05 path (b200als_split_plan_build); None if
         the path is not in use or no row can exceed the threshold."""
@@ -604,14 +685,19 @@ class FitSession:
         if model.gram_path == _lib.PATH_AUTO and 2 * self.k <= self.ld:
             return None
         r64 = rows.to(torch.int64)
-        nnz_list = int((indptr[r64 + 1] - indptr[r64]).sum().item())
+        cnt = indptr[r64 + 1] - indptr[r64]
+        thresh = model.split_rows or lib.b200als_split_default(0)
+        piece = model.split_piece or (lib.b200als_split_default(1) if not model.split_rows else 0)
+        nnz_list, n_long = (int(x) for x in torch.stack([cnt.sum(), (cnt > thresh).sum()]).tolist())
+        if n_long == 0:
+            return None
         need = C.c_size_t(0)
-        check(lib.b200als_split_plan_bytes(self.k, rows.numel(), nnz_list, model.split_rows, model.split_piece,
-                                           C.byref(need)), "split_plan_bytes")
+        check(lib.b200als_split_plan_bytes(self.k, rows.numel(), nnz_list, thresh, piece, n_long, C.byref(need)),
+              "split_plan_bytes")
         mem = torch.empty(max(need.value, 256), dtype=torch.uint8, device=self.dev)
         plan = _lib.SplitPlan()
-        check(lib.b200als_split_plan_build(ptr(indptr), ptr(rows), rows.numel(), nnz_list, self.k, model.split_rows,
-                                           model.split_piece, ptr(mem), mem.numel(), C.byref(plan), self._stream()),
+        check(lib.b200als_split_plan_build(ptr(indptr), ptr(rows), rows.numel(), nnz_list, self.k, thresh, piece,
+                                           n_long, ptr(mem), mem.numel(), C.byref(plan), self._stream()),
               "split_plan_build")
         if not plan.items:
             return None
@@ -619,10 +705,11 @@ class FitSession:
         return plan
 
     def _step(self, indptr, indices, vals, n_rows, rows, F, n_f_rows, bias_other, reg, reg_row, lamb, X, bias_own,
-              mode, stats=None, split=None, norms=None, peers=None):
+              mode, stats=None, split=None, norms=None, peers=None, row_ids=None, path=None):
         a = StepArgs()
+        a.row_ids = ptr(row_ids)
         a.struct_bytes = C.sizeof(StepArgs)
-        a.k, a.mode, a.path = self.k, mode, self.model.gram_path
+        a.k, a.mode, a.path = self.k, mode, (self.model.gram_path if path is None else path)
         a.n_rows = n_rows
         a.indptr, a.indices, a.vals = ptr(indptr), ptr(indices), ptr(vals)
         a.rows, a.n_list = ptr(rows), rows.numel()
@@ -677,10 +764,18 @@ class FitSession:
         self._mark("user")
         peers = self.peers
         model.last_paths["user"] = self._step(
-            rt.indptr, rt.indices, rt.vals, m, self.u_list, self.Z_d, n, self.b_i_d, self.reg_user, None,
+            rt.indptr, rt.indices, rt.vals, rt.indptr.numel() - 1, self.u_list, self.Z_d, n, self.b_i_d, self.reg_user, None,
             self.lam_bu, self.U_d, self.b_u_d, _lib.STEP_SOLVE, split=self.u_split,
             norms=(self.acc.data_ptr() + 16) if fused else None,
-            peers=(peers["U"], peers["b_u"]) if peers else None)
+            peers=(peers["U"], peers["b_u"]) if peers else None, row_ids=self.u_ids)
+        if self.u_f64 is not None:                      # the rows float32 cannot resolve: same update in float64
+            p64 = self._step(
+                rt.indptr, rt.indices, rt.vals, rt.indptr.numel() - 1, self.u_f64, self.Z_d, n, self.b_i_d,
+                self.reg_user, None, self.lam_bu, self.U_d, self.b_u_d, _lib.STEP_SOLVE,
+                norms=(self.acc.data_ptr() + 16) if fused else None,
+                peers=(peers["U"], peers["b_u"]) if peers else None, row_ids=self.u_ids, path=_lib.PATH_F64)
+            if self.u_list.numel() == 0:
+                model.last_paths["user"] = p64
         if shard.active:
             if peers:
                 shard.order_ranks(self._token)      # every rank's rows of U, b_u have landed in every replica
@@ -693,6 +788,12 @@ class FitSession:
             model.last_paths["item"] = self._step(
                 rt.cindptr, rt.cindices, rt.cvals, n, self.i_list, self.U_d, m, self.b_u_d, 0.0,
                 self.reg_item_d, self.lam_bi, self.V_d, self.b_i_d, _lib.STEP_FACTOR)
+            if self.i_f64 is not None:
+                p64 = self._step(rt.cindptr, rt.cindices, rt.cvals, n, self.i_f64, self.U_d, m, self.b_u_d, 0.0,
+                                 self.reg_item_d, self.lam_bi, self.V_d, self.b_i_d, _lib.STEP_FACTOR,
+                                 path=_lib.PATH_F64)
+                if self.i_list.numel() == 0:
+                    model.last_paths["item"] = p64
             lp = self.level_ptr
             for lv in range(lp.size - 1):
                 lo, hi = int(lp[lv]), int(lp[lv + 1])
@@ -705,11 +806,19 @@ class FitSession:
             # A10 fused: with Z == V and no sweep after it, the item step sees every residual of
             # the iteration's final state, so it accumulates sum d / sum d^2 itself
             model.last_paths["item"] = self._step(
-                rt.cindptr, rt.cindices, rt.cvals, n, self.i_list, self.U_d, m, self.b_u_d, 0.0,
+                rt.cindptr, rt.cindices, rt.cvals, rt.cindptr.numel() - 1, self.i_list, self.U_d, m, self.b_u_d, 0.0,
                 self.reg_item_d, self.lam_bi, self.V_d, self.b_i_d, _lib.STEP_SOLVE,
                 stats=self.acc if fused else None, split=self.i_split,
                 norms=(self.acc.data_ptr() + 24) if fused else None,
-                peers=(peers["V"], peers["b_i"]) if peers else None)
+                peers=(peers["V"], peers["b_i"]) if peers else None, row_ids=self.i_ids)
+            if self.i_f64 is not None:
+                p64 = self._step(
+                    rt.cindptr, rt.cindices, rt.cvals, rt.cindptr.numel() - 1, self.i_f64, self.U_d, m, self.b_u_d,
+                    0.0, self.reg_item_d, self.lam_bi, self.V_d, self.b_i_d, _lib.STEP_SOLVE,
+                    stats=self.acc if fused else None, norms=(self.acc.data_ptr() + 24) if fused else None,
+                    peers=(peers["V"], peers["b_i"]) if peers else None, row_ids=self.i_ids, path=_lib.PATH_F64)
+                if self.i_list.numel() == 0:
+                    model.last_paths["item"] = p64
             if shard.active and not peers:
                 shard.exchange_rows(self.V_d, self.i_plan)
                 shard.exchange_rows(self.b_i_d, self.i_plan)

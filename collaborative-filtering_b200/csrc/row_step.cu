@@ -2,6 +2,7 @@
 // Gram path that fits k: tcgen05 (row_step_umma.cuh) for k in {64, 128},
 // register-tiled FFMA (row_step_ffma.cuh) otherwise; and the Gauss–Seidel
 // Laplacian level solve (A8).
+#include "row_step_f64.cuh"
 #include "row_step_ffma.cuh"
 #include "row_step_umma.cuh"
 
@@ -121,20 +122,22 @@ int b200als_step_workspace_bytes(int32_t k, int32_t path, int64_t n_f_rows, size
 
 int b200als_last_path(void) { return g_last_path; }
 
+int b200als_split_default(int32_t which) { return which == 0 ? B200ALS_SPLIT_ROWS_DEFAULT : B200ALS_SPLIT_PIECE_DEFAULT; }
+
 int b200als_split_plan_bytes(int32_t k, int64_t n_list, int64_t nnz, int32_t split_rows, int32_t split_piece,
-                             size_t* bytes_host) {
+                             int64_t n_long, size_t* bytes_host) {
     ALS_CHECK_ARG(bytes_host, "null");
     ALS_CHECK_ARG(k >= 1 && k <= 128, "k out of range (the tcgen05 path covers k <= 128)");
     ALS_CHECK_ARG(n_list >= 0 && n_list < (1ll << 31) && nnz >= 0, "count out of range");
     k = umma_padded_k(k);
     SplitLayout L;
-    split_layout(k, n_list, nnz, split_rows, split_piece, 256, L);
+    split_layout(k, n_list, nnz, split_rows, split_piece, n_long, 256, L);
     *bytes_host = L.total;
     return B200ALS_OK;
 }
 
 int b200als_split_plan_build(const int64_t* indptr, const int32_t* rows, int64_t n_list, int64_t nnz, int32_t k,
-                             int32_t split_rows, int32_t split_piece, void* plan_mem, size_t plan_bytes,
+                             int32_t split_rows, int32_t split_piece, int64_t n_long, void* plan_mem, size_t plan_bytes,
                              b200als_split_plan* plan_host, b200als_stream_t stream) {
     ALS_CHECK_ARG(indptr && plan_host, "null");
     ALS_CHECK_ARG(k >= 1 && k <= 128, "k out of range (the tcgen05 path covers k <= 128)");
@@ -143,7 +146,7 @@ int b200als_split_plan_build(const int64_t* indptr, const int32_t* rows, int64_t
     memset(plan_host, 0, sizeof(*plan_host));
     plan_host->n_list = n_list;
     SplitLayout L;
-    if (!split_layout(k, n_list, nnz, split_rows, split_piece, 256, L)) return B200ALS_OK;   // nothing can be split
+    if (!split_layout(k, n_list, nnz, split_rows, split_piece, n_long, 256, L)) return B200ALS_OK;   // nothing can be split
     if (!plan_mem || plan_bytes < L.total) {
         set_error("b200als_split_plan_build: plan memory %zu < required %zu", plan_bytes, L.total);
         return B200ALS_E_WORKSPACE;
@@ -168,7 +171,7 @@ int b200als_row_step(const b200als_step_args* a, b200als_stream_t stream) {
     }
     int path = a->path;
     // FACTOR mode (graph sweep) stores the Cholesky factor from the tile solver: FFMA path only
-    if (path == B200ALS_PATH_AUTO || a->mode == B200ALS_STEP_FACTOR)
+    if (path != B200ALS_PATH_F64 && (path == B200ALS_PATH_AUTO || a->mode == B200ALS_STEP_FACTOR))
         path = (a->mode == B200ALS_STEP_SOLVE && umma_preferred(a->k, a->ldf)) ? B200ALS_PATH_UMMA : B200ALS_PATH_FFMA;
     g_last_path = path;
     size_t need = 256;
@@ -212,6 +215,7 @@ int b200als_row_step(const b200als_step_args* a, b200als_stream_t stream) {
         }
         return launch_umma(p, a->n_f_rows, a->split, static_cast<char*>(a->workspace), a->workspace_bytes, s);
     }
+    if (path == B200ALS_PATH_F64) return launch_f64(p, s);
     return dispatch_ffma(p, s);
 }
 

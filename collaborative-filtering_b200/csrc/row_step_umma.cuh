@@ -618,21 +618,28 @@ __device__ __forceinline__ void umma_role_solver(const RowStepParams& p, const U
         bool from_slot = false;
         float* gs = nullptr;
         if (any_part) {
-            if (part) gs = p.slot_acc + (size_t)slot * split_slot_floats(K) + (size_t)r * SLOT_LD;
+            // The slot is accumulated TRANSPOSED: thread r adds its entry (r, c) at [c][r], so the lanes of a warp
+            // (consecutive rows r) hit consecutive addresses and each warp-level red.add is one 128-byte (k = 64:
+            // two 64-byte) L2 transaction — adding at [r][c] was 32 scattered 4-byte atomics per instruction and
+            // made a piece's flush cost ~57 k cycles.  The normal matrix is symmetric, so reading the slot back
+            // row-wise ([r][c..c+3], float4) returns the sums of the entries (c, r) = (r, c).  c and s are rows K
+            // and K + 1 of the slot, (sum q, sum q^2) follow.
+            float* sb = p.slot_acc + (size_t)slot * split_slot_floats(K);
+            if (part) gs = sb + (size_t)r * SLOT_LD;
 #pragma unroll 1
             for (int c0 = 0; c0 < K; c0 += 16) {
                 float v[16];
                 ptx::tmem_ld16(trow + c0, v);
                 if (part) {
 #pragma unroll
-                    for (int i = 0; i < 16; ++i) atomicAdd(gs + c0 + i, v[i]);
+                    for (int i = 0; i < 16; ++i) atomicAdd(sb + (size_t)(c0 + i) * SLOT_LD + r, v[i]);
                 }
             }
             if (part) {
-                atomicAdd(gs + K, c_r);
-                atomicAdd(gs + K + 1, s_r);
+                atomicAdd(sb + (size_t)K * SLOT_LD + r, c_r);
+                atomicAdd(sb + (size_t)(K + 1) * SLOT_LD + r, s_r);
                 if (q == 0 && seg == 0) {
-                    float* tq = p.slot_acc + (size_t)slot * split_slot_floats(K) + (size_t)K * SLOT_LD;
+                    float* tq = sb + (size_t)(K + 2) * SLOT_LD;
                     atomicAdd(tq, tsum);
                     atomicAdd(tq + 1, qq);
                 }
@@ -647,9 +654,9 @@ __device__ __forceinline__ void umma_role_solver(const RowStepParams& p, const U
             from_slot = part && (lds_s32(lastf_a) != 0);
             if (from_slot) {
                 __threadfence();
-                c_r = __ldcg(gs + K);
-                s_r = __ldcg(gs + K + 1);
-                const float* tq = p.slot_acc + (size_t)slot * split_slot_floats(K) + (size_t)K * SLOT_LD;
+                c_r = __ldcg(sb + (size_t)K * SLOT_LD + r);
+                s_r = __ldcg(sb + (size_t)(K + 1) * SLOT_LD + r);
+                const float* tq = sb + (size_t)(K + 2) * SLOT_LD;
                 tsum = __ldcg(tq);
                 qq = __ldcg(tq + 1);
                 cnt = (int)(p.indptr[row + 1] - p.indptr[row]);

@@ -21,10 +21,10 @@
 namespace b200als {
 
 #ifndef B200ALS_SPLIT_ROWS_DEFAULT
-#define B200ALS_SPLIT_ROWS_DEFAULT 12288
+#define B200ALS_SPLIT_ROWS_DEFAULT 6144
 #endif
 #ifndef B200ALS_SPLIT_PIECE_DEFAULT
-#define B200ALS_SPLIT_PIECE_DEFAULT 8192
+#define B200ALS_SPLIT_PIECE_DEFAULT 4096
 #endif
 
 struct SplitLayout {                 // byte offsets inside the step workspace (after the bf16 copy)
@@ -33,10 +33,11 @@ struct SplitLayout {                 // byte offsets inside the step workspace (
     int thresh, piece, slot_floats;
 };
 
-__host__ __device__ constexpr int split_slot_floats(int k) { return k * (k + 4) + 4; }
+// slot: (k + 2) rows of k + 4 floats — the normal matrix, then c, then s — followed by (sum q, sum q^2, -, -)
+__host__ __device__ constexpr int split_slot_floats(int k) { return (k + 2) * (k + 4) + 4; }
 
 static inline bool split_layout(int k, int64_t n_list, int64_t nnz, int32_t split_rows, int32_t split_piece,
-                                size_t base, SplitLayout& L) {
+                                int64_t n_long, size_t base, SplitLayout& L) {
     L = SplitLayout{};
     L.total = base;
     if (split_rows < 0 || nnz <= 0 || n_list <= 0) return false;
@@ -54,6 +55,7 @@ static inline bool split_layout(int k, int64_t n_list, int64_t nnz, int32_t spli
     L.piece = piece;
     L.max_slots = nnz / L.thresh;
     if (L.max_slots > n_list) L.max_slots = n_list;
+    if (n_long >= 0 && n_long < L.max_slots) L.max_slots = n_long;   // the caller counted the rows above the threshold
     if (L.max_slots == 0) return false;                      // no row can exceed the threshold
     L.max_items = n_list + nnz / piece + L.max_slots;
     L.slot_floats = split_slot_floats(k);

@@ -90,6 +90,19 @@ class Shard:
         perm = torch.where(valid, rows, torch.full_like(rows, dummy_row))
         return ExchangePlan(perm, perm[self.rank * cnt:(self.rank + 1) * cnt].contiguous(), cnt)
 
+    def plan_exchange_ids(self, my_ids: torch.Tensor, dummy_row: int) -> ExchangePlan:
+        """Exchange plan when every rank already knows WHICH rows it solves (slab storage): the id lists are
+        all-gathered once, padded to the longest with the dummy row."""
+        n_mine = torch.tensor([int(my_ids.numel())], dtype=torch.int64, device=my_ids.device)
+        counts = [torch.zeros_like(n_mine) for _ in range(self.world)]
+        td.all_gather(counts, n_mine, group=self.group)
+        cnt = max(max(int(c.item()) for c in counts), 1)
+        mine = torch.full((cnt,), dummy_row, dtype=torch.int64, device=my_ids.device)
+        mine[:my_ids.numel()] = my_ids.to(torch.int64)
+        parts = [torch.empty_like(mine) for _ in range(self.world)]
+        td.all_gather(parts, mine, group=self.group)
+        return ExchangePlan(torch.cat(parts, 0), mine, cnt)
+
     # ---- collectives -------------------------------------------------------
     def exchange_rows(self, full: torch.Tensor, plan: ExchangePlan) -> None:
         """Every rank's solved rows of `full` ([rows(+1 dummy), ...]) land in every replica."""

@@ -94,3 +94,51 @@ def cv_score(make_model, flat_sorted: torch.Tensor, vals: torch.Tensor, shape, f
         hist = list(model.history.get("train_rmse", []))
         out.append({"rmse": rmse, "iters": len(hist), "train_rmse": hist, "bin_rmse": per_bin})
     return out
+
+
+def folds_of_rank(n_folds: int, rank: int, world: int):
+    """Fold indices rank `rank` of `world` evaluates: rank, rank + world, ... (every fold exactly once)."""
+    return list(range(rank, n_folds, world))
+
+
+def cv_score_fold_parallel(make_model, flat_sorted, vals, shape, folds, features=None, tol=1e-4, min_iters=10,
+                           verbose=0, item_bin=None, n_bins: int = N_POP_BINS, group=None):
+    """The same K-fold loop with the folds spread over the GPUs of the box — one fold per GPU at a time, each fit
+    un-sharded on its own device (second half: the reference's real throughput lever is
+    trials x folds, tune_params.py:341-421, and a bundled-shape fit cannot fill one B200, let alone eight).
+
+    Call it from every rank of an initialised torch.distributed group (torchrun, one process per GPU) with the
+    same arguments; `flat_sorted` / `vals` may be host arrays (each rank uploads its copy) or tensors on the rank's
+    device.  Fold f is evaluated by rank f % world; the per-fold dicts are exchanged with one all_gather_object and
+    every rank returns the full list in fold order — identical to `cv_score`'s on one GPU, fold by fold, because
+    each fold's fit is the same single-GPU fit.  Without a process group it is `cv_score`."""
+    import torch.distributed as td
+    if not (td.is_available() and td.is_initialized()):
+        return cv_score(make_model, torch.as_tensor(flat_sorted).cuda(), torch.as_tensor(vals).cuda(), shape, folds,
+                        features, tol, min_iters, verbose, item_bin, n_bins)
+    rank, world = td.get_rank(group), td.get_world_size(group)
+    mine = folds_of_rank(len(folds), rank, world)
+    res = []
+    if mine:
+        dev = torch.device("cuda", torch.cuda.current_device())
+        f_d = torch.as_tensor(flat_sorted).to(device=dev, dtype=torch.int64)
+        v_d = torch.as_tensor(vals).to(device=dev, dtype=torch.float32)
+        res = cv_score(make_model, f_d, v_d, shape, [folds[f] for f in mine], features, tol, min_iters, verbose,
+                       item_bin, n_bins)
+    return merge_fold_results(list(zip(mine, res)), len(folds), group)
+
+
+def merge_fold_results(mine, n_folds: int, group=None):
+    """all_gather_object of [(fold index, result)] lists -> results in fold order on every rank."""
+    import torch.distributed as td
+    box = [None] * td.get_world_size(group)
+    td.all_gather_object(box, mine, group=group)
+    out = [None] * n_folds
+    for part in box:
+        for f, r in part:
+            if out[f] is not None:
+                raise RuntimeError(f"fold {f} was evaluated twice")
+            out[f] = r
+    if any(r is None for r in out):
+        raise RuntimeError("a fold was not evaluated by any rank")
+    return out

@@ -146,6 +146,10 @@ int b200als_compose_z(const float* V, int64_t ldv, int64_t n, int32_t k,
 #define B200ALS_PATH_AUTO   0   /* tcgen05 when ldf in {64,128} and ldf/2 < k <= ldf (zero-padded rows), else FFMA */
 #define B200ALS_PATH_FFMA   1
 #define B200ALS_PATH_UMMA   2
+#define B200ALS_PATH_F64    3   /* normal matrix accumulated, factored and solved in float64 (any k <= 160, both modes):
+                                   for rows whose ridge is too small for float32 — fewer ratings than factors and
+                                   lambda below ~0.1, a quarter of the tuner's range (tune_params.py:102-103) — and
+                                   for callers who want the reference's arithmetic; never chosen by AUTO */
 
 /* ------------------------------------------------------------------------
  * Long rows (tcgen05 path).  One SM consumes a row's ratings 32 per pipeline stage, so a very popular
@@ -153,8 +157,14 @@ int b200als_compose_z(const float* V, int64_t ldv, int64_t n, int32_t k,
  * rows with more than split_rows ratings into pieces of about split_piece ratings that different SMs
  * accumulate: the partial normal matrices [A | c s] are added into a per-row slot in global memory and
  * the SM adding the last piece factors and solves — same sums, different summation order.
- *   split_rows: 0 = default (a quarter of one SM's share of nnz, at least 8192), < 0 = never split
+ *   split_rows: 0 = default (rows of more than 6144 ratings, pieces of 4096), < 0 = never split
  *   split_piece: ratings per piece, rounded up to 32; 0 = split_rows / 2
+ * The defaults are ABSOLUTE lengths on purpose.  The tensor core adds into its float32 accumulator with
+ * truncation: a chain of n accumulation steps (16 ratings each) biases the sums low by ~n 2^-24 relative — measured
+ * on B200 at the Netflix shape against the float64 oracle: 1.4e-3 ... 2.1e-3 relative error of the solved rows of
+ * 3.4e5 ... 4.8e5-rating items accumulated in one chain, 2.5e-5 with 8192-rating pieces, 6e-6 with 2048
+ * (profiles/r02_v1_scale_parity_c4*.json).  A fixed piece bounds the chain and makes the summation tree a function
+ * of the row alone, not of how many ranks share the launch.
  *   nnz: ratings held by the listed rows (bounds the number of slots)
  * plan_mem is caller-owned device memory of b200als_split_plan_bytes(); *plan_host describes it.
  * ---------------------------------------------------------------------- */
@@ -163,15 +173,19 @@ typedef struct b200als_split_plan {
     const int32_t* hdr;          /* device: [0] items, [1] split rows */
     const int32_t* slot_np;      /* pieces per split row */
     int32_t*       slot_ctr;     /* pieces accumulated so far (zeroed by every step) */
-    float*         slot_acc;     /* per slot: k x (k + 4) [A | c s - -], then t, qq, -, - (zeroed by every step) */
+    float*         slot_acc;     /* per slot: (K + 2) x (K + 4) floats [A (stored transposed: it is symmetric); c; s], then t, qq, -, -
+                                    (K = padded width 64 / 128; zeroed by every step) */
     int64_t        n_list;       /* list entries the plan was built for */
     int32_t        slot_floats, thresh, piece, reserved;
 } b200als_split_plan;
+/* n_long: how many listed rows hold more than split_rows ratings (sizes the accumulator slots exactly), or -1 for
+ * the bound nnz / split_rows.  b200als_split_default(0 | 1) returns the default split_rows | split_piece. */
+int b200als_split_default(int32_t which);
 int b200als_split_plan_bytes(int32_t k, int64_t n_list, int64_t nnz, int32_t split_rows, int32_t split_piece,
-                             size_t* bytes_host);
+                             int64_t n_long, size_t* bytes_host);
 /* returns 0 and fills *plan_host; plan_host->items == NULL when no row can exceed the threshold */
 int b200als_split_plan_build(const int64_t* indptr, const int32_t* rows, int64_t n_list, int64_t nnz, int32_t k,
-                             int32_t split_rows, int32_t split_piece, void* plan_mem, size_t plan_bytes,
+                             int32_t split_rows, int32_t split_piece, int64_t n_long, void* plan_mem, size_t plan_bytes,
                              b200als_split_plan* plan_host, b200als_stream_t stream);
 
 typedef struct b200als_step_args {

@@ -3,7 +3,7 @@ exception surface of the solve, and the reference drivers' dense call sequence o
 
   * lambda_u = lambda_v over the tuner's log-uniform range [1e-4, 1e4] (scripts/tune_params.py:102-103) with rows
     that hold FEWER ratings than factors (the Gram is rank deficient and only the ridge keeps it SPD), at
-    k = 32 (FFMA path), 64 and 128 (tcgen05 path);
+    k = 32 (FFMA path), 64 and 128 (tcgen05 path) — the rows float32 cannot resolve take the float64 half-step;
   * the `lambda_w = 0` ablation form (scripts/evaluate_models.py:413-426): features passed, W_f regularised by EPS alone;
   * a system that is not positive definite raises numpy.linalg.LinAlgError like scripts/helpers.py:19;
   * k = 50 at the bundled shape; a graph + features model at k = 64 (FACTOR mode keeps the item step on FFMA);
@@ -40,8 +40,11 @@ def _short_row_problem(seed, m=400, n=250, per_row=20):
 
 
 @pytest.mark.parametrize("k", [32, 64, 128])
-@pytest.mark.parametrize("lam", [1e-2, 1.0, 1e4])
+@pytest.mark.parametrize("lam", [1e-4, 1e-2, 1.0, 1e4])
 def test_lambda_range_short_rows_vs_oracle(cuda_device, k, lam):
+    """The whole range of the tuner's lambda at rows with fewer ratings than factors.  Below ~0.1 the float32 paths
+    cannot hold 1e-3 (measured: 2e-2 at lambda = 1e-2 on the tcgen05 path, loss of positive definiteness at 1e-4);
+    `precision = "auto"` sends exactly those rows — small ridge AND few ratings — to the float64 half-step."""
     import b200als
     flat, vals, m, n = _short_row_problem(seed=100 + k)
     cfg = b200als.ALSConfig(core=b200als.CoreConfig(n_factors=k, n_iters=3, lambda_u=lam, lambda_v=lam),
@@ -50,31 +53,48 @@ def test_lambda_range_short_rows_vs_oracle(cuda_device, k, lam):
     model = b200als.ALS(cfg).fit_coo(flat, vals, (m, n), tol=None, verbose=0, sorted_input=True)
     errs = {a: rel_err(getattr(model, a), getattr(o, a)) for a in ("U", "V", "b_u", "b_i")}
     d = float(np.abs(np.asarray(model.history["train_rmse"]) - np.asarray(o.history["train_rmse"])).max())
-    print(f"k={k} lambda={lam:g}: {errs} dRMSE={d:.2e}")
+    print(f"k={k} lambda={lam:g}: {errs} dRMSE={d:.2e} paths={model.last_paths}")
     assert max(errs.values()) < FACTOR_TOL, errs
     assert d < RMSE_TOL
+    if lam >= 1.0:
+        want = b200als._lib.PATH_UMMA if k > 32 else b200als._lib.PATH_FFMA
+        assert model.last_paths == {"user": want, "item": want}          # nothing left the fast paths
 
 
-@pytest.mark.parametrize("k", [32, 64, 128])
-def test_smallest_lambda_short_rows(cuda_device, k):
-    """lambda = 1e-4 with cnt < k: the normal matrices have condition numbers of 1e5..1e6 — beyond what a float32
-    Gram can resolve to 1e-3 in the FACTORS (the ridge is the size of the float32 rounding of the Gram itself), so
-    what is held here is what the model is used for: the fit runs, stays finite, and its train-RMSE curve and its
-    predictions on the observed entries follow the float64 reference's.  (The measured factor error is printed.)"""
+@pytest.mark.parametrize("k", [8, 50, 128, 150])
+def test_float64_path_every_row(cuda_device, k):
+    """precision = "f64": every row through the float64 half-step — the reference's arithmetic, float32 storage."""
     import b200als
-    flat, vals, m, n = _short_row_problem(seed=200 + k)
-    cfg = b200als.ALSConfig(core=b200als.CoreConfig(n_factors=k, n_iters=3, lambda_u=1e-4, lambda_v=1e-4),
+    from b200als.synth import synth_ratings
+    m, n, nnz = 300, 200, 9000
+    flat, vals = synth_ratings(m, n, nnz, seed=k)
+    cfg = b200als.ALSConfig(core=b200als.CoreConfig(n_factors=k, n_iters=3, lambda_u=4.0, lambda_v=3.0,
+                                                    pop_reg_mode="inverse_sqrt"),
                             biases=b200als.BiasesConfig(lambda_bu=2.0, lambda_bi=2.5))
     o = _oracle(cfg, flat, vals, m, n)
-    model = b200als.ALS(cfg).fit_coo(flat, vals, (m, n), tol=None, verbose=0, sorted_input=True)
-    errs = {a: rel_err(getattr(model, a), getattr(o, a)) for a in ("U", "V", "b_u", "b_i")}
-    hist = np.asarray(model.history["train_rmse"])
-    d = float(np.abs(hist - np.asarray(o.history["train_rmse"])).max())
-    print(f"k={k} lambda=1e-4: {errs} dRMSE={d:.2e}")
-    assert np.isfinite(hist).all() and all(np.isfinite(getattr(model, a)).all() for a in ("U", "V", "b_u", "b_i"))
-    assert d < 5e-3
-    pp = model.predict_pairs(flat // n, flat % n)
-    assert abs(np.sqrt(np.mean((pp - vals) ** 2)) - np.sqrt(np.mean((o.predict_pairs(flat // n, flat % n) - vals) ** 2))) < 5e-3
+    model = b200als.ALS(cfg)
+    model.precision = "f64"
+    model.fit_coo(flat, vals, (m, n), tol=None, verbose=0, sorted_input=True)
+    assert model.last_paths == {"user": b200als._lib.PATH_F64, "item": b200als._lib.PATH_F64}
+    for a in ("U", "V", "b_u", "b_i"):
+        assert rel_err(getattr(model, a), getattr(o, a)) < 2e-6, a
+    assert np.abs(np.asarray(model.history["train_rmse"]) - np.asarray(o.history["train_rmse"])).max() < 1e-6
+    for key, arr in (("U_norm", o.U), ("V_norm", o.V), ("bu_norm", o.b_u), ("bi_norm", o.b_i)):
+        assert abs(model.history[key][-1] - np.linalg.norm(arr)) < 1e-5 * max(np.linalg.norm(arr), 1.0)
+
+
+def test_full_model_small_lambda_float64_factor_mode(cuda_device):
+    """Graph + features with a small lambda_v: the Gauss-Seidel item step factors its short rows in float64."""
+    import b200als
+    c = load_case("small_full")
+    cfgd = dict(c.cfgd, core=dict(c.cfgd["core"], lambda_u=0.01, lambda_v=0.01, n_iters=3))
+    cfg = make_cfg(cfgd)
+    o = _oracle(cfg, c.flat, c.vals, c.m, c.n, c.features, c.lambda_w)
+    model = b200als.ALS(config=cfg, lambda_w=c.lambda_w).fit_coo(c.flat, c.vals, (c.m, c.n), features=c.features,
+                                                                 tol=None, verbose=0)
+    for a in ("U", "V", "b_u", "b_i"):
+        assert rel_err(getattr(model, a), getattr(o, a)) < FACTOR_TOL, a
+    assert np.abs(np.asarray(model.history["train_rmse"]) - np.asarray(o.history["train_rmse"])).max() < RMSE_TOL
 
 
 def test_lambda_w_zero_ablation_form(cuda_device):

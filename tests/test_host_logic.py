@@ -216,6 +216,15 @@ for b in bufs:
 rng = np.random.default_rng(42)
 for b, sh, d in zip(bufs, shapes, dts):
     assert np.array_equal(b.numpy(), rng.normal(scale=0.1, size=sh).astype(d)), s.rank
+# fold-per-GPU cross-validation: every fold evaluated once, results in fold order on every rank
+from b200als.evaluate import folds_of_rank, merge_fold_results
+mine = folds_of_rank(5, s.rank, 2)
+assert mine == ([0, 2, 4] if s.rank == 0 else [1, 3])
+got = merge_fold_results([(f, {"rmse": 0.5 + f, "by": s.rank}) for f in mine], 5)
+assert [g["rmse"] for g in got] == [0.5, 1.5, 2.5, 3.5, 4.5] and [g["by"] for g in got] == [0, 1, 0, 1, 0]
+# peer-mapped exchange is a CUDA facility: on CPU tensors the collective decision is "all-gather"
+assert s.share_replicas(dict(U=torch.zeros(4, 4))) is None
+tok = torch.zeros(1); s.order_ranks(tok)
 acc = torch.tensor([1.0 + s.rank, 10.0], dtype=torch.float64)
 s.all_reduce_sum(acc)
 assert acc.tolist() == [3.0, 20.0]
@@ -241,3 +250,54 @@ def test_row_sharding_collectives_gloo_world2(tmp_path):
     for p in procs:
         out, _ = p.communicate(timeout=180)
         assert p.returncode == 0, out.decode()
+
+
+def test_rating_slabs_partition_matches_csr_csc():
+    """slab.slabs_from_coo / synth_slabs_torch (CPU tensors): the slabs of all ranks together are the CSR and CSC of
+    the whole matrix (scripts/als.py:338-339 order inside every row), local pointers, global ids."""
+    import torch
+    import als_oracle
+    from b200als.slab import owned_count, slabs_from_coo, synth_slabs_torch
+    from b200als.synth import synth_ratings
+    m, n, nnz = 53, 37, 600
+    flat, vals = synth_ratings(m, n, nnz, seed=4)
+    sp = als_oracle.csr_csc_from_flat(flat, vals, m, n)
+    rows, cols = torch.from_numpy(flat // n), torch.from_numpy(flat % n)
+    for world in (1, 2, 3, 8):
+        seen_u = seen_i = 0
+        for rank in range(world):
+            s = slabs_from_coo(rows, cols, torch.from_numpy(vals.astype(np.float32)), m, n, rank, world)
+            assert s.nnz == nnz and abs(s.vals_sum - vals.sum()) < 1e-3
+            assert s.row_ids_u.numel() == owned_count(m, rank, world) == s.indptr.numel() - 1
+            assert s.row_ids_i.numel() == owned_count(n, rank, world) == s.cindptr.numel() - 1
+            for l, u in enumerate(s.row_ids_u.tolist()):
+                assert u % world == rank
+                a, b = int(s.indptr[l]), int(s.indptr[l + 1])
+                lo, hi = sp["indptr"][u], sp["indptr"][u + 1]
+                assert np.array_equal(s.indices[a:b].numpy(), sp["indices"][lo:hi])
+                assert np.array_equal(s.vals[a:b].numpy(), sp["vals"][lo:hi].astype(np.float32))
+                seen_u += b - a
+            for l, i in enumerate(s.row_ids_i.tolist()):
+                a, b = int(s.cindptr[l]), int(s.cindptr[l + 1])
+                lo, hi = sp["cindptr"][i], sp["cindptr"][i + 1]
+                assert np.array_equal(s.cindices[a:b].numpy(), sp["cindices"][lo:hi])
+                assert np.array_equal(s.cvals[a:b].numpy(), sp["cvals"][lo:hi].astype(np.float32))
+                seen_i += b - a
+        assert seen_u == nnz and seen_i == nnz
+    # shard-wise generation: all ranks agree on one data set without exchanging it
+    world = 3
+    parts = [synth_slabs_torch(3000, 1200, 4000, seed=11, rank=r, world=world, device="cpu", n_chunks=5) for r in range(world)]
+    total = parts[0].nnz
+    assert all(p.nnz == total and p.vals_sum == parts[0].vals_sum for p in parts)
+    assert abs(total - 4000) < 400          # de-duplication loses a few per cent at this density
+    pairs_u, pairs_i = set(), set()
+    for p in parts:
+        for l, u in enumerate(p.row_ids_u.tolist()):
+            seg = p.indices[int(p.indptr[l]):int(p.indptr[l + 1])].tolist()
+            assert seg == sorted(set(seg))
+            pairs_u.update((u, i) for i in seg)
+        for l, i in enumerate(p.row_ids_i.tolist()):
+            seg = p.cindices[int(p.cindptr[l]):int(p.cindptr[l + 1])].tolist()
+            assert seg == sorted(set(seg))
+            pairs_i.update((u, i) for u in seg)
+    assert pairs_u == pairs_i and len(pairs_u) == total
