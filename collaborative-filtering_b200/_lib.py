@@ -85,6 +85,8 @@ _SIGNATURES = {
     "b200als_row_step": [C.POINTER(StepArgs), vp],
     "b200als_graph_level_solve": [C.c_int32, vp, C.c_int64, vp, vp, vp, vp, vp,
                                   C.c_float, C.c_float, vp, vp, C.c_int64, vp, vp],
+    "b200als_graph_sweep": [C.c_int32, vp, C.c_int32, C.c_int64, vp, vp, vp, vp, vp, vp,
+                            C.c_float, C.c_float, vp, vp, C.c_int64, vp, vp],
     "b200als_residual_stats": [C.c_int64, vp, vp, vp, C.c_int32, vp, C.c_int64, vp, C.c_int64,
                                vp, vp, vp, vp],
     "b200als_sumsq": [vp, C.c_int64, C.c_int64, C.c_int64, vp, vp],

@@ -488,12 +488,24 @@ class FitSession:
             # all host cores (hostrng.py).  Sharded: one rank draws with every core and the device arrays are
             # broadcast, instead of N ranks walking the same stream on 1/N of the cores each.
             if shard.rank == 0 or not shard.active:
+                # large draws land in pinned host memory (torch caches the buffers between fits): the upload is a DMA
+                pinned = []
+
+                def alloc(shape, dtype):
+                    if int(np.prod(shape)) < (1 << 20) or not dev.type == "cuda":
+                        return np.empty(shape, dtype=dtype)
+                    t = torch.empty(tuple(shape), dtype=torch.float32 if np.dtype(dtype) == np.float32 else torch.float64,
+                                    pin_memory=True)
+                    pinned.append(t)
+                    return t.numpy()
                 draws = _hostrng.normal_stream(model.random_state, [(m, k), (n, k)] + [(features[nm].shape[1], k)
                                                                                       for nm in names],
                                                [np.float32, np.float32] + [np.float64] * len(names), SCALE_FACTOR,
-                                               n_threads=_hostrng.host_threads(shared=False))
-                U_d[:m, :k] = torch.from_numpy(draws[0]).to(dev)
-                V_d[:n, :k] = torch.from_numpy(draws[1]).to(dev)
+                                               n_threads=_hostrng.host_threads(shared=False), alloc=alloc)
+                U_d[:m, :k].copy_(torch.from_numpy(draws[0]), non_blocking=True)
+                V_d[:n, :k].copy_(torch.from_numpy(draws[1]), non_blocking=True)
+                torch.cuda.current_stream().synchronize() if dev.type == "cuda" else None
+                del pinned
                 for f, nm in enumerate(names):
                     w0 = draws[2 + f]
                     W64_d[f].copy_(torch.from_numpy(w0.reshape(-1)).to(dev))
@@ -601,6 +613,9 @@ class FitSession:
             self.sidx_d = torch.from_numpy(sidx).to(dev)
             self.sval_d = torch.from_numpy(sval).to(dev)
             self.level_rows_d = torch.from_numpy(level_rows).to(dev)
+            self.level_ptr_d = torch.from_numpy(np.ascontiguousarray(self.level_ptr, dtype=np.int64)).to(dev)
+            self.max_level = int(np.diff(self.level_ptr).max()) if self.level_ptr.size > 1 else 0
+            self.sweep_fused = os.environ.get("B200ALS_GRAPH_SWEEP", "fused") == "fused"
             self.chol_d = torch.empty(n * k * k, dtype=f32, device=dev)
             self.aux_d = torch.empty(n * (2 * k + 2), dtype=f32, device=dev)
         else:
@@ -795,13 +810,21 @@ class FitSession:
                 if self.i_list.numel() == 0:
                     model.last_paths["item"] = p64
             lp = self.level_ptr
-            for lv in range(lp.size - 1):
-                lo, hi = int(lp[lv]), int(lp[lv + 1])
-                check(lib.b200als_graph_level_solve(
-                    k, self.level_rows_d.data_ptr() + 4 * lo, hi - lo, ptr(self.chol_d), ptr(self.aux_d),
-                    ptr(self.sptr_d), ptr(self.sidx_d), ptr(self.sval_d), float(model.alpha), self.lam_bi, None,
-                    ptr(self.V_d), ld, ptr(self.b_i_d), stream), "graph_level_solve")
+            if self.sweep_fused:
+                # all levels in one cooperative launch, a grid barrier between them
+                check(lib.b200als_graph_sweep(
+                    k, ptr(self.level_ptr_d), lp.size - 1, self.max_level, ptr(self.level_rows_d), ptr(self.chol_d),
+                    ptr(self.aux_d), ptr(self.sptr_d), ptr(self.sidx_d), ptr(self.sval_d), float(model.alpha),
+                    self.lam_bi, None, ptr(self.V_d), ld, ptr(self.b_i_d), stream), "graph_sweep")
                 self.launches += 1
+            else:
+                for lv in range(lp.size - 1):
+                    lo, hi = int(lp[lv]), int(lp[lv + 1])
+                    check(lib.b200als_graph_level_solve(
+                        k, self.level_rows_d.data_ptr() + 4 * lo, hi - lo, ptr(self.chol_d), ptr(self.aux_d),
+                        ptr(self.sptr_d), ptr(self.sidx_d), ptr(self.sval_d), float(model.alpha), self.lam_bi, None,
+                        ptr(self.V_d), ld, ptr(self.b_i_d), stream), "graph_level_solve")
+                    self.launches += 1
         else:
             # A10 fused: with Z == V and no sweep after it, the item step sees every residual of
             # the iteration's final state, so it accumulates sum d / sum d^2 itself

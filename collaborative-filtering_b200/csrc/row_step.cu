@@ -2,6 +2,8 @@
 // Gram path that fits k: tcgen05 (row_step_umma.cuh) for k in {64, 128},
 // register-tiled FFMA (row_step_ffma.cuh) otherwise; and the Gauss–Seidel
 // Laplacian level solve (A8).
+#include <cooperative_groups.h>
+
 #include "row_step_f64.cuh"
 #include "row_step_ffma.cuh"
 #include "row_step_umma.cuh"
@@ -104,6 +106,147 @@ __global__ void __launch_bounds__(128) graph_level_kernel(int k, const int32_t* 
         const float lb = lam_bias_row ? lam_bias_row[i] : lam_bias;
         b_i[i] = (ax[2 * k] - dot) / (ax[2 * k + 1] + lb);
     }
+}
+
+// ---- A8 at speed: the whole Gauss–Seidel sweep in ONE cooperative launch ------------------------
+// All levels are walked inside the kernel with a grid barrier between them (the per-level launch above costs a
+// host call + a launch per level: 140 of them per iteration on the bundled genres graph).  One warp per item of a
+// level: the item's Cholesky factor (k x k float32, stored by the FACTOR step) is staged into the warp's shared
+// memory with coalesced 16-byte loads, the right-hand side b = c - b_i s + alpha S[i,:] V is built with the live V,
+// the forward substitution runs row-wise (one coalesced shared-memory row dot + a warp reduction per unknown, no
+// column-strided global reads), the backward substitution column-wise as rank-1 updates with a shuffle broadcast.
+// y stays in registers (lane l holds entries l, l + 32, ...).  Same arithmetic order across levels as als.py:453-461:
+// S is symmetric, so an item's neighbours are always in other levels.
+template <int NCH>
+__global__ void __launch_bounds__(256) graph_sweep_kernel(int k, const int64_t* __restrict__ level_ptr, int n_levels,
+                                                          const int32_t* __restrict__ level_rows,
+                                                          const float* __restrict__ chol, const float* __restrict__ aux,
+                                                          const int64_t* __restrict__ sptr,
+                                                          const int32_t* __restrict__ sidx,
+                                                          const float* __restrict__ sval, float alpha, float lam_bias,
+                                                          const float* __restrict__ lam_bias_row, float* V,
+                                                          int64_t ldv, float* b_i, int warps_per_cta) {
+    extern __shared__ __align__(16) float sweep_sm[];
+    namespace cg = cooperative_groups;
+    cg::grid_group grid = cg::this_grid();
+    const int lane = threadIdx.x & 31, w = threadIdx.x >> 5;
+    const bool active = w < warps_per_cta;
+    float* Ls = sweep_sm + (size_t)w * k * k;
+    const int64_t gw = (int64_t)blockIdx.x * warps_per_cta + w, nw = (int64_t)gridDim.x * warps_per_cta;
+    const int kk = k * k;
+    for (int lv = 0; lv < n_levels; ++lv) {
+        const int64_t lo = level_ptr[lv], hi = level_ptr[lv + 1];
+        if (active) {
+            for (int64_t slot = lo + gw; slot < hi; slot += nw) {
+                const int64_t i = level_rows[slot];
+                const float* L = chol + (size_t)i * kk;
+                const float* ax = aux + (size_t)i * (2 * k + 2);
+                // stage the factor (kk is a multiple of 4 only when k is even: scalar tail)
+                const int kk4 = kk & ~3;
+                if ((((uintptr_t)L) & 15) == 0) {
+                    for (int e = lane * 4; e < kk4; e += 128)
+                        *reinterpret_cast<float4*>(Ls + e) = *reinterpret_cast<const float4*>(L + e);
+                    for (int e = kk4 + lane; e < kk; e += 32) Ls[e] = L[e];
+                } else {
+                    for (int e = lane; e < kk; e += 32) Ls[e] = L[e];
+                }
+                const float bold = b_i[i];
+                float y[NCH];
+#pragma unroll
+                for (int t = 0; t < NCH; ++t) {
+                    const int c = lane + 32 * t;
+                    y[t] = c < k ? ax[c] - bold * ax[k + c] : 0.0f;
+                }
+                for (int64_t e = sptr[i]; e < sptr[i + 1]; ++e) {
+                    const float sv = alpha * sval[e];
+                    const float* vj = V + (size_t)sidx[e] * ldv;
+#pragma unroll
+                    for (int t = 0; t < NCH; ++t) {
+                        const int c = lane + 32 * t;
+                        if (c < k) y[t] = fmaf(sv, vj[c], y[t]);
+                    }
+                }
+                __syncwarp();
+                // forward: L y' = y, row by row
+                for (int r = 0; r < k; ++r) {
+                    const float* Lr = Ls + r * k;
+                    float part = 0.0f;
+#pragma unroll
+                    for (int t = 0; t < NCH; ++t) {
+                        const int c = lane + 32 * t;
+                        if (c < r) part = fmaf(Lr[c], y[t], part);
+                    }
+                    part = warp_sum(part);
+#pragma unroll
+                    for (int t = 0; t < NCH; ++t)
+                        if (lane + 32 * t == r) y[t] = (y[t] - part) / Lr[r];
+                }
+                // backward: L^T x = y', column by column (rank-1 updates with row r of L)
+                for (int r = k - 1; r >= 0; --r) {
+                    const float* Lr = Ls + r * k;
+                    float mine = 0.0f;
+#pragma unroll
+                    for (int t = 0; t < NCH; ++t)
+                        if (t == (r >> 5)) mine = y[t];
+                    float xr = __shfl_sync(0xffffffffu, mine, r & 31) / Lr[r];
+#pragma unroll
+                    for (int t = 0; t < NCH; ++t) {
+                        const int c = lane + 32 * t;
+                        if (c == r) y[t] = xr;
+                        else if (c < r) y[t] = fmaf(-Lr[c], xr, y[t]);
+                    }
+                }
+                float dot = 0.0f;
+#pragma unroll
+                for (int t = 0; t < NCH; ++t) {
+                    const int c = lane + 32 * t;
+                    if (c < k) {
+                        V[(size_t)i * ldv + c] = y[t];
+                        dot = fmaf(ax[k + c], y[t], dot);
+                    }
+                }
+                dot = warp_sum(dot);
+                if (lane == 0) {
+                    const float lb = lam_bias_row ? lam_bias_row[i] : lam_bias;
+                    b_i[i] = (ax[2 * k] - dot) / (ax[2 * k + 1] + lb);
+                }
+                __syncwarp();                       // Ls is reused by this warp's next item
+            }
+        }
+        __threadfence();
+        grid.sync();                                // level lv's rows of V are visible to level lv + 1
+    }
+}
+
+template <int NCH>
+static int launch_graph_sweep(int k, const int64_t* level_ptr, int n_levels, int64_t max_level, const int32_t* level_rows,
+                              const float* chol, const float* aux, const int64_t* sptr, const int32_t* sidx,
+                              const float* sval, float alpha, float lam_bias, const float* lam_bias_row, float* V,
+                              int64_t ldv, float* b_i, cudaStream_t s) {
+    auto kern = graph_sweep_kernel<NCH>;
+    const size_t per_warp = sizeof(float) * (size_t)k * k;
+    int wpc = (int)((200 * 1024) / per_warp);
+    if (wpc > 8) wpc = 8;
+    if (wpc < 1) {
+        set_error("graph_sweep: k = %d does not fit a factor in shared memory", k);
+        return B200ALS_E_UNSUPPORTED;
+    }
+    const size_t smem = per_warp * wpc;
+    ALS_CUDA(cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
+    int per_sm = 0;
+    ALS_CUDA(cudaOccupancyMaxActiveBlocksPerMultiprocessor(&per_sm, kern, 256, smem));
+    if (per_sm < 1) {
+        set_error("graph_sweep: kernel does not fit on an SM");
+        return B200ALS_E_UNSUPPORTED;
+    }
+    int64_t grid = ceil_div64(max_level, wpc);            // no more CTAs than the widest level can use
+    if (grid > (int64_t)kNumSMs * per_sm) grid = (int64_t)kNumSMs * per_sm;
+    if (grid < 1) grid = 1;
+    void* args[] = {&k, &level_ptr, &n_levels, &level_rows, &chol, &aux, &sptr, &sidx, &sval, &alpha, &lam_bias,
+                    &lam_bias_row, &V, &ldv, &b_i, &wpc};
+    ALS_CUDA(cudaLaunchCooperativeKernel((const void*)kern, dim3((unsigned)grid), dim3(256), args, smem, s));
+    g_launch_count++;
+    return B200ALS_OK;
 }
 
 }  // namespace b200als
@@ -240,6 +383,26 @@ int b200als_graph_level_solve(int32_t k, const int32_t* level_rows, int64_t n_le
         k, level_rows, n_level, chol, aux, sptr, sidx, sval, alpha, lam_bias, lam_bias_row, V, ldv, b_i);
     ALS_LAUNCH_CHECK();
     return B200ALS_OK;
+}
+
+int b200als_graph_sweep(int32_t k, const int64_t* level_ptr, int32_t n_levels, int64_t max_level_rows,
+                        const int32_t* level_rows, const float* chol, const float* aux, const int64_t* sptr,
+                        const int32_t* sidx, const float* sval, float alpha, float lam_bias, const float* lam_bias_row,
+                        float* V, int64_t ldv, float* b_i, b200als_stream_t stream) {
+    g_launch_count = 0;
+    ALS_CHECK_ARG(k >= 1 && k <= B200ALS_MAX_K, "k out of range");
+    ALS_CHECK_ARG(level_ptr && level_rows && chol && aux && sptr && sidx && sval && V && b_i, "null pointer");
+    if (n_levels <= 0) return B200ALS_OK;
+    cudaStream_t s = as_stream(stream);
+    const int nch = (k + 31) / 32;
+#define SWEEP_CASE(N) case N: return launch_graph_sweep<N>(k, level_ptr, n_levels, max_level_rows, level_rows, chol, aux, sptr, \
+                                                           sidx, sval, alpha, lam_bias, lam_bias_row, V, ldv, b_i, s)
+    switch (nch) {
+        SWEEP_CASE(1); SWEEP_CASE(2); SWEEP_CASE(3); SWEEP_CASE(4); SWEEP_CASE(5);
+    }
+#undef SWEEP_CASE
+    set_error("graph_sweep: k out of range");
+    return B200ALS_E_UNSUPPORTED;
 }
 
 }  // extern "C"

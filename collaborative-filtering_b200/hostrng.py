@@ -17,9 +17,11 @@ from ._hostlib import HOST_LIB_PATH, host_threads, load as _load   # noqa: F401 
 _M64 = (1 << 64) - 1
 
 
-def normal_stream(seed, shapes, dtypes, scale: float, n_threads: int | None = None, force_numpy: bool = False):
+def normal_stream(seed, shapes, dtypes, scale: float, n_threads: int | None = None, force_numpy: bool = False,
+                  alloc=None):
     """[rng.normal(scale=scale, size=s).astype(d) for s, d in zip(shapes, dtypes)] with rng = default_rng(seed),
-    dtypes float32 / float64."""
+    dtypes float32 / float64.  `alloc(shape, dtype)` (optional) supplies the output arrays — e.g. views of pinned
+    host buffers, so that the upload that follows is a DMA from where the values were written."""
     dtypes = [np.dtype(d) for d in dtypes]
     assert all(d in (np.dtype(np.float32), np.dtype(np.float64)) for d in dtypes)
     lib = None if force_numpy else _load()
@@ -29,9 +31,16 @@ def normal_stream(seed, shapes, dtypes, scale: float, n_threads: int | None = No
     # has the walk below: both go through numpy itself
     caller_owned = isinstance(seed, (np.random.Generator, np.random.BitGenerator))
     if lib is None or caller_owned or st["bit_generator"] != "PCG64" or st["has_uint32"]:
-        return [rng.normal(scale=scale, size=s).astype(d, copy=False) for s, d in zip(shapes, dtypes)]
+        res = [rng.normal(scale=scale, size=s).astype(d, copy=False) for s, d in zip(shapes, dtypes)]
+        if alloc is not None:
+            outs = [alloc(s, d) for s, d in zip(shapes, dtypes)]
+            for o, r in zip(outs, res):
+                o[...] = r
+            return outs
+        return res
     state, inc = int(st["state"]["state"]), int(st["state"]["inc"])
-    outs = [np.empty(s, dtype=d) for s, d in zip(shapes, dtypes)]
+    outs = [(alloc(s, d) if alloc is not None else np.empty(s, dtype=d)) for s, d in zip(shapes, dtypes)]
+    assert all(o.flags.c_contiguous and o.dtype == d and o.shape == tuple(s) for o, s, d in zip(outs, shapes, dtypes))
     counts = np.array([o.size for o in outs], dtype=np.int64)
     ptrs = np.array([o.ctypes.data for o in outs], dtype=np.uint64)
     as_f32 = np.array([d == np.dtype(np.float32) for d in dtypes], dtype=np.int32)

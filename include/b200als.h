@@ -260,6 +260,15 @@ int b200als_graph_level_solve(int32_t k, const int32_t* level_rows, int64_t n_le
                               float* V, int64_t ldv, float* b_i,
                               b200als_stream_t stream);
 
+/* The whole sweep in ONE cooperative launch: level_ptr (device int64 [n_levels + 1]) delimits the levels inside
+ * level_rows; a grid barrier separates them.  max_level_rows = rows of the widest level (sizes the grid).  Same
+ * arithmetic as n_levels calls of b200als_graph_level_solve in order. */
+int b200als_graph_sweep(int32_t k, const int64_t* level_ptr, int32_t n_levels, int64_t max_level_rows,
+                        const int32_t* level_rows, const float* chol, const float* aux,
+                        const int64_t* sptr, const int32_t* sidx, const float* sval,
+                        float alpha, float lam_bias, const float* lam_bias_row,
+                        float* V, int64_t ldv, float* b_i, b200als_stream_t stream);
+
 /* ------------------------------------------------------------------------
  * A10 — residual statistics over all observed entries (als.py:503-517):
  *   d_e = R_e - (U[u]·Z[i] + b_u[u] + b_i[i]);  acc[0] += sum d, acc[1] += sum d^2

@@ -271,3 +271,26 @@ def test_refit_appends_history(cuda_device):
     assert model.history["train_rmse"][:len(first)] == first
     assert np.allclose(model.history["train_rmse"][len(first):], first, atol=1e-6)     # same seed, same fit
     assert len(model.history["U_norm"]) == 2 * len(first)
+
+
+@pytest.mark.parametrize("k", [32, 64])
+def test_slab_storage_single_rank_equals_fit_coo(cuda_device, k):
+    """slab.RatingSlabs with one rank is the whole matrix with local == global ids: the fit through the slab entry
+    (row_ids map in the kernels, per-rank norm shares) must equal the ordinary fit bit for bit."""
+    import torch
+    import b200als
+    from b200als.slab import slabs_from_coo
+    from b200als.synth import synth_ratings
+    m, n, nnz = 500, 300, 20000
+    flat, vals = synth_ratings(m, n, nnz, seed=21)
+    keep = (flat // n != 3) & (flat % n != 11)               # a user and an item nobody rated
+    flat, vals = flat[keep], vals[keep]
+    cfg = b200als.ALSConfig(core=b200als.CoreConfig(n_factors=k, n_iters=3, lambda_u=4.0, lambda_v=3.0),
+                            biases=b200als.BiasesConfig(lambda_bu=2.0, lambda_bi=2.5))
+    a = b200als.ALS(cfg).fit_coo(flat, vals, (m, n), tol=None, verbose=0, sorted_input=True)
+    rows, cols = torch.from_numpy(flat // n).to(cuda_device), torch.from_numpy(flat % n).to(cuda_device)
+    slabs = slabs_from_coo(rows, cols, torch.from_numpy(vals.astype(np.float32)).to(cuda_device), m, n, 0, 1)
+    b = b200als.ALS(cfg).fit_slabs(slabs, tol=None, verbose=0)
+    for attr in ("U", "V", "b_u", "b_i"):
+        assert np.array_equal(getattr(a, attr), getattr(b, attr)), attr
+    assert a.history == b.history
