@@ -62,6 +62,25 @@ PRECISE_RIDGE = {_lib.PATH_FFMA: 0.1, _lib.PATH_UMMA: 0.3}
 PRECISE_COUNT_FACTOR = 4
 
 
+def draw_initial(seed, m, n, k, feature_dims, pin: bool):
+    """als.py:329, 367-376: default_rng(seed).normal(scale=0.1, ...) for U, V (float32 copies) and every W_f (float64),
+    the same values, drawn on all host cores (hostrng.py).  Large draws land in pinned host memory (torch caches the
+    buffers between fits), so the upload that follows is a DMA.  Returns (arrays, pinned tensors to keep alive)."""
+    pinned = []
+
+    def alloc(shape, dtype):
+        if int(np.prod(shape)) < (1 << 20) or not pin:
+            return np.empty(shape, dtype=dtype)
+        t = torch.empty(tuple(shape), dtype=torch.float32 if np.dtype(dtype) == np.float32 else torch.float64,
+                        pin_memory=True)
+        pinned.append(t)
+        return t.numpy()
+    draws = _hostrng.normal_stream(seed, [(m, k), (n, k)] + [(d, k) for d in feature_dims],
+                                   [np.float32, np.float32] + [np.float64] * len(feature_dims), SCALE_FACTOR,
+                                   n_threads=_hostrng.host_threads(shared=False), alloc=alloc)
+    return draws, pinned
+
+
 def _env_int(name: str, default: int) -> int:
     try:
         return int(os.environ.get(name, default))
@@ -216,11 +235,44 @@ class ALS:
         _lib.require_device()
         dev = self._dev()
         with torch.cuda.device(dev):
-            ratings = ratings_from_flat(flat_idx, vals, shape, dev, sorted_input=sorted_input)
+            self._start_predraw(shape, features, init)
+            try:
+                ratings = ratings_from_flat(flat_idx, vals, shape, dev, sorted_input=sorted_input)
+            except Exception:
+                self.__dict__.pop("_predraw", None)
+                raise
             if ratings.nnz == 0:
                 raise ValueError("no observed ratings")
             mu0 = float(ratings.vals.sum(dtype=torch.float64).item() / ratings.nnz)
             return self._fit_ratings(ratings, mu0, features, tol, min_iters, verbose, init)
+
+    def _start_predraw(self, shape, features, init) -> None:
+        """The initial draw is host work on all cores (~65 ms at the Netflix shape), the H2D copy and the CSR/CSC build
+        are device work: start the draw on a thread now, the session picks it up (FitSession.__init__)."""
+        import threading
+        shard = self.shard
+        if init is not None or (shard is not None and shard.active and shard.rank != 0):
+            return
+        m, n, k = int(shape[0]), int(shape[1]), int(self.n_factors)
+        feats = features or {}
+        if m * k < (1 << 22) or not (1 <= k <= _lib.MAX_K) or any(getattr(X, "ndim", 0) != 2 for X in feats.values()):
+            return                                     # small draws are not worth a thread
+        names = tuple(feats.keys())
+        dims = [int(feats[nm].shape[1]) for nm in names]
+        holder = {}
+        seed = self.random_state
+
+        dev = self._dev()
+
+        def work():
+            try:
+                torch.cuda.set_device(dev)             # the pinned allocations belong to this fit's device context
+                holder["draws"], holder["pinned"] = draw_initial(seed, m, n, k, dims, True)
+            except Exception as e:   # noqa: BLE001 — re-raised by the session
+                holder["error"] = e
+        th = threading.Thread(target=work, daemon=True)
+        th.start()
+        self._predraw = (th, holder, (m, n, k, names))
 
     def fit_ratings(self, ratings: Ratings, features=None, tol=1e-3, min_iters=5, verbose=1,
                     init=None) -> "ALS":
@@ -488,20 +540,15 @@ class FitSession:
             # all host cores (hostrng.py).  Sharded: one rank draws with every core and the device arrays are
             # broadcast, instead of N ranks walking the same stream on 1/N of the cores each.
             if shard.rank == 0 or not shard.active:
-                # large draws land in pinned host memory (torch caches the buffers between fits): the upload is a DMA
-                pinned = []
-
-                def alloc(shape, dtype):
-                    if int(np.prod(shape)) < (1 << 20) or not dev.type == "cuda":
-                        return np.empty(shape, dtype=dtype)
-                    t = torch.empty(tuple(shape), dtype=torch.float32 if np.dtype(dtype) == np.float32 else torch.float64,
-                                    pin_memory=True)
-                    pinned.append(t)
-                    return t.numpy()
-                draws = _hostrng.normal_stream(model.random_state, [(m, k), (n, k)] + [(features[nm].shape[1], k)
-                                                                                      for nm in names],
-                                               [np.float32, np.float32] + [np.float64] * len(names), SCALE_FACTOR,
-                                               n_threads=_hostrng.host_threads(shared=False), alloc=alloc)
+                pre = model.__dict__.pop("_predraw", None)
+                if pre is not None and pre[2] == (m, n, k, tuple(names)):
+                    pre[0].join()                      # started by fit_coo under the H2D copy and the CSR/CSC build
+                    if "error" in pre[1]:
+                        raise pre[1]["error"]
+                    draws, pinned = pre[1]["draws"], pre[1]["pinned"]
+                else:
+                    draws, pinned = draw_initial(model.random_state, m, n, k, [features[nm].shape[1] for nm in names],
+                                                 dev.type == "cuda")
                 U_d[:m, :k].copy_(torch.from_numpy(draws[0]), non_blocking=True)
                 V_d[:n, :k].copy_(torch.from_numpy(draws[1]), non_blocking=True)
                 torch.cuda.current_stream().synchronize() if dev.type == "cuda" else None

@@ -24,9 +24,10 @@ constexpr int F64_THREADS = 256;
 constexpr int F64_TR = 16;        // ratings per staged tile
 
 __host__ __device__ constexpr int f64_tri(int k) { return k * (k + 1) / 2; }
+__host__ __device__ constexpr int f64_tri_pad(int k) { return (f64_tri(k) + 1) & ~1; }   // keeps the float4 tile 16-byte aligned
 static inline size_t f64_smem_bytes(int k) {
     const int k4 = (k + 3) & ~3;
-    return sizeof(double) * ((size_t)f64_tri(k) + 4 * (size_t)k + 8 + F64_TR)   // G | c | s | b / y / x | - | scalars | q
+    return sizeof(double) * ((size_t)f64_tri_pad(k) + 4 * (size_t)k4 + 8 + F64_TR)   // G | c | s | b / y / x | - | scalars | q
            + sizeof(float) * ((size_t)F64_TR * k4)                       // tile
            + sizeof(int32_t) * (F64_TR + 8)                              // idx | flags
            + sizeof(uint16_t) * 2 * (size_t)f64_tri(k);                  // (i, j) table
@@ -36,11 +37,11 @@ __global__ void __launch_bounds__(F64_THREADS) row_step_f64_kernel(const RowStep
     extern __shared__ __align__(16) unsigned char smem_raw[];
     const int k = p.k, k4 = (k + 3) & ~3, tri = f64_tri(k);
     double* G = reinterpret_cast<double*>(smem_raw);
-    double* c_s = G + tri;
-    double* s_s = c_s + k;
-    double* b_s = s_s + k;           // right-hand side, then y, then x
-    double* x_s = b_s + k;
-    double* sc = x_s + k;            // [0] t, [1] qq, [2] pivot-ok flag, [3] s.x, [4] c.x, [5] x.x
+    double* c_s = G + f64_tri_pad(k);
+    double* s_s = c_s + k4;
+    double* b_s = s_s + k4;          // right-hand side, then y, then x
+    double* x_s = b_s + k4;
+    double* sc = x_s + k4;           // [0] t, [1] qq, [2] pivot-ok flag
     double* q_t = sc + 8;            // q = rating - mu - bias_other of the staged ratings, in double
     float* tile = reinterpret_cast<float*>(q_t + F64_TR);
     int32_t* idx_t = reinterpret_cast<int32_t*>(tile + F64_TR * k4);
@@ -74,7 +75,7 @@ __global__ void __launch_bounds__(F64_THREADS) row_step_f64_kernel(const RowStep
         const int64_t cnt = end - beg;
         if (cnt <= 0) continue;
         for (int e = tid; e < tri; e += F64_THREADS) G[e] = 0.0;
-        for (int i = tid; i < 4 * k + 8; i += F64_THREADS) c_s[i] = 0.0;     // c, s, b, x, scalars are contiguous
+        for (int i = tid; i < 4 * k4 + 8; i += F64_THREADS) c_s[i] = 0.0;    // c, s, b, x, scalars are contiguous
 
         for (int64_t t0 = beg; t0 < end; t0 += F64_TR) {
             const int live = (int)((end - t0) < F64_TR ? (end - t0) : F64_TR);

@@ -9,6 +9,8 @@
 // refreshes `residual` inside the feature loop, als.py:474-489).
 // Everything is float64: lambda_w may be 0 (evaluate_models.py "no_features"),
 // leaving the (d k)^2 system regularised by EPS alone (als.py:497-498).
+#include <cooperative_groups.h>
+
 #include "common.cuh"
 
 namespace b200als {
@@ -224,6 +226,171 @@ __global__ void __launch_bounds__(1024) cholesky_solve_f64_kernel(double* __rest
     }
 }
 
+// Blocked right-looking Cholesky + solve across the whole GPU, float64, one cooperative launch.
+// The single-CTA kernel above walks N columns with the trailing matrix going through L2 once per column
+// (measured: ~20 ms at N = 608, the genres system of the bundled shape — a fifth of a C2 fit).  Here the matrix is
+// cut into 32 x 32 tiles; per block column: (1) CTA 0 factors the diagonal tile in shared memory, (2) every row
+// below — and b, carried as row N — is forward-substituted against it, one thread per row, (3) the trailing tiles
+// are updated C -= P_I P_J^T, one tile per CTA at a time, operands staged in shared memory; grid barriers in between.
+// The back substitution runs block-wise on CTA 0.  Lower triangle only; x overwrites b.
+constexpr int CB = 32;
+
+__global__ void __launch_bounds__(256) cholesky_solve_f64_coop_kernel(double* __restrict__ A, double* __restrict__ b,
+                                                                      int N, int32_t* status, int* bad_flag) {
+    namespace cg = cooperative_groups;
+    cg::grid_group grid = cg::this_grid();
+    __shared__ double T[CB][CB + 1];
+    __shared__ double Pj[CB][CB + 1];
+    __shared__ double xs[CB];
+    __shared__ int bad_s;
+    const int tid = threadIdx.x;
+    const int nblk = (N + CB - 1) / CB;
+    auto row_ptr = [&](int i) -> double* { return i == N ? b : A + (size_t)i * N; };   // b rides along as row N
+
+    for (int jb = 0; jb < nblk; ++jb) {
+        const int j0 = jb * CB, w = (N - j0) < CB ? (N - j0) : CB;
+        // ---- (1) diagonal tile ----
+        if (blockIdx.x == 0) {
+            if (tid == 0) bad_s = 0;
+            for (int e = tid; e < CB * CB; e += 256) {
+                const int r = e / CB, c = e - r * CB;
+                T[r][c] = (r < w && c <= r) ? A[(size_t)(j0 + r) * N + j0 + c] : 0.0;
+            }
+            __syncthreads();
+            for (int j = 0; j < w; ++j) {
+                const double d = T[j][j];
+                if (!(d > 0.0)) {
+                    if (tid == 0) bad_s = 1;
+                    break;
+                }
+                const double sd = sqrt(d), inv = 1.0 / sd;
+                __syncthreads();
+                if (tid > j && tid < w) T[tid][j] *= inv;
+                if (tid == j) T[j][j] = sd;
+                __syncthreads();
+                for (int e = tid; e < CB * CB; e += 256) {
+                    const int r = e / CB, c = e - r * CB;
+                    if (c > j && c <= r && r < w) T[r][c] = fma(-T[r][j], T[c][j], T[r][c]);
+                }
+                __syncthreads();
+            }
+            __syncthreads();
+            if (bad_s) {
+                if (tid == 0) *bad_flag = 1;
+            } else {
+                for (int e = tid; e < CB * CB; e += 256) {
+                    const int r = e / CB, c = e - r * CB;
+                    if (r < w && c <= r) A[(size_t)(j0 + r) * N + j0 + c] = T[r][c];
+                }
+            }
+            __threadfence();
+        }
+        grid.sync();
+        if (*reinterpret_cast<volatile int*>(bad_flag)) break;
+        // ---- (2) panel: rows below (and b) against the factored tile ----
+        const int first = j0 + w;                            // first row below the tile; row N is b
+        for (int e = tid; e < CB * CB; e += 256) {
+            const int r = e / CB, c = e - r * CB;
+            T[r][c] = (r < w && c <= r) ? A[(size_t)(j0 + r) * N + j0 + c] : 0.0;
+        }
+        __syncthreads();
+        for (int64_t i = first + (int64_t)blockIdx.x * 256 + tid; i <= N; i += (int64_t)gridDim.x * 256) {
+            double* rp = row_ptr((int)i) + j0;
+            double a[CB];
+#pragma unroll
+            for (int c = 0; c < CB; ++c) a[c] = c < w ? rp[c] : 0.0;
+#pragma unroll
+            for (int c = 0; c < CB; ++c) {
+                if (c < w) {
+                    double v = a[c];
+#pragma unroll
+                    for (int t = 0; t < CB; ++t)
+                        if (t < c) v = fma(-a[t], T[c][t], v);
+                    a[c] = v / T[c][c];
+                }
+            }
+#pragma unroll
+            for (int c = 0; c < CB; ++c)
+                if (c < w) rp[c] = a[c];
+        }
+        __threadfence();
+        grid.sync();
+        // ---- (3) trailing update: tile (I, J), jb < J <= I, I == nblk is the single row b ----
+        const int nI = nblk - jb - 1;                        // block rows below
+        if (nI > 0 || first <= N) {
+            const int64_t tiles_sq = (int64_t)nI * (nI + 1) / 2;
+            const int64_t tiles = tiles_sq + nI;             // + one row-N strip per block column
+            for (int64_t tl = blockIdx.x; tl < tiles; tl += gridDim.x) {
+                int I, J;
+                if (tl < tiles_sq) {
+                    I = (int)((sqrt(8.0 * (double)tl + 1.0) - 1.0) * 0.5);
+                    while ((int64_t)(I + 1) * (I + 2) / 2 <= tl) ++I;
+                    while ((int64_t)I * (I + 1) / 2 > tl) --I;
+                    J = (int)(tl - (int64_t)I * (I + 1) / 2);
+                } else {
+                    I = nI;                                   // the b strip
+                    J = (int)(tl - tiles_sq);
+                }
+                const int ri0 = (I == nI) ? N : first + I * CB, rj0 = first + J * CB;
+                const int hi = (I == nI) ? 1 : ((N - ri0) < CB ? (N - ri0) : CB);
+                const int hj = (N - rj0) < CB ? (N - rj0) : CB;
+                __syncthreads();
+                for (int e = tid; e < CB * CB; e += 256) {
+                    const int r = e / CB, c = e - r * CB;
+                    T[r][c] = (r < hi && c < w) ? row_ptr(ri0 + r)[j0 + c] : 0.0;
+                    Pj[r][c] = (r < hj && c < w) ? A[(size_t)(rj0 + r) * N + j0 + c] : 0.0;
+                }
+                __syncthreads();
+                for (int e = tid; e < CB * CB; e += 256) {
+                    const int r = e / CB, c = e - r * CB;    // output (ri0 + r, rj0 + c)
+                    if (r < hi && c < hj && (I == nI || rj0 + c <= ri0 + r)) {
+                        double acc = 0.0;
+#pragma unroll
+                        for (int t = 0; t < CB; ++t) acc = fma(T[r][t], Pj[c][t], acc);
+                        row_ptr(ri0 + r)[rj0 + c] -= acc;
+                    }
+                }
+            }
+        }
+        __threadfence();
+        grid.sync();
+    }
+    if (*reinterpret_cast<volatile int*>(bad_flag)) {
+        if (blockIdx.x == 0 && tid == 0 && status) {
+            if (atomicAdd(&status[0], 1) == 0) { status[1] = -1; status[2] = 9; }
+        }
+        return;
+    }
+    // ---- back substitution L^T x = y on CTA 0, block by block from the end ----
+    if (blockIdx.x != 0) return;
+    for (int jb = nblk - 1; jb >= 0; --jb) {
+        const int j0 = jb * CB, w = (N - j0) < CB ? (N - j0) : CB;
+        __syncthreads();
+        for (int e = tid; e < CB * CB; e += 256) {
+            const int r = e / CB, c = e - r * CB;
+            T[r][c] = (r < w && c <= r) ? A[(size_t)(j0 + r) * N + j0 + c] : 0.0;
+        }
+        if (tid < CB) xs[tid] = tid < w ? b[j0 + tid] : 0.0;
+        __syncthreads();
+        if (tid < 32) {                                      // one warp: w dependent steps
+            double y = xs[tid];
+            for (int j = w - 1; j >= 0; --j) {
+                const double xj = __shfl_sync(0xffffffffu, y, j) / T[j][j];
+                if (tid == j) y = xj;
+                else if (tid < j) y = fma(-T[j][tid], xj, y);
+            }
+            xs[tid] = y;
+            if (tid < w) b[j0 + tid] = y;
+        }
+        __syncthreads();
+        for (int i = tid; i < j0; i += 256) {
+            double acc = b[i];
+            for (int r = 0; r < w; ++r) acc = fma(-A[(size_t)(j0 + r) * N + i], xs[r], acc);
+            b[i] = acc;
+        }
+    }
+}
+
 }  // namespace b200als
 
 using namespace b200als;
@@ -284,6 +451,25 @@ int b200als_wstep_system(int64_t n, int32_t k, int32_t d, const float* X, const 
 
 int b200als_cholesky_solve_f64(double* A, double* b, int32_t N, int32_t* status, b200als_stream_t stream) {
     ALS_CHECK_ARG(A && b && N >= 1, "bad args");
+    if (N > 64) {
+        // blocked, all SMs, one cooperative launch; its 'not positive definite' flag lives in the caller's status words
+        cudaStream_t s = as_stream(stream);
+        int* flag = nullptr;
+        ALS_CUDA(cudaMallocAsync(&flag, sizeof(int), s));
+        ALS_CUDA(cudaMemsetAsync(flag, 0, sizeof(int), s));
+        int per_sm = 0;
+        ALS_CUDA(cudaOccupancyMaxActiveBlocksPerMultiprocessor(&per_sm, cholesky_solve_f64_coop_kernel, 256, 0));
+        const int nblk = (N + CB - 1) / CB;
+        int64_t want = (int64_t)nblk * (nblk + 1) / 2;
+        int64_t cap = (int64_t)kNumSMs * (per_sm < 1 ? 1 : (per_sm > 2 ? 2 : per_sm));
+        int grid = (int)(want < cap ? want : cap);
+        if (grid < 1) grid = 1;
+        void* args[] = {&A, &b, &N, &status, &flag};
+        ALS_CUDA(cudaLaunchCooperativeKernel((const void*)cholesky_solve_f64_coop_kernel, dim3(grid), dim3(256), args, 0, s));
+        g_launch_count++;
+        ALS_CUDA(cudaFreeAsync(flag, s));
+        return B200ALS_OK;
+    }
     const size_t smem = sizeof(double) * ((size_t)N + 1);
     ALS_CHECK_ARG(smem <= 200 * 1024, "system too large for the single-CTA float64 solver (d*k <= 25599)");
     if (smem > 48 * 1024)

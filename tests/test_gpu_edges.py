@@ -294,3 +294,33 @@ def test_slab_storage_single_rank_equals_fit_coo(cuda_device, k):
     for attr in ("U", "V", "b_u", "b_i"):
         assert np.array_equal(getattr(a, attr), getattr(b, attr)), attr
     assert a.history == b.history
+
+
+@pytest.mark.parametrize("N", [1, 31, 33, 64, 65, 100, 257, 608, 1000])
+def test_cholesky_solve_f64_vs_numpy(cuda_device, N):
+    """b200als_cholesky_solve_f64 (the W step's (d k)^2 float64 system, scripts/als.py:497-500): the single-CTA kernel
+    up to N = 64, the blocked cooperative kernel above, ragged last blocks, and the not-positive-definite flag."""
+    import torch
+    import b200als
+    from b200als._lib import check, load, ptr
+    lib = load()
+    rng = np.random.default_rng(N)
+    B = rng.normal(size=(N, N + 3))
+    A = B @ B.T + 0.5 * np.eye(N)
+    rhs = rng.normal(size=N)
+    want = np.linalg.solve(A, rhs)
+    A_d = torch.from_numpy(A.copy()).to(cuda_device)
+    b_d = torch.from_numpy(rhs.copy()).to(cuda_device)
+    status = torch.zeros(4, dtype=torch.int32, device=cuda_device)
+    check(lib.b200als_cholesky_solve_f64(ptr(A_d), ptr(b_d), N, ptr(status), torch.cuda.current_stream().cuda_stream))
+    got = b_d.cpu().numpy()
+    assert int(status[0]) == 0
+    assert np.abs(got - want).max() <= 1e-9 * max(1.0, np.abs(want).max())
+    Lg = np.tril(A_d.cpu().numpy())
+    assert np.allclose(Lg, np.linalg.cholesky(A), rtol=1e-9, atol=1e-9)
+    if N >= 2:
+        A[N // 2, N // 2] = -1.0                                 # not positive definite
+        A_d = torch.from_numpy(A).to(cuda_device)
+        b_d = torch.from_numpy(rhs.copy()).to(cuda_device)
+        check(lib.b200als_cholesky_solve_f64(ptr(A_d), ptr(b_d), N, ptr(status), torch.cuda.current_stream().cuda_stream))
+        assert int(status[0]) == 1
