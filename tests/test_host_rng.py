@@ -77,7 +77,14 @@ def test_session_init_uses_the_stream(monkeypatch):
     """FitSession draws through hostrng with the reference's order and dtypes (U, V float32; W_f float64)."""
     import inspect
     src = inspect.getsource(b200als.als)
-    assert "_hostrng.normal_stream(model.random_state" in src and "rng.normal(" not in src
+    assert "_hostrng.normal_stream(seed" in src and "rng.normal(" not in src
+    # the function the session (and fit_coo's overlapped pre-draw) calls: reference order and dtypes
+    draws, pinned = b200als.als.draw_initial(42, 30, 20, 4, [3, 1], False)
+    rng = np.random.default_rng(42)
+    for got, (shape, dt) in zip(draws, [((30, 4), np.float32), ((20, 4), np.float32), ((3, 4), np.float64),
+                                        ((1, 4), np.float64)]):
+        assert got.dtype == dt and _same_bits(got, rng.normal(scale=0.1, size=shape).astype(dt))
+    assert pinned == []
 
 
 def test_tiny_chunks_exercise_the_stitch(tmp_path):
