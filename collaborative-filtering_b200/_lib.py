@@ -105,6 +105,9 @@ _SIGNATURES = {
     "b200als_fold_split": [vp, vp, C.c_int64, vp, C.c_int64, vp, vp, vp, vp, vp, vp, C.c_size_t, vp],
     "b200als_sse_on_flat": [vp, C.c_int64, vp, C.c_int64, vp, vp, vp, vp, vp, C.c_int64, C.c_int64, C.c_int32,
                             vp, C.c_int32, vp, vp, vp],
+    "b200als_normalize_workspace_bytes": [C.c_int64, C.POINTER(C.c_size_t)],
+    "b200als_normalize_feature": [vp, C.c_int64, C.c_int32, C.c_int32, C.c_int32, C.c_double, vp, vp, vp, C.c_size_t, vp],
+    "b200als_similarity_topk_rows": [vp, C.c_int64, C.c_int32, C.c_int32, C.c_float, vp, vp, C.c_int64, vp, vp, vp],
 }
 _RESTYPES = {"b200als_last_error": C.c_char_p}
 

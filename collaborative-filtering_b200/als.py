@@ -133,6 +133,10 @@ class ALS:
         # "auto": rows whose ridge is too small for float32 (few ratings AND small lambda, see PRECISE_RIDGE) take
         # the float64 half-step, the rest the fast paths; "f32": never; "f64": every row (the reference's arithmetic)
         self.precision = os.environ.get("B200ALS_PRECISION", "auto")
+        # "host": the similarity graph is built with the reference's own numpy calls (index parity with np.argpartition's
+        # tie-breaking); "device": cosine + top-k on the GPU with a documented tie rule (smaller column wins) — the same
+        # graph whenever similarities do not tie, a different but deterministic one when they do (binary genres)
+        self.graph_build = os.environ.get("B200ALS_GRAPH_BUILD", "host")
         self.shard: Shard | None = None    # row sharding across ranks (dist.Shard)
         self.timings: dict[str, float] = {}
         self.launches_per_iter: int = 0
@@ -524,10 +528,23 @@ class FitSession:
                                f"Graph regularization disabled.")
             else:
                 t0 = time.perf_counter()
-                model.S = _graph.similarity_topk(Xg, model.S_topk, model.S_eps)
+                self.S_csr = None
+                if (model.graph_build == "device" and model.S_topk is not None and 1 <= model.S_topk < n):
+                    # opt-in: cosine + top-k on the GPU with a documented tie rule (graph.similarity_topk_device)
+                    sp_, si_, sv_, D_ = _graph.similarity_topk_device(Xg, model.S_topk, model.S_eps, dev)
+                    self.S_csr = (sp_, si_, sv_, D_)
+                    model.S_csr = (sp_, si_, sv_)      # the graph as CSR; the dense `S` of the reference is not formed
+                                                       # (graph.csr_to_dense(*model.S_csr, n) gives it)
+                elif model.graph_build not in ("host", "device"):
+                    raise ValueError(f"graph_build={model.graph_build!r}: expected 'host' or 'device'")
+                else:
+                    model.S = _graph.similarity_topk(Xg, model.S_topk, model.S_eps)
                 model.timings["S_build_s"] = time.perf_counter() - t0
-        use_graph = self.use_graph = model.S is not None
-        D = model.S.sum(axis=1) if use_graph else None                  # als.py:357 (S's dtype)
+        use_graph = self.use_graph = (model.S is not None) or (getattr(self, "S_csr", None) is not None)
+        if use_graph and getattr(self, "S_csr", None) is not None:
+            D = self.S_csr[3]
+        else:
+            D = model.S.sum(axis=1) if use_graph else None              # als.py:357 (S's dtype)
 
         # ---- init (als.py:360-376): same PCG64 stream, order U, V, W_f ----------
         m_pad, n_pad = shard.padded_rows(m), shard.padded_rows(n)
@@ -653,7 +670,7 @@ class FitSession:
 
         if use_graph:
             t0 = time.perf_counter()
-            sptr, sidx, sval = _graph.to_csr(model.S)
+            sptr, sidx, sval = self.S_csr[:3] if getattr(self, "S_csr", None) is not None else _graph.to_csr(model.S)
             self.level_ptr, level_rows = _graph.level_schedule(sptr, sidx, item_counts > 0)
             model.timings["S_csr_levels_s"] = time.perf_counter() - t0
             self.sptr_d = torch.from_numpy(sptr).to(dev)

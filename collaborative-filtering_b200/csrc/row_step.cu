@@ -157,13 +157,28 @@ __global__ void __launch_bounds__(256) graph_sweep_kernel(int k, const int64_t* 
                     const int c = lane + 32 * t;
                     y[t] = c < k ? ax[c] - bold * ax[k + c] : 0.0f;
                 }
-                for (int64_t e = sptr[i]; e < sptr[i + 1]; ++e) {
-                    const float sv = alpha * sval[e];
-                    const float* vj = V + (size_t)sidx[e] * ldv;
+                // b += alpha S[i,:] V: the lanes fetch 32 (column, weight) pairs at once, then the 32 rows of V are read
+                // with independent loads (eight in flight) — a row of S holds up to ~500 neighbours on the bundled
+                // genres graph, and one dependent L2 round trip per neighbour made the widest row the whole level's time.
+                // Same summation order as the edge-by-edge loop.
+                const int64_t e1 = sptr[i + 1];
+                for (int64_t e0 = sptr[i]; e0 < e1; e0 += 32) {
+                    const int64_t eme = e0 + lane;
+                    const int32_t jl = eme < e1 ? sidx[eme] : 0;
+                    const float sl = eme < e1 ? alpha * sval[eme] : 0.0f;
+                    const int cnt_e = (int)((e1 - e0) < 32 ? (e1 - e0) : 32);
+#pragma unroll 8
+                    for (int u = 0; u < 32; ++u) {
+                        const int32_t j = __shfl_sync(0xffffffffu, jl, u);
+                        const float sv = __shfl_sync(0xffffffffu, sl, u);
+                        if (u < cnt_e) {
+                            const float* vj = V + (size_t)j * ldv;
 #pragma unroll
-                    for (int t = 0; t < NCH; ++t) {
-                        const int c = lane + 32 * t;
-                        if (c < k) y[t] = fmaf(sv, vj[c], y[t]);
+                            for (int t = 0; t < NCH; ++t) {
+                                const int c = lane + 32 * t;
+                                if (c < k) y[t] = fmaf(sv, __ldcg(vj + c), y[t]);
+                            }
+                        }
                     }
                 }
                 __syncwarp();

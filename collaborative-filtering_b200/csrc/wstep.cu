@@ -104,17 +104,36 @@ __global__ void __launch_bounds__(256) wstep_h_kernel(int64_t n, int k, const do
     }
 }
 
-// b[a*k + c] = sum_i X[i, a] h[i, c]; block per a, thread per c
-__global__ void wstep_b_kernel(int64_t n, int k, int d, const float* __restrict__ X, const double* __restrict__ h,
-                               double* __restrict__ b) {
-    const int a = blockIdx.x;
-    for (int c = threadIdx.x; c < k; c += blockDim.x) {
-        double s = 0.0;
-        for (int64_t i = 0; i < n; ++i) {
-            const float xa = X[i * d + a];
-            if (xa != 0.0f) s = fma((double)xa, h[i * k + c], s);
+// b[a*k + c] = sum_i X[i, a] h[i, c]; block per a: lane = c (32 columns per pass), the 8 warps stride the items and
+// their partial sums are combined in shared memory (a thread-per-c loop over all n items was 1.5 ms per call at the
+// bundled shape: 4980 dependent loads per thread on 32 threads per block)
+__global__ void __launch_bounds__(256) wstep_b_kernel(int64_t n, int k, int d, const float* __restrict__ X,
+                                                      const double* __restrict__ h, double* __restrict__ b) {
+    __shared__ double part[8][32];
+    const int a = blockIdx.x, lane = threadIdx.x & 31, w = threadIdx.x >> 5;
+    for (int c0 = 0; c0 < k; c0 += 32) {
+        const int c = c0 + lane;
+        double s0 = 0.0, s1 = 0.0;
+        int64_t i = w;
+        for (; i + 8 < n; i += 16) {                 // two independent chains per thread
+            const float x0 = X[i * d + a], x1 = X[(i + 8) * d + a];
+            if (c < k) {
+                if (x0 != 0.0f) s0 = fma((double)x0, h[i * k + c], s0);
+                if (x1 != 0.0f) s1 = fma((double)x1, h[(i + 8) * k + c], s1);
+            }
         }
-        b[(size_t)a * k + c] = s;
+        for (; i < n; i += 8) {
+            const float x0 = X[i * d + a];
+            if (c < k && x0 != 0.0f) s0 = fma((double)x0, h[i * k + c], s0);
+        }
+        __syncthreads();
+        part[w][lane] = s0 + s1;
+        __syncthreads();
+        if (w == 0 && c < k) {
+            double t = 0.0;
+            for (int ww = 0; ww < 8; ++ww) t += part[ww][lane];
+            b[(size_t)a * k + c] = t;
+        }
     }
 }
 

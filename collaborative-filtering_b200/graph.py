@@ -126,3 +126,83 @@ def level_schedule(sptr: np.ndarray, sidx: np.ndarray, rated: np.ndarray):
     level_ptr = np.zeros(nlev + 1, dtype=np.int64)
     np.cumsum(np.bincount(level[rows], minlength=nlev), out=level_ptr[1:])
     return level_ptr, rows.astype(np.int32)
+
+
+# ---- opt-in device build -------------------------------------------------------
+def topk_rule_reference(X: np.ndarray, topk: int, eps: float) -> np.ndarray:
+    """The DOCUMENTED tie rule of the device build, restated in numpy (tests compare the kernel with this):
+    cosine similarities in float32 exactly as the kernel forms them are not reproducible on the host bit for bit,
+    so this takes the similarity matrix as numpy computes it and applies the rule — row i keeps its `topk` largest
+    entries over ALL columns (zeroed diagonal included, as np.argpartition sees it in scripts/als.py:231-236), and
+    among entries equal to the topk-th largest value the SMALLER column index wins — then S = max(S, S^T)."""
+    X = np.asarray(X, dtype=np.float32)
+    unit = X / (np.sqrt((X * X).sum(axis=1, keepdims=True)) + np.float32(eps))
+    S = (unit @ unit.T).astype(np.float32)
+    np.fill_diagonal(S, 0.0)
+    n = S.shape[0]
+    keep = np.zeros_like(S, dtype=bool)
+    cols = np.arange(n)
+    for i in range(n):
+        order = np.lexsort((cols, -S[i]))            # by value descending, ties by ascending column
+        keep[i, order[:topk]] = True
+    K = np.where(keep, S, 0.0)
+    return np.maximum(K, K.T)
+
+
+def similarity_topk_device(X: np.ndarray, topk: int, eps: float, device):
+    """Cosine similarity + per-row top-k on the GPU (b200als_similarity_topk_rows) with the deterministic tie rule of
+    include/b200als.h, symmetrised to S = max(S, S^T).  Returns (sptr int64, sidx int32, sval float32, D float32) as
+    numpy arrays — CSR of the nonzeros of S, columns ascending, and the row sums S.sum(axis=1) (scripts/als.py:357).
+
+    NOT the default: with tied similarities (binary genre vectors) the reference's np.argpartition keeps an
+    implementation-defined subset, so only the host build (`similarity_topk`) reproduces the reference's graph
+    index for index.  Without ties both builds give the same graph."""
+    import ctypes as C
+    import torch
+    from . import _lib
+    from ._lib import check, ptr
+    lib = _lib.load()
+    _lib.require_device()
+    X = np.ascontiguousarray(X, dtype=np.float32)
+    n, d = X.shape
+    if not (1 <= int(topk) < n):
+        raise ValueError("the device graph build needs 1 <= topk < number of items")
+    topk = int(topk)
+    dev = torch.device(device)
+    with torch.cuda.device(dev):
+        X_d = torch.from_numpy(X).to(dev)
+        Xn = torch.empty_like(X_d)
+        rows = min(n, 148 * 4)
+        scratch = torch.empty(rows * n, dtype=torch.float32, device=dev)
+        idx = torch.empty(n * topk, dtype=torch.int32, device=dev)
+        val = torch.empty(n * topk, dtype=torch.float32, device=dev)
+        check(lib.b200als_similarity_topk_rows(ptr(X_d), n, d, topk, float(eps), ptr(Xn), ptr(scratch), rows, ptr(idx),
+                                               ptr(val), torch.cuda.current_stream().cuda_stream), "similarity_topk_rows")
+        # S = max(K, K^T) from the directed lists: a pair kept in one direction only survives iff its value is > 0
+        # (the other direction holds 0); kept in both, it keeps its value whatever the sign.  Edge-list plumbing.
+        i = torch.arange(n, device=dev, dtype=torch.int64).repeat_interleave(topk)
+        j = idx.to(torch.int64)
+        fwd, rev = i * n + j, j * n + i
+        keys = torch.cat([fwd, rev])
+        vals = torch.cat([val, val])
+        order = torch.argsort(keys, stable=True)
+        keys, vals = keys[order], vals[order]
+        uniq, counts = torch.unique_consecutive(keys, return_counts=True)
+        start = torch.cumsum(counts, 0) - counts
+        v = vals[start]
+        both = counts >= 2
+        v = torch.where(both, v, torch.clamp(v, min=0.0))
+        nz = v != 0
+        uniq, v = uniq[nz], v[nz]
+        r = uniq // n
+        sptr = torch.zeros(n + 1, dtype=torch.int64, device=dev)
+        sptr[1:] = torch.cumsum(torch.bincount(r, minlength=n), 0)
+        D = torch.zeros(n, dtype=torch.float32, device=dev).index_add_(0, r, v)
+        return (sptr.cpu().numpy(), (uniq - r * n).to(torch.int32).cpu().numpy(), v.cpu().numpy(), D.cpu().numpy())
+
+
+def csr_to_dense(sptr, sidx, sval, n: int) -> np.ndarray:
+    S = np.zeros((n, n), dtype=np.float32)
+    r = np.repeat(np.arange(n), np.diff(sptr))
+    S[r, sidx] = sval
+    return S

@@ -363,6 +363,33 @@ int b200als_sse_on_flat(const float* U, int64_t ldu, const float* Z, int64_t ldz
                         int64_t n, int32_t k, const int32_t* item_bin, int32_t n_bins,
                         double* sse, int64_t* cnt, b200als_stream_t stream);
 
+/* ------------------------------------------------------------------------
+ * N4 — `normalize_feature` (prepare_features.py:131-191) in place on X (n, d) float64 row-major.
+ *   impute: 0 none | 1 col_median (NaN / +-Inf -> np.nanmedian of the column, 0 for an all-NaN column; :83-94)
+ *   method: 0 none | 1 row_l1 | 2 row_l2 | 3 col_zscore | 4 col_minmax          (:97-128, eps as there)
+ * *n_nonfinite (device int64) = NaN / Inf entries of the INPUT (with impute 0 the caller raises the reference's
+ * ValueError on a non-zero count).  med_work: d + 1 doubles; workspace from b200als_normalize_workspace_bytes (both
+ * only needed with impute 1).
+ * ---------------------------------------------------------------------- */
+int b200als_normalize_workspace_bytes(int64_t n, size_t* bytes_host);
+int b200als_normalize_feature(double* X, int64_t n, int32_t d, int32_t method, int32_t impute, double eps,
+                              int64_t* n_nonfinite, double* med_work, void* workspace, size_t workspace_bytes,
+                              b200als_stream_t stream);
+
+/* ------------------------------------------------------------------------
+ * N3 — cosine similarity + per-row top-k of als.py:224-236 with a DETERMINISTIC tie rule (opt-in; the default
+ * graph build stays numpy's on the host because np.argpartition breaks ties in an implementation-defined way).
+ *   Xn = X / (||X||_row + eps);  s_ij = Xn_i . Xn_j, s_ii = 0;
+ *   row i keeps its topk largest s_ij over all j (the zeroed diagonal takes part, as in the reference);
+ *   among entries EQUAL to the topk-th largest value the smaller column index wins.
+ * Output: nbr_idx / nbr_val (n x topk), the kept columns of every row in ascending column order.  The caller forms
+ * S = max(S_kept, S_kept^T) (als.py:239) from the lists.  Xn_work: n x d floats; scratch: scratch_rows x n floats
+ * (one row per resident CTA; 148 * 4 is plenty).  Requires 1 <= topk < n.
+ * ---------------------------------------------------------------------- */
+int b200als_similarity_topk_rows(const float* X, int64_t n, int32_t d, int32_t topk, float eps, float* Xn_work,
+                                 float* scratch, int64_t scratch_rows, int32_t* nbr_idx, float* nbr_val,
+                                 b200als_stream_t stream);
+
 #ifdef __cplusplus
 }
 #endif
