@@ -167,17 +167,27 @@ __global__ void __launch_bounds__(256) graph_sweep_kernel(int k, const int64_t* 
                     const int32_t jl = eme < e1 ? sidx[eme] : 0;
                     const float sl = eme < e1 ? alpha * sval[eme] : 0.0f;
                     const int cnt_e = (int)((e1 - e0) < 32 ? (e1 - e0) : 32);
-#pragma unroll 8
-                    for (int u = 0; u < 32; ++u) {
-                        const int32_t j = __shfl_sync(0xffffffffu, jl, u);
-                        const float sv = __shfl_sync(0xffffffffu, sl, u);
-                        if (u < cnt_e) {
+                    // eight rows of V in flight: all loads of a group are issued before the first is consumed (lanes
+                    // past the end of the row carry weight 0 and column 0: no branch inside the group)
+#pragma unroll 1
+                    for (int u0 = 0; u0 < 32; u0 += 8) {
+                        if (u0 >= cnt_e) break;
+                        float vv[8][NCH];
+#pragma unroll
+                        for (int q = 0; q < 8; ++q) {
+                            const int32_t j = __shfl_sync(0xffffffffu, jl, u0 + q);
                             const float* vj = V + (size_t)j * ldv;
 #pragma unroll
                             for (int t = 0; t < NCH; ++t) {
                                 const int c = lane + 32 * t;
-                                if (c < k) y[t] = fmaf(sv, __ldcg(vj + c), y[t]);
+                                vv[q][t] = c < k ? __ldcg(vj + c) : 0.0f;
                             }
+                        }
+#pragma unroll
+                        for (int q = 0; q < 8; ++q) {
+                            const float sv = __shfl_sync(0xffffffffu, sl, u0 + q);
+#pragma unroll
+                            for (int t = 0; t < NCH; ++t) y[t] = fmaf(sv, vv[q][t], y[t]);
                         }
                     }
                 }
