@@ -15,14 +15,14 @@ data.  The solved rows travel packed: index_select -> all_gather_into_tensor ->
 index_copy_ through a precomputed permutation; the padding slots of the last
 round point at one dummy row appended to each replica.
 
-Fused exchange (the default on a GPU box): every rank maps the other ranks'
+Fused exchange (opt-in, B200ALS_EXCHANGE=peer — see share_replicas): every rank maps the other ranks'
 replicas into its address space (CUDA IPC handles, exchanged once per fit through
 the process group) and the half-step kernel itself stores each solved row and bias
 into all replicas — coalesced 128-byte NVLink writes from the solver's epilogue,
 overlapped with the rows still being solved — so no separate collective moves the
 factors; one small all-reduce per half-step orders the ranks (a kernel's peer
-stores are visible once it has completed).  The packed all-gather stays as the
-fallback (no peer access, CPU `gloo` groups, B200ALS_EXCHANGE=allgather).
+stores are visible once it has completed).  The packed all-gather is the default
+(and the only path on CPU `gloo` groups or without peer access).
 
 Residual sums are combined with one float64 all-reduce per iteration.
 
@@ -132,7 +132,10 @@ class Shard:
         of a kernel on this device), or None when any rank could not set it up — the decision is collective, so
         all ranks fall back to the packed all-gather together."""
         import os
-        if not self.active or os.environ.get("B200ALS_EXCHANGE", "peer") != "peer":
+        # Opt-in until it has passed on a multi-GPU box: measured at N = 2 (round 2), torch's CUDA-IPC import maps the
+        # peer's memory under the PEER's device context, and a kernel of this rank's device then faults on it
+        # (illegal address) although peer access is enabled.  The packed all-gather is the default.
+        if not self.active or os.environ.get("B200ALS_EXCHANGE", "allgather") != "peer":
             return None
         ok, out, err = 1, {}, ""
         try:
