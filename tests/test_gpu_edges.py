@@ -276,7 +276,8 @@ def test_refit_appends_history(cuda_device):
 @pytest.mark.parametrize("k", [32, 64])
 def test_slab_storage_single_rank_equals_fit_coo(cuda_device, k):
     """slab.RatingSlabs with one rank is the whole matrix with local == global ids: the fit through the slab entry
-    (row_ids map in the kernels, per-rank norm shares) must equal the ordinary fit bit for bit."""
+    (row_ids map in the kernels, per-rank norm shares) must equal the ordinary fit — bit for bit where the path is
+    run-to-run deterministic (FFMA), to float32 rounding on the tcgen05 path."""
     import torch
     import b200als
     from b200als.slab import slabs_from_coo
@@ -292,9 +293,15 @@ def test_slab_storage_single_rank_equals_fit_coo(cuda_device, k):
     slabs = slabs_from_coo(rows, cols, torch.from_numpy(vals.astype(np.float32)).to(cuda_device), m, n, 0, 1)
     b = b200als.ALS(cfg).fit_slabs(slabs, tol=None, verbose=0)
     for attr in ("U", "V", "b_u", "b_i"):
-        assert np.array_equal(getattr(a, attr), getattr(b, attr)), attr
+        if k <= 32:
+            assert np.array_equal(getattr(a, attr), getattr(b, attr)), attr       # FFMA path: one CTA per row, bit for bit
+        else:
+            # tcgen05 path: which solver group (forward or reversed elimination order) takes a row depends on the
+            # order the CTAs claim work from the atomic cursor, so two runs of the SAME fit differ at float32
+            # rounding level (measured ~7e-6); a tenth of the parity bar is the bound here
+            assert rel_err(getattr(a, attr), getattr(b, attr)) < 1e-4, attr
     for key in a.history:                       # float64 atomics accumulate in a different order: last-digit agreement
-        assert np.allclose(a.history[key], b.history[key], rtol=1e-12, atol=0), key
+        assert np.allclose(a.history[key], b.history[key], rtol=1e-12 if k <= 32 else 1e-5, atol=0), key
 
 
 @pytest.mark.parametrize("N", [1, 31, 33, 64, 65, 100, 257, 608, 1000])
