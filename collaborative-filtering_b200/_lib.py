@@ -73,6 +73,8 @@ _SIGNATURES = {
                                vp, vp, vp, vp, vp, vp, vp, vp, C.c_size_t, vp, vp],
     "b200als_row_order_workspace_bytes": [C.c_int64, C.POINTER(C.c_size_t)],
     "b200als_row_order": [vp, C.c_int64, vp, vp, vp, C.c_size_t, vp],
+    "b200als_row_order_static_max_rows": [],
+    "b200als_row_order_static": [vp, C.c_int64, vp, vp, vp],
     "b200als_compose_z": [vp, C.c_int64, C.c_int64, C.c_int32, C.c_int32,
                           C.POINTER(vp), C.POINTER(C.c_int32), C.POINTER(vp),
                           C.c_int64, C.c_int32, vp, C.c_int64, vp],
@@ -109,7 +111,7 @@ _SIGNATURES = {
     "b200als_normalize_feature": [vp, C.c_int64, C.c_int32, C.c_int32, C.c_int32, C.c_double, vp, vp, vp, C.c_size_t, vp],
     "b200als_similarity_topk_rows": [vp, C.c_int64, C.c_int32, C.c_int32, C.c_float, vp, vp, C.c_int64, vp, vp, vp],
 }
-_RESTYPES = {"b200als_last_error": C.c_char_p}
+_RESTYPES = {"b200als_last_error": C.c_char_p, "b200als_row_order_static_max_rows": C.c_int64}
 
 EXPORTED_SYMBOLS = tuple(_SIGNATURES)
 

@@ -105,6 +105,21 @@ int b200als_row_order(const int64_t* indptr, int64_t n_rows,
                       void* workspace, size_t workspace_bytes,
                       b200als_stream_t stream);
 
+/* b200als_row_order without any allocation.  No counterpart in the reference: added
+ * for callers that cannot call cudaMalloc (CUDA graph capture, tight serving loops, harnesses that forbid
+ * it).  Same outputs as b200als_row_order; the scratch (sort keys, row ids, radix-sort temporary storage) is a
+ * file-scope `static __device__` array inside the library: 7 MiB, held by every GPU that loads the library until
+ * the process exits.  Limit: n_rows <= B200ALS_ROW_ORDER_STATIC_MAX_ROWS (262 144), larger inputs are rejected with
+ * B200ALS_E_UNSUPPORTED (use b200als_row_order with a caller-owned workspace).  The call itself performs no
+ * cudaMalloc / cudaFree / allocating library call.  Every call shares the array (it keeps the last call's contents;
+ * nothing in it needs to start at zero, *n_nonempty is cleared by the call): calls that overlap on the GPU — two
+ * streams, two host threads — RACE on it and must be serialised by the caller. */
+#define B200ALS_ROW_ORDER_STATIC_MAX_ROWS (1 << 18)
+int64_t b200als_row_order_static_max_rows(void);
+int b200als_row_order_static(const int64_t* indptr, int64_t n_rows,
+                             int32_t* order, int64_t* n_nonempty,
+                             b200als_stream_t stream);
+
 /* ------------------------------------------------------------------------
  * A5 — Z = V + sum_f X_f W_f  (als.py:262-281, 411, 504, 568-572)
  * X_f is (n, d_f) float32 row-major, W_f is (d_f, k) float32 row-major with
