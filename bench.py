@@ -304,6 +304,7 @@ def resident_run(b200als, wl_shape, K, W, shard, path, dev, sampler=None, keep=F
                rmse_last=float(hist[-1, 0]), paths=paths, fused_exchange=bool(getattr(ses, "peers", None)))
     if keep:
         out.update(flat=flat, vals=vals, rt=rt, mu0=mu0)
+    ses.close()
     del ses
     return out
 
@@ -340,6 +341,7 @@ def sharded_vs_single(b200als, rt, mu0, k, shard, path, dev, iters=3):
                "train_rmse_single": [float(x) for x in hist_1[:, 0]]}
         del ses_1
     shard.barrier()
+    ses_s.close()
     del ses_s
     return out
 
@@ -628,6 +630,7 @@ def c5_arm(args):
     check = c5_row_check(ses, slabs, U0, V0, mu0, dev) if rank == 0 else None
     shard.barrier()
     fused = bool(ses.peers)
+    ses.close()
     del ses, V0
     torch.cuda.empty_cache()
     peak_all = float(torch.cuda.max_memory_allocated())          # generation + check included

@@ -64,6 +64,9 @@ _SIGNATURES = {
     "b200als_last_error": [],
     "b200als_device_ok": [],
     "b200als_peer_enable": [C.c_int32],
+    "b200als_ipc_export": [vp, C.c_char_p, C.POINTER(C.c_int64)],
+    "b200als_ipc_import": [C.c_char_p, C.c_int64, C.POINTER(vp)],
+    "b200als_ipc_release": [C.c_char_p],
     "b200als_last_launch_count": [],
     "b200als_last_path": [],
     "b200als_dense_indptr": [vp, C.c_int64, C.c_int64, vp, vp, vp],

@@ -650,8 +650,8 @@ class FitSession:
         if shard.active and not use_graph:
             shared = shard.share_replicas(dict(U=U_d, V=V_d, b_u=self.b_u_d, b_i=self.b_i_d))
             if shared is not None:
-                self.peers = {nm: [t.data_ptr() for t in ts] for nm, ts in shared.items()}
-                self._peer_tensors = shared             # keeps the mappings alive
+                self.peers = shared["ptrs"]
+                self._peer_handles = shared["handles"]  # released by close()
                 self._token = torch.zeros(1, dtype=torch.float32, device=dev)
         # rows that need float64 (small ridge, few ratings) leave the fast lists
         self.u_list, self.u_f64 = self._precision_split(rt.indptr, self.u_list, self.reg_user, None, self.u_ids, False)
@@ -964,6 +964,25 @@ class FitSession:
         self.launches += 1
         self._mark("end")
 
+    def close(self) -> None:
+        """Drop the mappings of the other ranks' replicas (fused exchange).  Every rank has stopped storing into this
+        rank's replicas once the last iteration's all-reduce has completed on its stream; a barrier after the release
+        keeps the owners from freeing the memory under a mapping that is still open."""
+        handles = getattr(self, "_peer_handles", None)
+        if handles:
+            torch.cuda.current_stream().synchronize()
+            Shard.release_replicas(handles, self.dev)
+            self.peers = None
+            self.shard.barrier()
+
+    def __del__(self):
+        try:
+            handles = getattr(self, "_peer_handles", None)
+            if handles:
+                Shard.release_replicas(handles, self.dev)
+        except Exception:   # noqa: BLE001 — interpreter shutdown
+            pass
+
     # ---- host sync points -----------------------------------------------------------------
     def raise_if_bad(self) -> None:
         st = self.status.cpu().numpy()
@@ -980,6 +999,7 @@ class FitSession:
         """Copy the learned parameters back to the model's public float64 attributes."""
         model, rt, k = self.model, self.rt, self.k
         h = self.read_history(done)
+        self.close()
         model._set_history(h)
         if done:
             model.mu = float(h[-1, 5])

@@ -126,48 +126,75 @@ class Shard:
 
     # ---- fused exchange: peer-mapped replicas ------------------------------------
     def share_replicas(self, tensors: dict) -> dict | None:
-        """Map every other rank's copy of each named CUDA tensor into this process.
+        """Map every other rank's copy of each named CUDA tensor into this process, in THIS rank's device context.
 
-        Returns {name: [peer tensors, one per other rank]} (aliases of the peers' memory, usable as store targets
-        of a kernel on this device), or None when any rank could not set it up — the decision is collective, so
-        all ranks fall back to the packed all-gather together."""
+        Returns {"ptrs": {name: [device address on each other rank, in rank order]}, "handles": [bytes, ...]} — the
+        addresses are valid store targets for kernels of this rank's device; `release_replicas(handles)` drops the
+        mappings — or None when any rank could not set it up (the decision is collective: all ranks then use the
+        packed all-gather together).
+
+        Opt-in (B200ALS_EXCHANGE=peer) until it has passed on a multi-GPU box.  The handles are exported / imported by
+        libb200als (b200als_ipc_export / _import: cudaIpcOpenMemHandle with this rank's device current, as NCCL's P2P
+        transport does).  Round 2's first version used torch.multiprocessing's tensor rebuild, which opens the handle
+        under the EXPORTER's device context; kernels of this rank's device then faulted on those addresses at N = 2."""
+        import ctypes as C
         import os
-        # Opt-in until it has passed on a multi-GPU box: measured at N = 2 (round 2), torch's CUDA-IPC import maps the
-        # peer's memory under the PEER's device context, and a kernel of this rank's device then faults on it
-        # (illegal address) although peer access is enabled.  The packed all-gather is the default.
         if not self.active or os.environ.get("B200ALS_EXCHANGE", "allgather") != "peer":
             return None
-        ok, out, err = 1, {}, ""
+        ok, ptrs, handles, err = 1, {}, [], ""
+        first = next(iter(tensors.values()))
         try:
-            first = next(iter(tensors.values()))
             if not first.is_cuda or self.world - 1 > 7:
                 raise RuntimeError("peer exchange needs CUDA tensors and at most 8 ranks")
-            from torch.multiprocessing.reductions import reduce_tensor
             from . import _lib
-            mine = {nm: reduce_tensor(t) for nm, t in tensors.items()}
+            lib = _lib.load()
+            mine = {}
+            for nm, t in tensors.items():
+                if not t.is_contiguous():
+                    raise RuntimeError(f"replica '{nm}' is not contiguous")
+                buf, off = C.create_string_buffer(64), C.c_int64(0)
+                if lib.b200als_ipc_export(t.data_ptr(), buf, C.byref(off)) != 0:
+                    raise RuntimeError(_lib.last_error())
+                mine[nm] = (buf.raw, int(off.value), tuple(t.shape), str(t.dtype), int(t.device.index))
             box = [None] * self.world
             td.all_gather_object(box, mine, group=self.group)
-            lib = _lib.load()
-            for r, entry in enumerate(box):
-                if r == self.rank:
-                    continue
-                for nm, (rebuild, args) in entry.items():
-                    t = rebuild(*args)
-                    if lib.b200als_peer_enable(int(t.device.index)) != 0:
-                        raise RuntimeError(_lib.last_error())
-                    if tuple(t.shape) != tuple(tensors[nm].shape) or t.stride() != tensors[nm].stride():
-                        raise RuntimeError(f"replica '{nm}' differs in shape between ranks")
-                    out.setdefault(nm, []).append(t)
+            with torch.cuda.device(first.device):
+                for r, entry in enumerate(box):
+                    if r == self.rank:
+                        continue
+                    for nm, (h, off, shape, dtype, dev_idx) in entry.items():
+                        if shape != tuple(tensors[nm].shape) or dtype != str(tensors[nm].dtype):
+                            raise RuntimeError(f"replica '{nm}' differs in shape or dtype between ranks")
+                        if lib.b200als_peer_enable(dev_idx) != 0:
+                            raise RuntimeError(_lib.last_error())
+                        out = C.c_void_p(0)
+                        if lib.b200als_ipc_import(h, off, C.byref(out)) != 0:
+                            raise RuntimeError(_lib.last_error())
+                        handles.append(h)
+                        ptrs.setdefault(nm, []).append(int(out.value))
         except Exception as e:   # noqa: BLE001 — any failure means: use the collective instead
             ok, err = 0, f"{type(e).__name__}: {e}"
-        flag = torch.tensor([ok], dtype=torch.int32, device=next(iter(tensors.values())).device)
+        flag = torch.tensor([ok], dtype=torch.int32, device=first.device)
         td.all_reduce(flag, op=td.ReduceOp.MIN, group=self.group)
         if int(flag.item()) == 0:
+            self.release_replicas(handles, first.device)
             if err:
                 import logging
                 logging.getLogger(__name__).warning("peer-mapped exchange unavailable (%s): using all-gather", err)
             return None
-        return out
+        return {"ptrs": ptrs, "handles": handles}
+
+    @staticmethod
+    def release_replicas(handles, device) -> None:
+        """Drop the mappings made by share_replicas (call once every rank has stopped storing into them)."""
+        if not handles:
+            return
+        from . import _lib
+        lib = _lib.load()
+        with torch.cuda.device(device):
+            for h in handles:
+                lib.b200als_ipc_release(h)
+        handles.clear()
 
     def order_ranks(self, token: torch.Tensor) -> None:
         """Every rank's work enqueued so far (peer stores included) is complete before anything enqueued after

@@ -53,6 +53,16 @@ int         b200als_device_ok(void);
 /* Let kernels on the current device store into memory of `peer_device` (NVLink peer access; idempotent).  Needed
  * before b200als_step_args.peer_X / peer_bias point at another GPU's replicas. */
 int         b200als_peer_enable(int32_t peer_device);
+/* Replicas of the other ranks of a box for the fused exchange (peer_X / peer_bias of b200als_step_args); no counterpart
+ * in the reference, which is one process.  export: the 64-byte CUDA IPC handle of the cudaMalloc block that holds
+ * dev_ptr and dev_ptr's offset inside it (the owner sends both to the other ranks by any means).  import: the address
+ * of that memory in THIS process, mapped with the CURRENT device's context (cudaIpcMemLazyEnablePeerAccess) so that
+ * kernels of the current device can store into it; opens are cached and reference counted per (device, handle).
+ * release: drops one reference (the mapping is closed with the last one).  The owner must keep the memory allocated
+ * until every importer has released it. */
+int         b200als_ipc_export(const void* dev_ptr, void* handle64_host, int64_t* offset_host);
+int         b200als_ipc_import(const void* handle64_host, int64_t offset, void** ptr_out_host);
+int         b200als_ipc_release(const void* handle64_host);
 
 /* ------------------------------------------------------------------------
  * A1 — CSR / CSC construction (als.py:335-340), index-bit-exact:
