@@ -412,6 +412,11 @@ def c2_run(b200als, dev, n_iters, with_cpu=True):
         return dt, model, pred
 
     one()                                            # warm-up (context, module load)
+    # a fit that has to build the similarity graph (the first fold of a trial) ...
+    from b200als import graph as _graph
+    _graph._S_CACHE.clear()
+    t_cold, _, _ = one()
+    # ... and fits that find it built (every later fold of the trial: same features, top-k and eps)
     times = []
     for _ in range(3):
         dt, model, pred = one()
@@ -431,7 +436,10 @@ def c2_run(b200als, dev, n_iters, with_cpu=True):
     t = float(np.median(times))
     out = {"workload": WORKLOAD_NAMES["c2"], "users": c.m, "items": c.n, "ratings": nnz, "k": cfgd["core"]["n_factors"],
            "iterations": n_iters, "model": "biases + W_f(genres, years) + inverse_sqrt + genres Laplacian (alpha 0.5, topk 50)",
-           "seconds_fit_predict": t, "seconds_all": times, "value": nnz * n_iters / t, "unit": "ratings/s",
+           "seconds_fit_predict": t, "seconds_all": times, "seconds_fit_predict_graph_rebuilt": t_cold,
+           "graph_reuse": "the similarity graph depends only on (feature matrix, top-k, eps): built once, reused by the "
+                          "later folds of a trial (graph.similarity_topk_cached); seconds_fit_predict is a fit that reuses it",
+           "value": nnz * n_iters / t, "unit": "ratings/s",
            "timed_like": "scripts/evaluate_models.py:245-255 (construct + fit(dense R, features) + dense predict)",
            "phase_ms_total": ph, "session_setup_s": setup_s, "timings": dict(m2.timings),
            "graph_levels": int(ses.level_ptr.size - 1) if ses.use_graph else 0,

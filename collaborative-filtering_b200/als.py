@@ -538,13 +538,17 @@ class FitSession:
                 elif model.graph_build not in ("host", "device"):
                     raise ValueError(f"graph_build={model.graph_build!r}: expected 'host' or 'device'")
                 else:
-                    model.S = _graph.similarity_topk(Xg, model.S_topk, model.S_eps)
+                    # the reference's own numpy calls (tie parity); the same graph is reused across the folds of a trial
+                    model.S, csr_, D_ = _graph.similarity_topk_cached(Xg, model.S_topk, model.S_eps)
+                    self.S_host = (csr_, D_)
                 model.timings["S_build_s"] = time.perf_counter() - t0
         use_graph = self.use_graph = (model.S is not None) or (getattr(self, "S_csr", None) is not None)
         if use_graph and getattr(self, "S_csr", None) is not None:
             D = self.S_csr[3]
+        elif use_graph and getattr(self, "S_host", None) is not None:
+            D = self.S_host[1]                                          # als.py:357 (S's dtype), cached with S
         else:
-            D = model.S.sum(axis=1) if use_graph else None              # als.py:357 (S's dtype)
+            D = model.S.sum(axis=1) if use_graph else None
 
         # ---- init (als.py:360-376): same PCG64 stream, order U, V, W_f ----------
         m_pad, n_pad = shard.padded_rows(m), shard.padded_rows(n)
@@ -670,7 +674,12 @@ class FitSession:
 
         if use_graph:
             t0 = time.perf_counter()
-            sptr, sidx, sval = self.S_csr[:3] if getattr(self, "S_csr", None) is not None else _graph.to_csr(model.S)
+            if getattr(self, "S_csr", None) is not None:
+                sptr, sidx, sval = self.S_csr[:3]
+            elif getattr(self, "S_host", None) is not None:
+                sptr, sidx, sval = self.S_host[0]
+            else:
+                sptr, sidx, sval = _graph.to_csr(model.S)
             self.level_ptr, level_rows = _graph.level_schedule(sptr, sidx, item_counts > 0)
             model.timings["S_csr_levels_s"] = time.perf_counter() - t0
             self.sptr_d = torch.from_numpy(sptr).to(dev)

@@ -131,7 +131,10 @@ __global__ void __launch_bounds__(256) graph_sweep_kernel(int k, const int64_t* 
     cg::grid_group grid = cg::this_grid();
     const int lane = threadIdx.x & 31, w = threadIdx.x >> 5;
     const bool active = w < warps_per_cta;
-    float* Ls = sweep_sm + (size_t)w * k * k;
+    // the factor is staged with an ODD row stride: rows (backward substitution) and columns (forward substitution) of L
+    // are then both conflict-free for the 32 lanes
+    const int ks = k | 1;
+    float* Ls = sweep_sm + (size_t)w * k * ks;
     const int64_t gw = (int64_t)blockIdx.x * warps_per_cta + w, nw = (int64_t)gridDim.x * warps_per_cta;
     const int kk = k * k;
     for (int lv = 0; lv < n_levels; ++lv) {
@@ -141,14 +144,22 @@ __global__ void __launch_bounds__(256) graph_sweep_kernel(int k, const int64_t* 
                 const int64_t i = level_rows[slot];
                 const float* L = chol + (size_t)i * kk;
                 const float* ax = aux + (size_t)i * (2 * k + 2);
-                // stage the factor (kk is a multiple of 4 only when k is even: scalar tail)
+                // stage the factor: coalesced 16-byte global loads, scalar shared stores (the odd stride breaks the
+                // 16-byte alignment of the rows)
                 const int kk4 = kk & ~3;
                 if ((((uintptr_t)L) & 15) == 0) {
-                    for (int e = lane * 4; e < kk4; e += 128)
-                        *reinterpret_cast<float4*>(Ls + e) = *reinterpret_cast<const float4*>(L + e);
-                    for (int e = kk4 + lane; e < kk; e += 32) Ls[e] = L[e];
+                    for (int e = lane * 4; e < kk4; e += 128) {
+                        const float4 v = *reinterpret_cast<const float4*>(L + e);
+                        const float vv4[4] = {v.x, v.y, v.z, v.w};
+#pragma unroll
+                        for (int u = 0; u < 4; ++u) {
+                            const int ee = e + u, rr = ee / k;
+                            Ls[rr * ks + (ee - rr * k)] = vv4[u];
+                        }
+                    }
+                    for (int e = kk4 + lane; e < kk; e += 32) { const int rr = e / k; Ls[rr * ks + (e - rr * k)] = L[e]; }
                 } else {
-                    for (int e = lane; e < kk; e += 32) Ls[e] = L[e];
+                    for (int e = lane; e < kk; e += 32) { const int rr = e / k; Ls[rr * ks + (e - rr * k)] = L[e]; }
                 }
                 const float bold = b_i[i];
                 float y[NCH];
@@ -192,28 +203,38 @@ __global__ void __launch_bounds__(256) graph_sweep_kernel(int k, const int64_t* 
                     }
                 }
                 __syncwarp();
-                // forward: L y' = y, row by row
-                for (int r = 0; r < k; ++r) {
-                    const float* Lr = Ls + r * k;
-                    float part = 0.0f;
+                // reciprocals of the diagonal, once (the divisions leave the substitution chains)
+                float dinv[NCH];
 #pragma unroll
-                    for (int t = 0; t < NCH; ++t) {
-                        const int c = lane + 32 * t;
-                        if (c < r) part = fmaf(Lr[c], y[t], part);
-                    }
-                    part = warp_sum(part);
-#pragma unroll
-                    for (int t = 0; t < NCH; ++t)
-                        if (lane + 32 * t == r) y[t] = (y[t] - part) / Lr[r];
+                for (int t = 0; t < NCH; ++t) {
+                    const int c = lane + 32 * t;
+                    dinv[t] = c < k ? 1.0f / Ls[c * ks + c] : 0.0f;
                 }
-                // backward: L^T x = y', column by column (rank-1 updates with row r of L)
-                for (int r = k - 1; r >= 0; --r) {
-                    const float* Lr = Ls + r * k;
+                // forward, column-oriented: y_r = y_r / L_rr is final once the columns before r are folded in; its
+                // owner broadcasts it and every lane c > r folds column r in (L[c][r]: stride ks, conflict-free).
+                // Chain per unknown: multiply, shuffle, multiply-add (the row-oriented form cost a five-shuffle
+                // reduction and a division per unknown).
+                for (int r = 0; r < k; ++r) {
                     float mine = 0.0f;
 #pragma unroll
                     for (int t = 0; t < NCH; ++t)
-                        if (t == (r >> 5)) mine = y[t];
-                    float xr = __shfl_sync(0xffffffffu, mine, r & 31) / Lr[r];
+                        if (t == (r >> 5)) mine = y[t] * dinv[t];
+                    const float yr = __shfl_sync(0xffffffffu, mine, r & 31);
+#pragma unroll
+                    for (int t = 0; t < NCH; ++t) {
+                        const int c = lane + 32 * t;
+                        if (c == r) y[t] = yr;
+                        else if (c > r && c < k) y[t] = fmaf(-Ls[c * ks + r], yr, y[t]);
+                    }
+                }
+                // backward: L^T x = y', column-oriented as well (rank-1 updates with row r of L)
+                for (int r = k - 1; r >= 0; --r) {
+                    const float* Lr = Ls + r * ks;
+                    float mine = 0.0f;
+#pragma unroll
+                    for (int t = 0; t < NCH; ++t)
+                        if (t == (r >> 5)) mine = y[t] * dinv[t];
+                    const float xr = __shfl_sync(0xffffffffu, mine, r & 31);
 #pragma unroll
                     for (int t = 0; t < NCH; ++t) {
                         const int c = lane + 32 * t;
@@ -249,7 +270,7 @@ static int launch_graph_sweep(int k, const int64_t* level_ptr, int n_levels, int
                               const float* sval, float alpha, float lam_bias, const float* lam_bias_row, float* V,
                               int64_t ldv, float* b_i, cudaStream_t s) {
     auto kern = graph_sweep_kernel<NCH>;
-    const size_t per_warp = sizeof(float) * (size_t)k * k;
+    const size_t per_warp = sizeof(float) * (size_t)k * (size_t)(k | 1);
     int wpc = (int)((200 * 1024) / per_warp);
     if (wpc > 8) wpc = 8;
     if (wpc < 1) {

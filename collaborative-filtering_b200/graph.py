@@ -128,6 +128,32 @@ def level_schedule(sptr: np.ndarray, sidx: np.ndarray, rated: np.ndarray):
     return level_ptr, rows.astype(np.int32)
 
 
+# ---- the same graph for every fold of a trial --------------------------------------------------------
+# The drivers fit one model per fold with the SAME feature matrix, top-k and eps (tune_params.py:341-421,
+# evaluate_models.py:194-276), and the similarity graph depends on nothing else (als.py:220-240) — but at the bundled
+# shape building it is the largest single piece of a fit (0.12 s of 0.26 s).  The last few graphs are kept, keyed by a
+# digest of the feature matrix's bytes, its shape / dtype, top-k and eps.  A hit returns the SAME arrays (S is shared
+# between the models that asked for it: treat `model.S` as read-only, as the reference's own code does).
+_S_CACHE: dict = {}
+_S_CACHE_MAX = 2
+
+
+def similarity_topk_cached(X: np.ndarray, topk, eps: float):
+    """(S, (sptr, sidx, sval), D) of `similarity_topk` / `to_csr` / `S.sum(axis=1)`, computed once per distinct input."""
+    import hashlib
+    Xc = np.ascontiguousarray(X)
+    key = (hashlib.blake2b(Xc.view(np.uint8).reshape(-1), digest_size=16).digest(), Xc.shape, str(Xc.dtype),
+           None if topk is None else int(topk), float(eps))
+    hit = _S_CACHE.get(key)
+    if hit is None:
+        S = similarity_topk(X, topk, eps)
+        hit = (S, to_csr(S), S.sum(axis=1))                              # als.py:357: D in S's dtype
+        while len(_S_CACHE) >= _S_CACHE_MAX:
+            _S_CACHE.pop(next(iter(_S_CACHE)))
+        _S_CACHE[key] = hit
+    return hit
+
+
 # ---- opt-in device build (SURVEY.md §8f N3) -------------------------------------------------------
 def topk_rule_reference(X: np.ndarray, topk: int, eps: float) -> np.ndarray:
     """The DOCUMENTED tie rule of the device build, restated in numpy (tests compare the kernel with this):
