@@ -427,3 +427,25 @@ def test_device_graph_build_tie_rule_and_fit(cuda_device):
     S_d = G.csr_to_dense(*model.S_csr, c.n)
     if np.array_equal(S_d != 0, host.S != 0):                    # same graph (no ties in this fixture) -> same fit
         assert rel_err(model.V, host.V) < 1e-4
+
+
+def test_refit_matches_reference_fixture(cuda_device):
+    """Two fits on one object against the reference's own (tests/golden/small_refit.npz): combined history, and the
+    second fit's early stop decided on entries of the first (it stops after one iteration, like the reference)."""
+    import json
+    import b200als
+    z = np.load(os.path.join(GOLDEN, "small_refit.npz"))
+    cfgd, fits = json.loads(str(z["cfg"])), json.loads(str(z["fits"]))
+    m, n = int(z["m"]), int(z["n"])
+    model = b200als.ALS(b200als.ALSConfig(core=b200als.CoreConfig(**cfgd["core"]),
+                                          biases=b200als.BiasesConfig(**cfgd["biases"])))
+    for j, kw in enumerate(fits):
+        model.fit_coo(z[f"flat_idx_{j}"], z[f"vals_{j}"], (m, n), tol=kw["tol"], min_iters=kw["min_iters"], verbose=0)
+        assert len(model.history["train_rmse"]) == int(z[f"len_after_{j}"])
+        for a in ("U", "V", "b_u", "b_i"):
+            assert rel_err(getattr(model, a), z[f"{a}_{j}"]) < FACTOR_TOL, (j, a)
+        assert abs(model.mu - float(z[f"mu_{j}"])) < RMSE_TOL
+    for key in ("train_rmse", "U_norm", "V_norm", "bu_norm", "bi_norm"):
+        got, want = np.asarray(model.history[key]), z["hist_" + key]
+        assert got.shape == want.shape
+        assert np.abs(got - want).max() < (RMSE_TOL if key == "train_rmse" else 1e-3 * max(1.0, np.abs(want).max())), key

@@ -1,10 +1,12 @@
 """CPU: the oracle (oracle/als_oracle.py) against fixtures produced by the unmodified
 reference (tests/golden/make_golden.py).  Same numpy/scipy calls on the same operands →
 bit-identical, including every per-iteration snapshot."""
+import os
+
 import numpy as np
 import pytest
 
-from _util import SMALL_CASES, bundled_features, load_case, run_oracle
+from _util import GOLDEN, SMALL_CASES, bundled_features, load_case, run_oracle
 
 
 @pytest.mark.parametrize("name", SMALL_CASES)
@@ -86,3 +88,26 @@ def test_oracle_csr_csc_match_numpy_flatnonzero():
     assert np.array_equal(sp["rows_u"], ru) and np.array_equal(sp["indices"], ri)
     # perm maps CSC positions to CSR positions
     assert np.array_equal(sp["vals"][sp["perm"]], sp["cvals"])
+
+
+def test_refit_on_the_same_object_matches_reference():
+    """history is created once and every fit() appends (scripts/als.py:185-191, 510-517); `_converged` of a second fit
+    looks at entries of the first — tests/golden/small_refit.npz (make_golden_refit.py) pins the reference's
+    behaviour, including the second fit stopping after ONE iteration."""
+    import json
+    import als_oracle
+    import b200als
+    z = np.load(os.path.join(GOLDEN, "small_refit.npz"))
+    cfgd, fits = json.loads(str(z["cfg"])), json.loads(str(z["fits"]))
+    m, n = int(z["m"]), int(z["n"])
+    cfg = b200als.ALSConfig(core=b200als.CoreConfig(**cfgd["core"]), biases=b200als.BiasesConfig(**cfgd["biases"]))
+    o = als_oracle.SparseALSOracle(cfg)
+    for j, kw in enumerate(fits):
+        sp = als_oracle.csr_csc_from_flat(z[f"flat_idx_{j}"], z[f"vals_{j}"], m, n)
+        o.fit_sparse(sp, m, n, tol=kw["tol"], min_iters=kw["min_iters"])
+        assert len(o.history["train_rmse"]) == int(z[f"len_after_{j}"])
+        assert np.array_equal(o.U, z[f"U_{j}"]) and np.array_equal(o.V, z[f"V_{j}"])
+        assert np.array_equal(o.b_u, z[f"b_u_{j}"]) and np.array_equal(o.b_i, z[f"b_i_{j}"])
+    assert int(z["len_after_1"]) == int(z["len_after_0"]) + 1          # the quirk the fixture exists for
+    for key in o.history:
+        assert np.array_equal(np.asarray(o.history[key]), z["hist_" + key]), key
