@@ -125,3 +125,25 @@ def test_readback_float64_copies(monkeypatch):
         readback.f64_from_device(base, mode="lazy")
     monkeypatch.setenv("B200ALS_READBACK", "pipelined")
     assert np.array_equal(readback.f64_from_device(base), base.double().numpy())
+
+
+def test_similarity_graph_is_reused_for_identical_inputs():
+    """graph.similarity_topk_cached: the graph depends only on (feature matrix, top-k, eps) (scripts/als.py:220-240), so
+    the folds of a trial share one build; a different matrix, top-k or eps is a different entry; at most two are kept."""
+    from b200als import graph as G
+    G._S_CACHE.clear()
+    rng = np.random.default_rng(2)
+    X = (rng.random((300, 7)) < 0.3).astype(np.float32)
+    S1, csr1, D1 = G.similarity_topk_cached(X, 20, 1e-8)
+    S2, csr2, D2 = G.similarity_topk_cached(X.copy(), 20, 1e-8)           # same bytes, another object
+    assert S2 is S1 and csr2 is csr1 and D2 is D1
+    assert np.array_equal(S1, G.similarity_topk(X, 20, 1e-8))
+    assert np.array_equal(D1, S1.sum(axis=1)) and D1.dtype == S1.dtype      # als.py:357: D in S's dtype
+    sp, si, sv = G.to_csr(S1)
+    assert np.array_equal(csr1[0], sp) and np.array_equal(csr1[1], si) and np.array_equal(csr1[2], sv)
+    Y = X.copy(); Y[0, 0] = 1.0 - Y[0, 0]
+    assert G.similarity_topk_cached(Y, 20, 1e-8)[0] is not S1
+    assert G.similarity_topk_cached(X, 21, 1e-8)[0] is not S1
+    assert len(G._S_CACHE) <= G._S_CACHE_MAX
+    assert G.similarity_topk_cached(X.astype(np.float64), 20, 1e-8)[0].dtype == np.float64
+    G._S_CACHE.clear()
