@@ -125,6 +125,12 @@ __device__ __forceinline__ void sts_b64_nc(uint32_t a, uint32_t x, uint32_t y) {
 }
 __device__ __forceinline__ uint32_t bf162_bits(__nv_bfloat162 v) { return *reinterpret_cast<uint32_t*>(&v); }
 
+// 0 (default): diag4; 1: diag4p, the software-pipelined variant — correct (parity suite green) but measured NOT faster
+// on B200: C4 user half-step 35.3 ms (unchanged), k = 64 shapes ~5 % slower (its 96-register solver starts to spill)
+#ifndef B200ALS_DIAG_PIPELINE
+#define B200ALS_DIAG_PIPELINE 0
+#endif
+
 template <int K, int RPW>
 struct Ldl {
     static constexpr int NW = K / RPW;       // warps per group (4)
@@ -296,6 +302,109 @@ struct Ldl {
             a[c4 - 2] = fmaf(-w3, v3.z, fmaf(-w2, v2.z, fmaf(-w1, v1.z, fmaf(-w0, v0.z, a[c4 + 2]))));
             a[c4 - 1] = fmaf(-w3, v3.w, fmaf(-w2, v2.w, fmaf(-w1, v1.w, fmaf(-w0, v0.w, a[c4 + 3]))));
         }
+    }
+
+    // diag4 software-pipelined (B200ALS_DIAG_PIPELINE=1; kept as a measured negative, off by default).  A step is a long dependent pivot chain followed by
+    // the rank-4 update of the window's remaining columns; the NEXT step's chain needs only the first four of them.  So a
+    // step applies only the first update group (columns 4..7 -> the next pivots) and hands its multipliers w and its
+    // raw-row buffer to the next step, which applies the other groups (DEFER) in the same basic block as its own pivot
+    // chain: independent LDS.128 + FFMA work that the scheduler interleaves with the chain's dependent instructions.
+    // The raw-row scratch is double buffered by step parity, so the previous step's rows are intact while this step
+    // publishes its own.  Same operations per entry, in the same order, as diag4.
+    template <bool DEFER>
+    static __device__ __forceinline__ void diag4p(float (&a)[RPW], float& rhs, bool& ok, float (&wp)[4], uint32_t& rwp,
+                                                  const float ridge, const int r, const uint32_t cbs, const int j0,
+                                                  const bool final_step) {
+        const int g = j0 >> 2;
+        const uint32_t zb = cbs + Z_OFF;
+        const uint32_t raw = cbs + RAW_OFF + (uint32_t)(g & 1) * (4u * RAWSZ);
+        const uint32_t S4 = 4u * (uint32_t)(K - 4 * g);
+        const uint32_t col0 = col_block(cbs, g);
+        const int dr = r - j0;
+        const uint32_t dmy = raw + 4u * (uint32_t)(4 * K + 4);
+#pragma unroll
+        for (int s = 0; s < 4; ++s) sts_f32(raw + 4u * (uint32_t)(s * K + r), a[s]);
+        sts_f32(raw + 4u * (uint32_t)(4 * K) + 4u * min((uint32_t)dr, 4u), rhs);
+        __syncwarp();
+        const float4 p0 = lds_f32x4(raw + 4u * (uint32_t)(0 * K + j0));
+        const float4 p1 = lds_f32x4(raw + 4u * (uint32_t)(1 * K + j0));
+        const float4 p2 = lds_f32x4(raw + 4u * (uint32_t)(2 * K + j0));
+        const float4 p3 = lds_f32x4(raw + 4u * (uint32_t)(3 * K + j0));
+        const float4 zr = lds_f32x4(raw + 4u * (uint32_t)(4 * K));
+        if (DEFER) {
+            // the previous step's update of its window columns 8 .. RPW-1 (that step only slid its first group)
+            const float q0 = wp[0], q1 = wp[1], q2 = wp[2], q3 = wp[3];
+#pragma unroll
+            for (int c4 = 8; c4 < RPW; c4 += 4) {
+                const float4 v0 = lds_f32x4(rwp + 4u * (uint32_t)(0 * K + c4));
+                const float4 v1 = lds_f32x4(rwp + 4u * (uint32_t)(1 * K + c4));
+                const float4 v2 = lds_f32x4(rwp + 4u * (uint32_t)(2 * K + c4));
+                const float4 v3 = lds_f32x4(rwp + 4u * (uint32_t)(3 * K + c4));
+                a[c4 - 4] = fmaf(-q3, v3.x, fmaf(-q2, v2.x, fmaf(-q1, v1.x, fmaf(-q0, v0.x, a[c4 + 0]))));
+                a[c4 - 3] = fmaf(-q3, v3.y, fmaf(-q2, v2.y, fmaf(-q1, v1.y, fmaf(-q0, v0.y, a[c4 + 1]))));
+                a[c4 - 2] = fmaf(-q3, v3.z, fmaf(-q2, v2.z, fmaf(-q1, v1.z, fmaf(-q0, v0.z, a[c4 + 2]))));
+                a[c4 - 1] = fmaf(-q3, v3.w, fmaf(-q2, v2.w, fmaf(-q1, v1.w, fmaf(-q0, v0.w, a[c4 + 3]))));
+            }
+        }
+        const float d0 = p0.x + ridge, c11 = p1.y + ridge;
+        const float det1 = fmaf(d0, c11, -p0.y * p0.y);
+        const float i0 = rcp_approx(d0), i1 = d0 * rcp_approx(det1);
+        const float d1 = det1 * i0;
+        const float l10 = p0.y * i0, l20 = p0.z * i0, l30 = p0.w * i0;
+        const float u21 = fmaf(-l20, p0.y, p1.z), u31 = fmaf(-l30, p0.y, p1.w);
+        const float l21 = u21 * i1, l31 = u31 * i1;
+        const float d2 = fmaf(-l21, u21, fmaf(-l20, p0.z, p2.z + ridge));
+        const float u32 = fmaf(-l31, u21, fmaf(-l30, p0.z, p2.w));
+        const float s33 = fmaf(-l31, u31, fmaf(-l30, p0.w, p3.w + ridge));
+        const float det2 = fmaf(d2, s33, -u32 * u32);
+        const float i2 = rcp_approx(d2), i3 = d2 * rcp_approx(det2);
+        const float d3 = det2 * i2;
+        const float l32 = u32 * i2;
+        const float u0 = a[0], t0 = u0 * i0;
+        const float u1 = fmaf(-t0, p0.y, a[1]), t1 = u1 * i1;
+        const float u2 = fmaf(-t1, u21, fmaf(-t0, p0.z, a[2])), t2 = u2 * i2;
+        const float u3 = fmaf(-t2, u32, fmaf(-t1, u31, fmaf(-t0, p0.w, a[3]))), t3 = u3 * i3;
+        sts_f32(dr >= 0 ? col0 + 4u * r : dmy, u0);
+        sts_f32(dr >= 1 ? col0 + S4 + 4u * r : dmy, u1);
+        sts_f32(dr >= 2 ? col0 + 2u * S4 + 4u * r : dmy, u2);
+        sts_f32(dr >= 3 ? col0 + 3u * S4 + 4u * r : dmy, u3);
+        const float z0 = zr.x;
+        const float z1 = fmaf(-l10, z0, zr.y);
+        const float z2 = fmaf(-l21, z1, fmaf(-l20, z0, zr.z));
+        const float z3 = fmaf(-l32, z2, fmaf(-l31, z1, fmaf(-l30, z0, zr.w)));
+        {
+            const bool piv = (unsigned)dr < 4u;
+            const bool e1 = dr == 1, e2 = dr == 2, e3 = dr == 3;
+            float zsel = e1 ? z1 : z0, dsel = e1 ? d1 : d0, isel = e1 ? i1 : i0;
+            zsel = e2 ? z2 : zsel; dsel = e2 ? d2 : dsel; isel = e2 ? i2 : isel;
+            zsel = e3 ? z3 : zsel; dsel = e3 ? d3 : dsel; isel = e3 ? i3 : isel;
+            sts_f32(piv ? zb + 4u * r : dmy, zsel);
+            sts_f32(piv ? cbs + INV_OFF + 4u * r : dmy, isel);
+            // 1/sqrt(d) for the tensor-core panel of the rows below: stored whether or not this phase feeds an update
+            // (the x array is free until the back substitution) — no branch inside the step
+            sts_f32(piv ? cbs + X_OFF + 4u * r : dmy, rsqrt_approx(dsel));
+            ok = piv ? (dsel > 0.0f) : ok;
+        }
+        if (final_step) return;
+        rhs = fmaf(-t3, z3, fmaf(-t2, z2, fmaf(-t1, z1, fmaf(-t0, z0, rhs))));
+        const float w3 = t3;
+        const float w2 = fmaf(-w3, l32, t2);
+        const float w1 = fmaf(-w3, l31, fmaf(-w2, l21, t1));
+        const float w0 = fmaf(-w3, l30, fmaf(-w2, l20, fmaf(-w1, l10, t0)));
+        const uint32_t rw = raw + 4u * (uint32_t)j0;
+        {
+            // first update group only: the next step's pivots
+            const float4 v0 = lds_f32x4(rw + 4u * (uint32_t)(0 * K + 4));
+            const float4 v1 = lds_f32x4(rw + 4u * (uint32_t)(1 * K + 4));
+            const float4 v2 = lds_f32x4(rw + 4u * (uint32_t)(2 * K + 4));
+            const float4 v3 = lds_f32x4(rw + 4u * (uint32_t)(3 * K + 4));
+            a[0] = fmaf(-w3, v3.x, fmaf(-w2, v2.x, fmaf(-w1, v1.x, fmaf(-w0, v0.x, a[4]))));
+            a[1] = fmaf(-w3, v3.y, fmaf(-w2, v2.y, fmaf(-w1, v1.y, fmaf(-w0, v0.y, a[5]))));
+            a[2] = fmaf(-w3, v3.z, fmaf(-w2, v2.z, fmaf(-w1, v1.z, fmaf(-w0, v0.z, a[6]))));
+            a[3] = fmaf(-w3, v3.w, fmaf(-w2, v2.w, fmaf(-w1, v1.w, fmaf(-w0, v0.w, a[7]))));
+        }
+        wp[0] = w0; wp[1] = w1; wp[2] = w2; wp[3] = w3;
+        rwp = rw;
     }
 
     // Rows below the diagonal block J0 .. J0 + RPW - 1 (finished, in the column store): forward substitution of the
@@ -504,9 +613,20 @@ struct Ldl {
             const bool tile_on = p < MMA_PHASES;
             if (p == q) {
                 // the diagonal block: this warp alone, four columns per step
+#if B200ALS_DIAG_PIPELINE
+                {
+                    float wp[4] = {0.0f, 0.0f, 0.0f, 0.0f};
+                    uint32_t rwp = 0;
+                    diag4p<false>(a, rhs, ok, wp, rwp, ridge, r, cbs, p * RPW, false);
+#pragma unroll 1
+                    for (int it = 1; it < RPW / 4; ++it)
+                        diag4p<true>(a, rhs, ok, wp, rwp, ridge, r, cbs, p * RPW + 4 * it, it == RPW / 4 - 1);
+                }
+#else
 #pragma unroll 1
                 for (int it = 0; it < RPW / 4; ++it)
                     diag4(a, rhs, ok, ridge, r, cbs, p * RPW + 4 * it, tile_on, it == RPW / 4 - 1);
+#endif
                 if (nthr > 32) {
                     named_bar_arrive(bar_id, nthr);        // block, z, 1/d, 1/sqrt(d) published: the rows below substitute
                     named_bar_arrive(start_bar, nthr);     // and this warp signs off on the phase
