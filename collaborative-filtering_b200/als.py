@@ -1000,6 +1000,14 @@ class FitSession:
 
     # ---- host sync points -----------------------------------------------------------------
     def raise_if_bad(self) -> None:
+        if self.shard.active:
+            # every rank must take the same branch here (the ranks meet again in the next collective): the counts
+            # are summed over the ranks, so a system that is not positive definite on ONE rank raises on all of them
+            cnt = self.status[:1].to(torch.float32)
+            self.shard.all_reduce_sum(cnt)
+            if float(cnt.item()) != 0.0 and int(self.status[0].item()) == 0:
+                raise np.linalg.LinAlgError(
+                    f"{int(cnt.item())} normal matrices were not positive definite (on another rank)")
         st = self.status.cpu().numpy()
         if st[0] != 0:
             raise np.linalg.LinAlgError(
@@ -1013,8 +1021,10 @@ class FitSession:
     def finish(self, done: int) -> None:
         """Copy the learned parameters back to the model's public float64 attributes."""
         model, rt, k = self.model, self.rt, self.k
-        h = self.read_history(done)
-        self.close()
+        try:
+            h = self.read_history(done)
+        finally:
+            self.close()        # also on the LinAlgError path: every rank releases its mappings and meets the barrier
         model._set_history(h)
         if done:
             model.mu = float(h[-1, 5])

@@ -36,6 +36,20 @@ for k, (m, n, nnz) in ((64, (3000, 500, 120000)), (128, (700, 900, 60000)), (32,
         assert abs(h1[-1] - want) < 1e-5 * max(want, 1.0), (k, key, h1[-1], want)
     if td.get_rank() == 0:
         print(f"k={k} world={td.get_world_size()} ok: rmse {r1:.6f} vs {r2:.6f}")
+# a system that is not positive definite: every rank raises numpy.linalg.LinAlgError (helpers.py:19), none hangs —
+# the rows are dealt over the ranks, so without the summed status word only SOME ranks would see a bad pivot
+flat, vals = synth_ratings(200, 150, 4000, seed=9)
+cfg = b200als.ALSConfig(core=b200als.CoreConfig(n_factors=64, n_iters=2, lambda_u=-50.0, lambda_v=3.0),
+                        biases=b200als.BiasesConfig(lambda_bu=2.0, lambda_bi=2.0))
+bad = b200als.ALS(cfg)
+bad.shard = b200als.Shard.from_env()
+try:
+    bad.fit_coo(flat, vals, (200, 150), tol=None, verbose=0)
+    raised = False
+except np.linalg.LinAlgError:
+    raised = True
+assert raised, "sharded fit of a non-SPD system did not raise LinAlgError"
+td.barrier()
 if td.get_rank() == 0:
     print("dist_check ok, worst rel diff", worst)
 td.destroy_process_group()
