@@ -28,7 +28,7 @@ from . import _lib, graph as _graph, hostrng as _hostrng, readback as _readback
 from ._lib import StepArgs, check, ptr
 from .config import ALSConfig
 from .dist import Shard
-from .sparse import Ratings, ratings_from_dense, ratings_from_flat, row_schedule
+from .sparse import Ratings, ratings_from_dense, ratings_from_flat, row_schedule, upload_flat_sharded
 
 SCALE_FACTOR = 0.1      # als.py:93 — std of the Gaussian factor init
 EPS = 1e-10             # als.py:94 — added to every ridge term
@@ -241,6 +241,11 @@ class ALS:
         with torch.cuda.device(dev):
             self._start_predraw(shape, features, init)
             try:
+                sh = self.shard
+                on_dev = isinstance(flat_idx, torch.Tensor) and flat_idx.is_cuda
+                if sh is not None and sh.active and not on_dev and os.environ.get("B200ALS_SHARDED_UPLOAD", "1") != "0":
+                    # every rank holds the same host arrays: each copies 1/N over PCIe, NVLink does the rest
+                    flat_idx, vals = upload_flat_sharded(flat_idx, vals, dev, sh)
                 ratings = ratings_from_flat(flat_idx, vals, shape, dev, sorted_input=sorted_input)
             except Exception:
                 self.__dict__.pop("_predraw", None)

@@ -123,6 +123,34 @@ def ratings_from_flat(flat_idx, vals, shape, device, sorted_input: bool = False,
                    perm[:nnz] if perm is not None else None)
 
 
+def upload_flat_sharded(flat_idx, vals, device, shard):
+    """Host (flat_idx, vals) -> device tensors on EVERY rank, each rank copying only its 1/N slice over PCIe and the
+    ranks all-gathering the slices over NVLink.  Contract of the sharded `fit_coo`: every rank is given the same
+    arrays (checked: same length on all ranks).  At the Netflix shape the whole list is 1.2 GB per rank; with 8 ranks
+    the host copy drops from ~48 ms to ~6 ms + a 2 ms all-gather."""
+    import torch.distributed as td
+    nnz = int(flat_idx.numel() if isinstance(flat_idx, torch.Tensor) else np.asarray(flat_idx).shape[0])
+    w, r = shard.world, shard.rank
+    lens = torch.tensor([nnz, -nnz], dtype=torch.int64, device=device)
+    td.all_reduce(lens, op=td.ReduceOp.MAX, group=shard.group)
+    if int(lens[0].item()) != nnz or int(-lens[1].item()) != nnz:
+        raise ValueError("sharded fit_coo: the ranks were given rating lists of different lengths")
+    per = max((nnz + w - 1) // w, 1)
+    lo, hi = min(r * per, nnz), min((r + 1) * per, nnz)
+
+    def part(x, dtype, np_dtype):
+        buf = torch.zeros(per, dtype=dtype, device=device)
+        if hi > lo:
+            if isinstance(x, torch.Tensor):
+                buf[:hi - lo].copy_(x[lo:hi].to(dtype), non_blocking=True)
+            else:
+                buf[:hi - lo].copy_(torch.from_numpy(np.ascontiguousarray(np.asarray(x)[lo:hi], dtype=np_dtype)))
+        full = torch.empty(w * per, dtype=dtype, device=device)
+        td.all_gather_into_tensor(full, buf, group=shard.group)
+        return full[:nnz]
+    return part(flat_idx, torch.int64, np.int64), part(vals, torch.float32, np.float32)
+
+
 def row_schedule(indptr: torch.Tensor):
     """Longest-first row order and the number of non-empty rows."""
     lib = _lib.load()
