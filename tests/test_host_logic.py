@@ -225,6 +225,20 @@ assert [g["rmse"] for g in got] == [0.5, 1.5, 2.5, 3.5, 4.5] and [g["by"] for g 
 # peer-mapped exchange is a CUDA facility: on CPU tensors the collective decision is "all-gather"
 assert s.share_replicas(dict(U=torch.zeros(4, 4))) is None
 tok = torch.zeros(1); s.order_ranks(tok)
+# sharded upload of the rating list: each rank copies 1/N, all ranks end with the whole list (ragged length)
+from b200als.sparse import upload_flat_sharded
+flat_all = np.arange(0, 3 * 1001, 3, dtype=np.int64)
+vals_all = (np.arange(1001) % 10 / 2.0 + 0.5)
+f_d, v_d = upload_flat_sharded(flat_all, vals_all, torch.device("cpu"), s)
+assert f_d.dtype == torch.int64 and v_d.dtype == torch.float32
+assert np.array_equal(f_d.numpy(), flat_all) and np.array_equal(v_d.numpy(), vals_all.astype(np.float32))
+f_d, v_d = upload_flat_sharded(torch.from_numpy(flat_all[:1]), torch.from_numpy(vals_all[:1]).float(), torch.device("cpu"), s)
+assert f_d.tolist() == [0] and v_d.tolist() == [0.5]
+try:
+    upload_flat_sharded(flat_all[: 10 + s.rank], vals_all[: 10 + s.rank], torch.device("cpu"), s)
+    raise AssertionError("lists of different lengths were accepted")
+except ValueError:
+    pass
 acc = torch.tensor([1.0 + s.rank, 10.0], dtype=torch.float64)
 s.all_reduce_sum(acc)
 assert acc.tolist() == [3.0, 20.0]
