@@ -21,7 +21,8 @@ numpy loop timed on this box's host cores over a bounded row sample.
 The default run (c4, one GPU) also carries `secondary`: the other configurations
 north_star states a target on, each a small record of its own — `c3` (k = 64, the
 50 %-of-roofline target), `c4k64`, `c3k96` on the tensor-core path next to
-`c3k96_ffma` (zero-padded tcgen05 against the scalar path), and `c2`: the
+`c3k96_ffma` (zero-padded tcgen05 against the scalar path), `c1` (the bundled shape
+with U/V + biases only, k = 32: launch-bound, reported for completeness), and `c2`: the
 reference's own workload (full model at the bundled shape), timed end to end as
 scripts/evaluate_models.py:245-255 times it, with the oracle port's whole fit on
 the same input beside it.  At N > 1 the line carries `sharded_vs_single`: three
@@ -264,7 +265,13 @@ def timed_iterations(ses, shard, K, W, dev, sampler=None):
     return float(tms.item()), phases, ses.launches, t0, t1
 
 
-def roofline_of(wl_shape, world, phases, ms_per_step):
+# dram__bytes_read.sum + dram__bytes_write.sum per launch of row_step_umma_kernel<128> from the one `ncu --set full`
+# capture of this configuration (C4, one GPU, tensor-core path): profiles/r02_ncu_c4_umma_k128_v5.txt.  Not measured by
+# this run; any other configuration reports null.
+NCU_TRAFFIC_C4_1GPU = {"user": 0.974320e9 + 249.351424e6, "item": 27.729372e9 + 985.316096e6}
+
+
+def roofline_of(wl_shape, world, phases, ms_per_step, paths=None):
     m, n, nnz, k = wl_shape
     peak, peak_kind = measured_peaks()
     rows_u, rows_i = (m + world - 1) // world, (n + world - 1) // world
@@ -272,10 +279,13 @@ def roofline_of(wl_shape, world, phases, ms_per_step):
     dom = max(("user", "item"), key=lambda p: phases[p])
     ach = cand[dom] / (phases[dom] * 1e-3) / 1e9 if phases[dom] > 0 else 0.0
     b_iter = cand["user"] + cand["item"]
+    captured = (wl_shape == WORKLOADS["c4"] and world == 1 and paths is not None and paths.get(dom) == 2)
+    traffic = NCU_TRAFFIC_C4_1GPU[dom] if captured else None
     return {"bound": "hbm", "kernel": f"row_step ({dom} half-step)", "achieved": ach, "peak": peak,
             "unit": "GB/s", "frac": ach / peak,
-            # dram__bytes of the launch is an ncu quantity; this run did not measure it (see profiles/ for captures)
-            "traffic": None, "peak_source": peak_kind,
+            # dram__bytes of the launch is an ncu quantity: the committed capture's figure where one exists, else null
+            "traffic": traffic, "traffic_source": ("profiles/r02_ncu_c4_umma_k128_v5.txt" if traffic else None),
+            "peak_source": peak_kind,
             "algorithmic_bytes_per_launch": cand[dom],
             "half_step_frac": {p: (cand[p] / (phases[p] * 1e-3) / 1e9 / peak if phases[p] > 0 else None)
                                for p in ("user", "item")},
@@ -517,7 +527,7 @@ def b200_arm(args):
         "clocks": clocks,
         "e2e": e2e,
         "gpu_launches": int(res["launches"] * K),
-        "roofline": roofline_of(shape, world, res["phases"], ms_per_step),
+        "roofline": roofline_of(shape, world, res["phases"], ms_per_step, res["paths"]),
         "phase_ms": res["phases"],
     }
     if svs is not None:
@@ -529,7 +539,7 @@ def b200_arm(args):
         # the other configurations north_star states a target on, each as its own small record
         sec = {}
         torch.cuda.empty_cache()
-        for name, p2 in (("c3", path), ("c4k64", path), ("c3k96", path), ("c3k96_ffma", 1)):
+        for name, p2 in (("c3", path), ("c4k64", path), ("c3k96", path), ("c3k96_ffma", 1), ("c1", 0)):
             shp = WORKLOADS[name.split("_")[0]]
             r2 = resident_run(b200als, shp, K, W, shard, p2, dev)
             sec[name] = {"workload": WORKLOAD_NAMES[name.split("_")[0]], "users": shp[0], "items": shp[1], "ratings": shp[2],
