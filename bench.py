@@ -508,7 +508,7 @@ def b200_arm(args):
     flat_h = res.pop("flat").cpu().pin_memory()
     vals_h = res.pop("vals").cpu().pin_memory()
     res.pop("rt")
-    e2e = e2e_run(b200als, shape, flat_h, vals_h, K, shard, path, dev)
+    e2e = None if args.no_e2e else e2e_run(b200als, shape, flat_h, vals_h, K, shard, path, dev)
     del flat_h, vals_h
 
     if rank != 0:
@@ -781,6 +781,7 @@ def main():
     ap.add_argument("--path", default="auto", choices=["auto", "ffma", "umma"])
     ap.add_argument("--no-cpu", action="store_true", help="skip the cpu_baseline legs")
     ap.add_argument("--no-secondary", action="store_true", help="skip the c3 / c4k64 / c3k96 / c2 records of the default run")
+    ap.add_argument("--no-e2e", action="store_true", help="kernel A/B runs only: skip the end-to-end leg (the line then has e2e null)")
     ap.add_argument("--no-parity", action="store_true", help="N > 1: skip the sharded_vs_single check")
     ap.add_argument("--c2-iters", type=int, default=20, help="iterations of the c2 record (scripts/als.py:52 uses 20)")
     ap.add_argument("--cpu-budget", type=float, default=15.0)

@@ -80,4 +80,29 @@ __device__ __forceinline__ int ld_stream_s32(const int* p) {
     return v;
 }
 
+// 1: the register-tile updates of the solvers (rank-4 row updates of the LDL^T, Gram tiles of the FFMA path) issue
+// packed fma.rn.f32x2 (SASS FFMA2: two IEEE fp32 FMAs per instruction on an aligned register pair, the multiplier
+// broadcast) instead of scalar FFMA.  Same operations on every entry in the same order, so the results are
+// bit-identical; what changes is the number of instructions on the fma pipe.  Measured on B200 (tools/ffma2_bench.cu,
+// profiles/r02_ffma2_microbench.txt): in isolation FFMA2 issues every 2.27 cycles against 1.05 for FFMA (no gain in
+// lanes per clock), but inside the LDL^T solver, where the update shares a sub-partition with dependent pivot chains,
+// the C4 user half-step went from 34.6 to 32.2 ms (profiles/r02_ffma2_ab.txt).
+#ifndef B200ALS_FFMA2
+#define B200ALS_FFMA2 1
+#endif
+
+__device__ __forceinline__ uint64_t pack_f32x2(float lo, float hi) {
+    uint64_t r;
+    asm("mov.b64 %0, {%1, %2};" : "=l"(r) : "f"(lo), "f"(hi));
+    return r;
+}
+__device__ __forceinline__ void unpack_f32x2(uint64_t v, float& lo, float& hi) {
+    asm("mov.b64 {%0, %1}, %2;" : "=f"(lo), "=f"(hi) : "l"(v));
+}
+__device__ __forceinline__ uint64_t fma_f32x2(uint64_t a, uint64_t b, uint64_t c) {
+    uint64_t d;
+    asm("fma.rn.f32x2 %0, %1, %2, %3;" : "=l"(d) : "l"(a), "l"(b), "l"(c));
+    return d;
+}
+
 }  // namespace b200als

@@ -125,10 +125,37 @@ __device__ __forceinline__ void sts_b64_nc(uint32_t a, uint32_t x, uint32_t y) {
 }
 __device__ __forceinline__ uint32_t bf162_bits(__nv_bfloat162 v) { return *reinterpret_cast<uint32_t*>(&v); }
 
+// (o0..o3) = (i0..i3) - t0 v0 - t1 v1 - t2 v2 - t3 v3, entry by entry in that order (t0 first)
+__device__ __forceinline__ void rank4_sub(float& o0, float& o1, float& o2, float& o3, const float i0, const float i1,
+                                          const float i2, const float i3, const float t0, const float t1, const float t2,
+                                          const float t3, const float4 v0, const float4 v1, const float4 v2,
+                                          const float4 v3) {
+#if B200ALS_FFMA2
+    const uint64_t T0 = pack_f32x2(-t0, -t0), T1 = pack_f32x2(-t1, -t1), T2 = pack_f32x2(-t2, -t2), T3 = pack_f32x2(-t3, -t3);
+    uint64_t x = pack_f32x2(i0, i1), y = pack_f32x2(i2, i3);
+    x = fma_f32x2(T0, pack_f32x2(v0.x, v0.y), x); y = fma_f32x2(T0, pack_f32x2(v0.z, v0.w), y);
+    x = fma_f32x2(T1, pack_f32x2(v1.x, v1.y), x); y = fma_f32x2(T1, pack_f32x2(v1.z, v1.w), y);
+    x = fma_f32x2(T2, pack_f32x2(v2.x, v2.y), x); y = fma_f32x2(T2, pack_f32x2(v2.z, v2.w), y);
+    x = fma_f32x2(T3, pack_f32x2(v3.x, v3.y), x); y = fma_f32x2(T3, pack_f32x2(v3.z, v3.w), y);
+    unpack_f32x2(x, o0, o1);
+    unpack_f32x2(y, o2, o3);
+#else
+    o0 = fmaf(-t3, v3.x, fmaf(-t2, v2.x, fmaf(-t1, v1.x, fmaf(-t0, v0.x, i0))));
+    o1 = fmaf(-t3, v3.y, fmaf(-t2, v2.y, fmaf(-t1, v1.y, fmaf(-t0, v0.y, i1))));
+    o2 = fmaf(-t3, v3.z, fmaf(-t2, v2.z, fmaf(-t1, v1.z, fmaf(-t0, v0.z, i2))));
+    o3 = fmaf(-t3, v3.w, fmaf(-t2, v2.w, fmaf(-t1, v1.w, fmaf(-t0, v0.w, i3))));
+#endif
+}
+
 // 0 (default): diag4; 1: diag4p, the software-pipelined variant — correct (parity suite green) but measured NOT faster
 // on B200: C4 user half-step 35.3 ms (unchanged), k = 64 shapes ~5 % slower (its 96-register solver starts to spill)
 #ifndef B200ALS_DIAG_PIPELINE
 #define B200ALS_DIAG_PIPELINE 0
+#endif
+// 1: the second half of a diagonal block's steps runs a copy of diag4 that updates only the window entries still inside
+// the block (3 groups of four instead of 7 at k = 128, 1 instead of 3 at k = 64)
+#ifndef B200ALS_DIAG_TAPER
+#define B200ALS_DIAG_TAPER 1
 #endif
 
 template <int K, int RPW>
@@ -193,10 +220,8 @@ struct Ldl {
             const float4 v1 = lds_f32x4(cw + S4 + 4u * c4);
             const float4 v2 = lds_f32x4(cw + 2u * S4 + 4u * c4);
             const float4 v3 = lds_f32x4(cw + 3u * S4 + 4u * c4);
-            a[c4 + 0] = fmaf(-t3, v3.x, fmaf(-t2, v2.x, fmaf(-t1, v1.x, fmaf(-t0, v0.x, a[c4 + 0]))));
-            a[c4 + 1] = fmaf(-t3, v3.y, fmaf(-t2, v2.y, fmaf(-t1, v1.y, fmaf(-t0, v0.y, a[c4 + 1]))));
-            a[c4 + 2] = fmaf(-t3, v3.z, fmaf(-t2, v2.z, fmaf(-t1, v1.z, fmaf(-t0, v0.z, a[c4 + 2]))));
-            a[c4 + 3] = fmaf(-t3, v3.w, fmaf(-t2, v2.w, fmaf(-t1, v1.w, fmaf(-t0, v0.w, a[c4 + 3]))));
+            rank4_sub(a[c4 + 0], a[c4 + 1], a[c4 + 2], a[c4 + 3], a[c4 + 0], a[c4 + 1], a[c4 + 2], a[c4 + 3],
+                      t0, t1, t2, t3, v0, v1, v2, v3);
         }
     }
 
@@ -216,6 +241,10 @@ struct Ldl {
     // tile_on (warp-uniform): the phase feeds a tensor-core update, so 1/sqrt(d) of the pivots is kept (in the
     // x array, unused until the back substitution) for the rows below.  final_step: the block's last four
     // columns — nothing of this warp is left to update.
+    // NG: groups of four window columns the rank-4 update writes.  After the step at position `it` of the block only
+    // RPW - 4 (it + 1) window entries are still inside the block (the window slides), so NG >= RPW/4 - 1 - it is enough;
+    // the columns behind them are never read again by this warp.
+    template <int NG = RPW / 4 - 1>
     static __device__ __forceinline__ void diag4(float (&a)[RPW], float& rhs, bool& ok, const float ridge,
                                                  const int r, const uint32_t cbs, const int j0, const bool tile_on,
                                                  const bool final_step) {
@@ -291,16 +320,30 @@ struct Ldl {
         const float w1 = fmaf(-w3, l31, fmaf(-w2, l21, t1));
         const float w0 = fmaf(-w3, l30, fmaf(-w2, l20, fmaf(-w1, l10, t0)));
         const uint32_t rw = raw + 4u * (uint32_t)j0;           // rho_{j0+c}[s] at rw + 4 (s K + c)
+        static_assert(NG >= 1 && NG <= RPW / 4 - 1, "update groups");
 #pragma unroll
-        for (int c4 = 4; c4 < RPW; c4 += 4) {
+        for (int c4 = 4; c4 <= 4 * NG; c4 += 4) {
             const float4 v0 = lds_f32x4(rw + 4u * (uint32_t)(0 * K + c4));
             const float4 v1 = lds_f32x4(rw + 4u * (uint32_t)(1 * K + c4));
             const float4 v2 = lds_f32x4(rw + 4u * (uint32_t)(2 * K + c4));
             const float4 v3 = lds_f32x4(rw + 4u * (uint32_t)(3 * K + c4));
-            a[c4 - 4] = fmaf(-w3, v3.x, fmaf(-w2, v2.x, fmaf(-w1, v1.x, fmaf(-w0, v0.x, a[c4 + 0]))));
-            a[c4 - 3] = fmaf(-w3, v3.y, fmaf(-w2, v2.y, fmaf(-w1, v1.y, fmaf(-w0, v0.y, a[c4 + 1]))));
-            a[c4 - 2] = fmaf(-w3, v3.z, fmaf(-w2, v2.z, fmaf(-w1, v1.z, fmaf(-w0, v0.z, a[c4 + 2]))));
-            a[c4 - 1] = fmaf(-w3, v3.w, fmaf(-w2, v2.w, fmaf(-w1, v1.w, fmaf(-w0, v0.w, a[c4 + 3]))));
+            rank4_sub(a[c4 - 4], a[c4 - 3], a[c4 - 2], a[c4 - 1], a[c4 + 0], a[c4 + 1], a[c4 + 2], a[c4 + 3],
+                      w0, w1, w2, w3, v0, v1, v2, v3);
+        }
+    }
+
+    // B200ALS_DIAG_TAPER == 2: the block's steps two at a time, each pair with the update width its first step needs
+    // (7, 5, 3, 1 groups at k = 128): RPW/8 copies of the step
+    template <int IT0>
+    static __device__ __forceinline__ void diag_pairs(float (&a)[RPW], float& rhs, bool& ok, const float ridge,
+                                                      const int r, const uint32_t cbs, const int jb, const bool tile_on) {
+        constexpr int STEPS = RPW / 4;
+        if constexpr (IT0 < STEPS) {
+            constexpr int NGP = (STEPS - 1 - IT0) > 0 ? (STEPS - 1 - IT0) : 1;
+#pragma unroll 1
+            for (int it = IT0; it < IT0 + 2; ++it)
+                diag4<NGP>(a, rhs, ok, ridge, r, cbs, jb + 4 * it, tile_on, it == STEPS - 1);
+            diag_pairs<IT0 + 2>(a, rhs, ok, ridge, r, cbs, jb, tile_on);
         }
     }
 
@@ -436,10 +479,8 @@ struct Ldl {
                 const float4 v2 = lds_f32x4(ci + 2u * S4i);
                 const float4 v3 = lds_f32x4(ci + 3u * S4i);
                 const float t0 = a[4 * ib], t1 = a[4 * ib + 1], t2 = a[4 * ib + 2], t3 = a[4 * ib + 3];
-                a[4 * gb + 0] = fmaf(-t3, v3.x, fmaf(-t2, v2.x, fmaf(-t1, v1.x, fmaf(-t0, v0.x, a[4 * gb + 0]))));
-                a[4 * gb + 1] = fmaf(-t3, v3.y, fmaf(-t2, v2.y, fmaf(-t1, v1.y, fmaf(-t0, v0.y, a[4 * gb + 1]))));
-                a[4 * gb + 2] = fmaf(-t3, v3.z, fmaf(-t2, v2.z, fmaf(-t1, v1.z, fmaf(-t0, v0.z, a[4 * gb + 2]))));
-                a[4 * gb + 3] = fmaf(-t3, v3.w, fmaf(-t2, v2.w, fmaf(-t1, v1.w, fmaf(-t0, v0.w, a[4 * gb + 3]))));
+                rank4_sub(a[4 * gb + 0], a[4 * gb + 1], a[4 * gb + 2], a[4 * gb + 3], a[4 * gb + 0], a[4 * gb + 1],
+                          a[4 * gb + 2], a[4 * gb + 3], t0, t1, t2, t3, v0, v1, v2, v3);
             }
             const float4 c0 = lds_f32x4(colb + rowoff);              // d, U10, U20, U30 of the group's triangle
             const float4 c1 = lds_f32x4(colb + S4 + rowoff);         // -, -,   U21, U31
@@ -505,10 +546,8 @@ struct Ldl {
                         const float4 v3 = lds_f32x4(ci + 3u * S4i);
                         const float t0 = a[4 * ib], t1 = a[4 * ib + 1], t2 = a[4 * ib + 2], t3 = a[4 * ib + 3];
                         const int c = H + 4 * jb;
-                        a[c + 0] = fmaf(-t3, v3.x, fmaf(-t2, v2.x, fmaf(-t1, v1.x, fmaf(-t0, v0.x, a[c + 0]))));
-                        a[c + 1] = fmaf(-t3, v3.y, fmaf(-t2, v2.y, fmaf(-t1, v1.y, fmaf(-t0, v0.y, a[c + 1]))));
-                        a[c + 2] = fmaf(-t3, v3.z, fmaf(-t2, v2.z, fmaf(-t1, v1.z, fmaf(-t0, v0.z, a[c + 2]))));
-                        a[c + 3] = fmaf(-t3, v3.w, fmaf(-t2, v2.w, fmaf(-t1, v1.w, fmaf(-t0, v0.w, a[c + 3]))));
+                        rank4_sub(a[c + 0], a[c + 1], a[c + 2], a[c + 3], a[c + 0], a[c + 1], a[c + 2], a[c + 3],
+                                  t0, t1, t2, t3, v0, v1, v2, v3);
                     }
                 }
 #pragma unroll
@@ -621,6 +660,20 @@ struct Ldl {
 #pragma unroll 1
                     for (int it = 1; it < RPW / 4; ++it)
                         diag4p<true>(a, rhs, ok, wp, rwp, ridge, r, cbs, p * RPW + 4 * it, it == RPW / 4 - 1);
+                }
+#elif B200ALS_DIAG_TAPER == 2
+                diag_pairs<0>(a, rhs, ok, ridge, r, cbs, p * RPW, tile_on);
+#elif B200ALS_DIAG_TAPER
+                // the first half of the block's steps updates the whole window, the second half only the
+                // RPW/2 - 4 entries that are still inside the block: two copies of the step instead of one
+                {
+                    constexpr int STEPS = RPW / 4, HALF = STEPS / 2;
+#pragma unroll 1
+                    for (int it = 0; it < HALF; ++it)
+                        diag4<STEPS - 1>(a, rhs, ok, ridge, r, cbs, p * RPW + 4 * it, tile_on, false);
+#pragma unroll 1
+                    for (int it = HALF; it < STEPS; ++it)
+                        diag4<HALF - 1>(a, rhs, ok, ridge, r, cbs, p * RPW + 4 * it, tile_on, it == STEPS - 1);
                 }
 #else
 #pragma unroll 1

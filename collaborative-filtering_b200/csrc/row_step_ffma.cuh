@@ -11,6 +11,11 @@
 #pragma once
 #include "row_solve.cuh"
 
+// the Gram register tile on packed FFMA2 (common.cuh); own switch so that it can be measured apart from the LDL^T's
+#ifndef B200ALS_FFMA2_GRAM
+#define B200ALS_FFMA2_GRAM B200ALS_FFMA2
+#endif
+
 namespace b200als {
 
 constexpr int FF_TR = 16;       // ratings per pipeline tile
@@ -209,10 +214,22 @@ __global__ void __launch_bounds__(FfmaCfg<KP, T>::THREADS) row_step_ffma_kernel(
                             av[v] = a4.x; av[v + 1] = a4.y; av[v + 2] = a4.z; av[v + 3] = a4.w;
                             bv[v] = b4.x; bv[v + 1] = b4.y; bv[v + 2] = b4.z; bv[v + 3] = b4.w;
                         }
+#if B200ALS_FFMA2_GRAM
+#pragma unroll
+                        for (int a = 0; a < T; ++a) {
+                            const uint64_t aa = pack_f32x2(av[a], av[a]);
+#pragma unroll
+                            for (int b = 0; b < T; b += 2) {
+                                const uint64_t x = fma_f32x2(aa, pack_f32x2(bv[b], bv[b + 1]), pack_f32x2(acc[a][b], acc[a][b + 1]));
+                                unpack_f32x2(x, acc[a][b], acc[a][b + 1]);
+                            }
+                        }
+#else
 #pragma unroll
                         for (int a = 0; a < T; ++a)
 #pragma unroll
                             for (int b = 0; b < T; ++b) acc[a][b] = fmaf(av[a], bv[b], acc[a][b]);
+#endif
                     }
                 }
                 if (tid < KP) {
