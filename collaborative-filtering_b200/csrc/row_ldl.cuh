@@ -154,9 +154,62 @@ __device__ __forceinline__ void rank4_sub(float& o0, float& o1, float& o2, float
 #endif
 // 1: the second half of a diagonal block's steps runs a copy of diag4 that updates only the window entries still inside
 // the block (3 groups of four instead of 7 at k = 128, 1 instead of 3 at k = 64)
+// 1: the forward substitution of the rows below a diagonal block runs in right-looking order (subst_tri_rl)
+#ifndef B200ALS_SUBST_RL
+#define B200ALS_SUBST_RL 1
+#endif
 #ifndef B200ALS_DIAG_TAPER
 #define B200ALS_DIAG_TAPER 1
 #endif
+
+// 1: the panel entries of the tensor-core update are scaled and split into bf16 hi + lo with packed FMUL2 / FADD2 and
+// two-instruction bf16 -> fp32 widenings (same IEEE operations per entry: identical bits)
+#ifndef B200ALS_PANEL2
+#define B200ALS_PANEL2 1
+#endif
+__device__ __forceinline__ uint64_t mul_f32x2(uint64_t a, uint64_t b) {
+    uint64_t d;
+    asm("mul.rn.f32x2 %0, %1, %2;" : "=l"(d) : "l"(a), "l"(b));
+    return d;
+}
+__device__ __forceinline__ uint64_t sub_f32x2(uint64_t a, uint64_t b) {
+    uint64_t d;
+    asm("sub.rn.f32x2 %0, %1, %2;" : "=l"(d) : "l"(a), "l"(b));
+    return d;
+}
+// w_k = u_k rs_k (k = 0..3) as bf16 hi + lo: four panel columns = 8 bytes of the row's core-matrix line at `ta` (hi)
+// and `ta + tile_lo` (lo)
+__device__ __forceinline__ void panel_store4(const float u0, const float u1, const float u2, const float u3,
+                                             const float4 rs, const uint32_t ta, const uint32_t tile_lo) {
+#ifdef B200ALS_MMA_NULL
+    const __nv_bfloat162 z = __floats2bfloat162_rn(0.0f, 0.0f);
+    sts_b64_nc(ta, bf162_bits(z), bf162_bits(z));
+    sts_b64_nc(ta + tile_lo, bf162_bits(z), bf162_bits(z));
+#elif B200ALS_PANEL2
+    const uint64_t w01 = mul_f32x2(pack_f32x2(u0, u1), pack_f32x2(rs.x, rs.y));
+    const uint64_t w23 = mul_f32x2(pack_f32x2(u2, u3), pack_f32x2(rs.z, rs.w));
+    float w0, w1, w2, w3;
+    unpack_f32x2(w01, w0, w1);
+    unpack_f32x2(w23, w2, w3);
+    const uint32_t h01 = bf162_bits(__floats2bfloat162_rn(w0, w1)), h23 = bf162_bits(__floats2bfloat162_rn(w2, w3));
+    // bf16 -> fp32 is the same bits in the upper half of the word
+    const uint64_t f01 = pack_f32x2(__uint_as_float(h01 << 16), __uint_as_float(h01 & 0xffff0000u));
+    const uint64_t f23 = pack_f32x2(__uint_as_float(h23 << 16), __uint_as_float(h23 & 0xffff0000u));
+    float l0, l1, l2, l3;
+    unpack_f32x2(sub_f32x2(w01, f01), l0, l1);
+    unpack_f32x2(sub_f32x2(w23, f23), l2, l3);
+    sts_b64_nc(ta, h01, h23);
+    sts_b64_nc(ta + tile_lo, bf162_bits(__floats2bfloat162_rn(l0, l1)), bf162_bits(__floats2bfloat162_rn(l2, l3)));
+#else
+    const float w0 = u0 * rs.x, w1 = u1 * rs.y, w2 = u2 * rs.z, w3 = u3 * rs.w;
+    const __nv_bfloat162 h01 = __floats2bfloat162_rn(w0, w1), h23 = __floats2bfloat162_rn(w2, w3);
+    const float2 f01 = __bfloat1622float2(h01), f23 = __bfloat1622float2(h23);
+    const __nv_bfloat162 l01 = __floats2bfloat162_rn(w0 - f01.x, w1 - f01.y);
+    const __nv_bfloat162 l23 = __floats2bfloat162_rn(w2 - f23.x, w3 - f23.y);
+    sts_b64_nc(ta, bf162_bits(h01), bf162_bits(h23));
+    sts_b64_nc(ta + tile_lo, bf162_bits(l01), bf162_bits(l23));
+#endif
+}
 
 template <int K, int RPW>
 struct Ldl {
@@ -500,19 +553,70 @@ struct Ldl {
             if (tile_on) {                                   // warp-uniform: this phase feeds the tensor-core update
                 // w_k = u_k / sqrt(d_k) as bf16 hi + lo, four panel columns = 8 bytes of the row's core-matrix line
                 const float4 rs = lds_f32x4(cbs + X_OFF + rowoff);
-#ifdef B200ALS_MMA_NULL
-                const float w0 = 0.0f, w1 = 0.0f, w2 = 0.0f, w3 = 0.0f;
-#else
-                const float w0 = u0 * rs.x, w1 = u1 * rs.y, w2 = u2 * rs.z, w3 = u3 * rs.w;
-#endif
-                const __nv_bfloat162 h01 = __floats2bfloat162_rn(w0, w1), h23 = __floats2bfloat162_rn(w2, w3);
-                const float2 f01 = __bfloat1622float2(h01), f23 = __bfloat1622float2(h23);
-                const __nv_bfloat162 l01 = __floats2bfloat162_rn(w0 - f01.x, w1 - f01.y);
-                const __nv_bfloat162 l23 = __floats2bfloat162_rn(w2 - f23.x, w3 - f23.y);
                 const int jj = 4 * gb;                       // column inside the panel
-                const uint32_t ta = tile_row + (uint32_t)((jj >> 3) * 128 + (jj & 7) * 2);
-                sts_b64_nc(ta, bf162_bits(h01), bf162_bits(h23));
-                sts_b64_nc(ta + tile_lo, bf162_bits(l01), bf162_bits(l23));
+                panel_store4(u0, u1, u2, u3, rs, tile_row + (uint32_t)((jj >> 3) * 128 + (jj & 7) * 2), tile_lo);
+            }
+        }
+    }
+
+    // The same substitution in RIGHT-LOOKING order (B200ALS_SUBST_RL): as soon as the triangle of column group gb is
+    // solved, its four multipliers are folded into every later group of the window — the rest of this half and, when
+    // `ext` is set (warp-uniform: the first half), the NC entries behind it.  Every entry still receives its column
+    // groups in ascending order, one fused multiply-add per column, so the results are bit-identical to subst_tri +
+    // the rectangle of subst; what changes is the address arithmetic: all loads of column group gb sit at
+    // (column s of the group) + 16 (g0 + gc) with gc a compile-time constant, i.e. FOUR base registers per group and
+    // immediates, where the left-looking order computes four addresses per (gb, ib) pair.
+    template <int NC>
+    static __device__ __forceinline__ void subst_tri_rl(float (&a)[RPW], float& rhs, const int r, const uint32_t cbs,
+                                                        const int J0, const uint32_t tile_row, const uint32_t tile_lo,
+                                                        const bool tile_on, const bool ext) {
+        static_assert(2 * NC <= RPW, "the extension is the second half of the window");
+        const int g0 = J0 >> 2;
+        const uint32_t row16 = 16u * (uint32_t)g0;
+#pragma unroll
+        for (int gb = 0; gb < NC / 4; ++gb) {
+            const int g = g0 + gb;
+            const uint32_t S4 = 4u * (uint32_t)(K - 4 * g);
+            const uint32_t colb = col_block(cbs, g);                 // element (i, 4 g + s) at colb + s S4 + 4 i
+            const uint32_t b0 = colb + row16, b1 = b0 + S4, b2 = b1 + S4, b3 = b2 + S4;   // rows 4 g0 .. of the group's columns
+            const float4 c0 = lds_f32x4(b0 + 16u * gb);              // d, U10, U20, U30 of the group's triangle
+            const float4 c1 = lds_f32x4(b1 + 16u * gb);              // -, -,   U21, U31
+            const float4 c2 = lds_f32x4(b2 + 16u * gb);              // -, -,   -,   U32
+            const float4 inv = lds_f32x4(cbs + INV_OFF + row16 + 16u * gb);
+            const float4 zz = lds_f32x4(cbs + Z_OFF + row16 + 16u * gb);
+            const float u0 = a[4 * gb], t0 = u0 * inv.x;
+            const float u1 = fmaf(-t0, c0.y, a[4 * gb + 1]), t1 = u1 * inv.y;
+            const float u2 = fmaf(-t1, c1.z, fmaf(-t0, c0.z, a[4 * gb + 2])), t2 = u2 * inv.z;
+            const float u3 = fmaf(-t2, c2.w, fmaf(-t1, c1.w, fmaf(-t0, c0.w, a[4 * gb + 3]))), t3 = u3 * inv.w;
+            rhs = fmaf(-t3, zz.w, fmaf(-t2, zz.z, fmaf(-t1, zz.y, fmaf(-t0, zz.x, rhs))));
+            const uint32_t own = 4u * (uint32_t)r - row16;           // this row inside the group's columns
+            sts_f32_nc(b0 + own, u0);
+            sts_f32_nc(b1 + own, u1);
+            sts_f32_nc(b2 + own, u2);
+            sts_f32_nc(b3 + own, u3);
+            a[4 * gb] = t0; a[4 * gb + 1] = t1; a[4 * gb + 2] = t2; a[4 * gb + 3] = t3;
+            // fold the group into the later groups of this half ...
+#pragma unroll
+            for (int gc = gb + 1; gc < NC / 4; ++gc) {
+                const float4 v0 = lds_f32x4(b0 + 16u * gc), v1 = lds_f32x4(b1 + 16u * gc);
+                const float4 v2 = lds_f32x4(b2 + 16u * gc), v3 = lds_f32x4(b3 + 16u * gc);
+                rank4_sub(a[4 * gc + 0], a[4 * gc + 1], a[4 * gc + 2], a[4 * gc + 3], a[4 * gc + 0], a[4 * gc + 1],
+                          a[4 * gc + 2], a[4 * gc + 3], t0, t1, t2, t3, v0, v1, v2, v3);
+            }
+            // ... and, in the first half, into the half behind it
+            if (ext) {
+#pragma unroll
+                for (int gc = NC / 4; gc < 2 * (NC / 4); ++gc) {
+                    const float4 v0 = lds_f32x4(b0 + 16u * gc), v1 = lds_f32x4(b1 + 16u * gc);
+                    const float4 v2 = lds_f32x4(b2 + 16u * gc), v3 = lds_f32x4(b3 + 16u * gc);
+                    rank4_sub(a[4 * gc + 0], a[4 * gc + 1], a[4 * gc + 2], a[4 * gc + 3], a[4 * gc + 0], a[4 * gc + 1],
+                              a[4 * gc + 2], a[4 * gc + 3], t0, t1, t2, t3, v0, v1, v2, v3);
+                }
+            }
+            if (tile_on) {                                   // warp-uniform: this phase feeds the tensor-core update
+                const float4 rs = lds_f32x4(cbs + X_OFF + row16 + 16u * gb);
+                const int jj = 4 * gb;                       // column inside the panel
+                panel_store4(u0, u1, u2, u3, rs, tile_row + (uint32_t)((jj >> 3) * 128 + (jj & 7) * 2), tile_lo);
             }
         }
     }
@@ -526,6 +630,17 @@ struct Ldl {
                                                  const bool tile_on) {
         constexpr int H = RPW / 2;
         static_assert(H % 8 == 0, "a half must be whole 8-column core matrices of the panel");
+#if B200ALS_SUBST_RL
+#pragma unroll 1
+        for (int hf = 0; hf < 2; ++hf) {
+            subst_tri_rl<H>(a, rhs, r, cbs, J0 + H * hf, tile_row + (uint32_t)(H / 8) * 128u * (uint32_t)hf, tile_lo, tile_on,
+                            hf == 0);
+            if (hf == 0) {
+#pragma unroll
+                for (int i = 0; i < H; ++i) a[i] = a[H + i];
+            }
+        }
+#else
 #pragma unroll 1
         for (int hf = 0; hf < 2; ++hf) {
             const int Jh = J0 + H * hf;
@@ -554,6 +669,7 @@ struct Ldl {
                 for (int i = 0; i < H; ++i) a[i] = a[H + i];
             }
         }
+#endif
     }
 
     // Factor + forward substitution.  load_window(p, a, is_last) fills a[c] = A[r][RPW p + c] from
