@@ -315,3 +315,32 @@ def test_rating_slabs_partition_matches_csr_csc():
             assert seg == sorted(set(seg))
             pairs_i.update((u, i) for u in seg)
     assert pairs_u == pairs_i and len(pairs_u) == total
+
+
+def test_library_sass_holds_the_sm100_instructions_the_design_claims():
+    """The built library is sm_100a code that really uses what DESIGN.md §4.1 says it uses: tcgen05 MMAs (SASS UTCHMMA)
+    and TMEM loads (LDTM) in both instantiations of the Gram kernel, and packed fp32 FMAs (FFMA2) in the solvers of the
+    tensor-core and of the FFMA path.  (cuobjdump ships with the CUDA toolkit; skipped where it is absent.)"""
+    import re
+    import shutil
+    import subprocess
+    import b200als
+    exe = shutil.which("cuobjdump") or "/usr/local/cuda/bin/cuobjdump"
+    if not os.path.exists(exe):
+        pytest.skip("cuobjdump not available")
+    sass = subprocess.run([exe, "-sass", b200als._lib.LIB_PATH], capture_output=True, text=True, timeout=300).stdout
+    assert "sm_100a" in sass
+    bodies = {}
+    for m in re.finditer(r"Function : (\S+)", sass):
+        end = sass.find("Function :", m.end())
+        bodies[m.group(1)] = sass[m.end(): end if end > 0 else len(sass)]
+    for K in (64, 128):
+        name = next(n for n in bodies if f"row_step_umma_kernelILi{K}E" in n)
+        body = bodies[name]
+        assert len(re.findall(r"\bUTCHMMA\b", body)) >= 6, name        # Gram (3 products) + trailing updates of the LDL^T
+        assert "LDTM" in body and "UTCBAR" in body, name
+        assert len(re.findall(r"\bFFMA2\b", body)) >= 60, name
+    ffma = [n for n in bodies if "row_step_ffma_kernel" in n]
+    assert len(ffma) >= 5
+    for n in ffma:
+        assert len(re.findall(r"\bFFMA2\b", bodies[n])) >= 32, n
