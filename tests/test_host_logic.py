@@ -344,3 +344,54 @@ def test_library_sass_holds_the_sm100_instructions_the_design_claims():
     assert len(ffma) >= 5
     for n in ffma:
         assert len(re.findall(r"\bFFMA2\b", bodies[n])) >= 32, n
+
+
+def test_factor_row_stride_and_float64_routing():
+    """Host rules that decide WHICH kernel a row runs on (als.py): the factor row stride that selects the zero-padded
+    tcgen05 kernels, and the rows that go to the float64 half-step (small ridge AND fewer than 4 k ratings)."""
+    import types
+    import torch
+    import b200als
+    from b200als import als as A
+    from b200als._lib import PATH_AUTO, PATH_FFMA, PATH_UMMA
+    # stride: (32, 64] -> 64, (64, 128] -> 128 on the tensor-core path; everything else 16-byte aligned rows
+    want = {(8, PATH_AUTO): 8, (32, PATH_AUTO): 32, (33, PATH_AUTO): 64, (50, PATH_AUTO): 64, (64, PATH_AUTO): 64,
+            (65, PATH_AUTO): 128, (96, PATH_AUTO): 128, (128, PATH_AUTO): 128, (129, PATH_AUTO): 132, (150, PATH_AUTO): 152,
+            (20, PATH_UMMA): 64, (64, PATH_UMMA): 64, (100, PATH_UMMA): 128, (50, PATH_FFMA): 52, (96, PATH_FFMA): 96}
+    for (k, path), ld in want.items():
+        assert A.factor_ld(k, path) == ld, (k, path)
+
+    cnt = torch.tensor([1, 300, 5, 1000, 0, 10], dtype=torch.int64)
+    indptr = torch.zeros(7, dtype=torch.int64)
+    indptr[1:] = torch.cumsum(cnt, 0)
+    rows = torch.tensor([3, 1, 5, 2, 0], dtype=torch.int32)                  # a schedule: longest first, row 4 is empty
+
+    def session(precision, path):
+        s = types.SimpleNamespace(model=types.SimpleNamespace(precision=precision), k=64)
+        s._fast_path = lambda factor_mode: path
+        return s
+
+    split = A.FitSession._precision_split
+    # scalar ridge below the tensor-core threshold (0.3): the rows with fewer than 4 k = 256 ratings go to float64
+    fast, slow = split(session("auto", PATH_UMMA), indptr, rows, 0.05, None, None, False)
+    assert fast.tolist() == [3, 1] and slow.tolist() == [5, 2, 0]
+    # 0.2 is below the tcgen05 threshold but above the FFMA one (0.1)
+    fast, slow = split(session("auto", PATH_FFMA), indptr, rows, 0.2, None, None, False)
+    assert fast.tolist() == rows.tolist() and slow is None
+    fast, slow = split(session("auto", PATH_UMMA), indptr, rows, 5.0, None, None, False)
+    assert fast.tolist() == rows.tolist() and slow is None
+    # per-row ridge (popularity-scaled lambda_v): only short rows whose OWN ridge is small
+    reg_row = torch.tensor([0.01, 0.01, 5.0, 0.01, 0.01, 0.2], dtype=torch.float32)
+    fast, slow = split(session("auto", PATH_UMMA), indptr, rows, 0.0, reg_row, None, False)
+    assert fast.tolist() == [3, 1, 2] and slow.tolist() == [5, 0]
+    # ... looked up through the slab's global row ids when the schedule is local
+    ids = torch.tensor([5, 4, 3, 2, 1, 0], dtype=torch.int64)
+    reg_glob = torch.tensor([5.0, 0.01, 0.01, 0.01, 0.01, 0.01], dtype=torch.float32)
+    fast, slow = split(session("auto", PATH_UMMA), indptr, rows, 0.0, reg_glob, ids, False)
+    assert fast.tolist() == [3, 1, 5] and slow.tolist() == [2, 0]          # local row 5 is global row 0: ridge 5.0
+    fast, slow = split(session("f32", PATH_UMMA), indptr, rows, 1e-4, None, None, False)
+    assert fast.tolist() == rows.tolist() and slow is None
+    fast, slow = split(session("f64", PATH_UMMA), indptr, rows, 5.0, None, None, False)
+    assert fast.numel() == 0 and slow.tolist() == rows.tolist()
+    with pytest.raises(ValueError):
+        split(session("double", PATH_UMMA), indptr, rows, 1.0, None, None, False)
