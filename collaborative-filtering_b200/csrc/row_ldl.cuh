@@ -158,6 +158,12 @@ __device__ __forceinline__ void rank4_sub(float& o0, float& o1, float& o2, float
 #ifndef B200ALS_SUBST_RL
 #define B200ALS_SUBST_RL 1
 #endif
+// 1: at k = 128 the right-looking substitution drops the dead writes of the multipliers into the window registers and
+// takes the panel flag as a compile-time constant (C4 user half-step -2.3 %; at k = 64 the same change costs 0.3 %
+// — its 80-register solver starts to spill — so it is not applied there)
+#ifndef B200ALS_SUBST_LEAN
+#define B200ALS_SUBST_LEAN 1
+#endif
 #ifndef B200ALS_DIAG_TAPER
 #define B200ALS_DIAG_TAPER 1
 #endif
@@ -214,6 +220,7 @@ __device__ __forceinline__ void panel_store4(const float u0, const float u1, con
 template <int K, int RPW>
 struct Ldl {
     static constexpr int NW = K / RPW;       // warps per group (4)
+    static constexpr bool SUBST_LEAN = B200ALS_SUBST_LEAN && K >= 128;
     static constexpr int RAWSZ = 4 * K + 8;  // floats of one raw-row scratch buffer: rho[4][K] | rhs[4] | 4 dummy words (stores of lanes that have nothing to store)
     static_assert(NW == 4, "a solver group is the four TMEM lane quadrants");
 
@@ -594,7 +601,9 @@ struct Ldl {
             sts_f32_nc(b1 + own, u1);
             sts_f32_nc(b2 + own, u2);
             sts_f32_nc(b3 + own, u3);
-            a[4 * gb] = t0; a[4 * gb + 1] = t1; a[4 * gb + 2] = t2; a[4 * gb + 3] = t3;
+            // the multipliers are consumed right here: nothing reads a[4 gb ..] again (the caller reloads the window),
+            // and the lean form drops these register writes
+            if constexpr (!SUBST_LEAN) { a[4 * gb] = t0; a[4 * gb + 1] = t1; a[4 * gb + 2] = t2; a[4 * gb + 3] = t3; }
             // fold the group into the later groups of this half ...
 #pragma unroll
             for (int gc = gb + 1; gc < NC / 4; ++gc) {
@@ -807,7 +816,10 @@ struct Ldl {
                 const uint32_t tile_lo = tile_half(tile_on ? p : 0);
                 named_bar_sync(bar_id, nthr);
                 LDL_TICK(12);
-                subst(a, rhs, r, cbs, p * RPW, tile_row, tile_lo, tile_on);
+                // rows below exist only in phases p <= NW - 2: when every such phase feeds a tensor-core update the flag
+                // is a compile-time constant and the four branches per pass around the panel stores go away
+                if constexpr (SUBST_LEAN && MMA_PHASES >= NW - 1) subst(a, rhs, r, cbs, p * RPW, tile_row, tile_lo, true);
+                else subst(a, rhs, r, cbs, p * RPW, tile_row, tile_lo, tile_on);
                 LDL_TICK(13);
             }
         }
