@@ -395,3 +395,24 @@ def test_factor_row_stride_and_float64_routing():
     assert fast.numel() == 0 and slow.tolist() == rows.tolist()
     with pytest.raises(ValueError):
         split(session("double", PATH_UMMA), indptr, rows, 1.0, None, None, False)
+
+
+def test_bench_reference_arm_prints_the_contract_line():
+    """`bench.py --impl reference` needs no GPU: it times the CPU port (oracle/) on a bounded sample.  The line must carry
+    the keys the driver reads, with the same `metric` / `unit` / `config` naming as the CUDA arm."""
+    import json
+    out = subprocess.run([sys.executable, os.path.join(REPO, "bench.py"), "--impl", "reference", "--workload", "tiny",
+                          "--steps", "1", "--warmup", "1"], capture_output=True, text=True, timeout=600, cwd=REPO)
+    assert out.returncode == 0, out.stderr[-2000:]
+    line = json.loads(out.stdout.strip().splitlines()[-1])
+    for key in ("impl", "metric", "value", "unit", "n_gpus", "steps", "warmup", "ms_per_step", "higher_is_better", "scaling",
+                "vs_baseline", "dtype", "data", "config", "cpu_baseline", "e2e"):
+        assert key in line, key
+    assert line["impl"] == "reference" and line["unit"] == "ratings/s" and line["higher_is_better"] is True
+    assert line["config"]["workload"] == "tiny_debug" and "model" in line["config"]
+    assert line["vs_baseline"] is None and line["value"] > 0
+    cb = line["cpu_baseline"]
+    assert cb["kind"] == "port" and cb["cores"] >= 1 and cb["value"] == line["value"] and "sample" in cb
+    e2e = line["e2e"]
+    assert e2e["value"] == line["value"] and e2e["unit"] == line["unit"]
+    assert e2e["h2d_bytes_per_step"] == 0 and e2e["d2h_bytes_per_step"] == 0
